@@ -1,0 +1,305 @@
+"""Pin the oracle against the UNMODIFIED reference and (re)generate tests/golden/.
+
+Runs only in the build container (needs /root/reference; the GPU box does not have it):
+
+    python oracle/pin_reference.py
+
+What it does
+  1. imports the reference modules with the scratch-layout recipe of SURVEY.md 8c
+     (``../mpc_data_clean.pkl`` and ``fwd_models/`` are resolved relative to the cwd at import,
+     model_scripts/basic_model.py:9, eval_models.py:18,28); matplotlib / seaborn / mpclab_common
+     are absent and are stubbed in ``sys.modules`` (they are never called on this path);
+  2. exports the data assets the tests need on the GPU box as plain arrays
+     (tests/golden/data/*.npy, tests/golden/checkpoints/*.npz) -- data, not source;
+  3. checks bit-identity oracle == reference for: dataset build + z-score (a1, a3), forward of all
+     16 checkpoints on every validation row/window (a2, a4, a5, stateless and stateful), the noise
+     model forward under a shared seed (a6), the history buffering of DynamicsNN.get_prediction
+     (a7), calc_error (a9);
+  4. drives the REFERENCE modules in a python loop (closed loop of DESIGN.md) and stores the
+     trajectories as golden vectors; checks oracle.rollout_* reproduces them bit-for-bit.
+Exit code 0 and "PINNED" on the last line when everything holds.
+"""
+from __future__ import annotations
+
+import contextlib
+import io
+import os
+import pickle
+import sys
+import tempfile
+import types
+
+import numpy as np
+import torch
+
+sys.dont_write_bytecode = True
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = "/root/reference"
+GOLD = os.path.join(ROOT, "tests", "golden")
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "mpc-deep-learning-sp24_b200"))
+
+from oracle import rollout_ref as R  # noqa: E402
+
+torch.set_num_threads(1)
+checks = []
+
+
+def check(name, ok):
+    checks.append((name, bool(ok)))
+    print(("ok   " if ok else "FAIL ") + name, flush=True)
+
+
+def bit_equal(a, b):
+    return a.shape == b.shape and torch.equal(a, b)
+
+
+# ---------------------------------------------------------------------------- 1. import
+def import_reference():
+    scratch = tempfile.mkdtemp(prefix="mpcdl_ref_")
+    os.makedirs(os.path.join(scratch, "model_data"))
+    os.symlink(f"{REF}/data/validation/mpc_data_clean.pkl", f"{scratch}/mpc_data_clean.pkl")
+    for d in ("fwd_models", "rnn_models"):
+        os.symlink(f"{REF}/model_data/{d}", f"{scratch}/model_data/{d}")
+    os.chdir(os.path.join(scratch, "model_data"))
+    for name in ("matplotlib", "matplotlib.pyplot", "seaborn", "mpclab_common",
+                 "mpclab_common.track", "mpclab_common.pytypes", "mpclab_common.models",
+                 "mpclab_common.models.model_types", "mpclab_common.models.dynamics_models"):
+        sys.modules[name] = types.ModuleType(name)
+    sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
+    sys.modules["mpclab_common.track"].get_track = lambda *a, **k: None
+
+    class _VS:  # VehicleState(t=0) is evaluated as a default argument, noise_model.py:69
+        def __init__(self, *a, **k):
+            pass
+    sys.modules["mpclab_common.pytypes"].VehicleState = _VS
+    sys.modules["mpclab_common.models.model_types"].DynamicBicycleConfig = object
+    sys.modules["mpclab_common.models.dynamics_models"].CasadiDynamicCLBicycle = object
+    sys.path.insert(0, f"{REF}/model_scripts")
+    sys.path.insert(0, REF)
+    import basic_model, deep_models, eval_models          # noqa: E401
+    import utils.data_utils as du
+    du.q_labels = ["v_long", "v_tran", "w_psi", "x", "y", "psi"]     # utils/data_utils.py:100
+    du.u_labels = ["u_a", "u_steer"]                                 # utils/data_utils.py:101
+    import noise_model
+    return basic_model, deep_models, eval_models, noise_model
+
+
+fwd, rnn, ev, nm = import_reference()
+
+
+# ---------------------------------------------------------------------------- 2. fixtures
+def export_fixtures():
+    os.makedirs(f"{GOLD}/data", exist_ok=True)
+    os.makedirs(f"{GOLD}/checkpoints", exist_ok=True)
+    for name in ("mpc_data_clean", "pid_data_clean"):
+        bags = pickle.load(open(f"{REF}/data/validation/{name}.pkl", "rb"))
+        assert len(bags) == 1
+        np.save(f"{GOLD}/data/{name}.npy", np.asarray(bags[0], dtype=np.float64))
+    for d in ("fwd_models", "rnn_models"):
+        for f in sorted(os.listdir(f"{REF}/model_data/{d}")):
+            sd = torch.load(f"{REF}/model_data/{d}/{f}", map_location="cpu")
+            np.savez(f"{GOLD}/checkpoints/{f[:-3]}.npz", **{k: v.numpy() for k, v in sd.items()})
+
+
+export_fixtures()
+from mpcdl import synth  # noqa: E402  (needs the data fixture written above)
+
+bags = synth.load_bags("mpc_data_clean")
+check("fixture rows == pickle rows (float64 exact)", bags == fwd.DATA)
+
+
+def ckpt(name):
+    return {k: torch.from_numpy(v) for k, v in np.load(f"{GOLD}/checkpoints/{name}.npz").items()}
+
+
+# ---------------------------------------------------------------------------- 3a. datasets
+mf, ml = R.mlp_dataset(bags)
+mst = R.zscore_stats(mf, ml)
+mfn, mln = R.apply_zscore(mf, ml, mst)
+ref_ds = fwd.dataset
+check("a1 MLP dataset+zscore bit-identical", bit_equal(mfn, ref_ds.featrs.cpu()) and bit_equal(mln, ref_ds.labels.cpu()))
+rf, rl = R.rnn_dataset(bags, 4)
+rst = R.zscore_stats(rf, rl)
+rfn, rln = R.apply_zscore(rf, rl, rst)
+ref_rds = rnn.dataset
+check("a3 RNN dataset+zscore bit-identical (T=4)", bit_equal(rfn, ref_rds.featrs.cpu()) and bit_equal(rln, ref_rds.labels.cpu()))
+check("a3 stats are per window position [4,8]", tuple(rst["f_mean"].shape) == (4, 8))
+np.savez(f"{GOLD}/stats.npz", **{f"mlp_{k}": v.numpy() for k, v in mst.items()},
+         **{f"rnn4_{k}": v.numpy() for k, v in rst.items()})
+
+# ---------------------------------------------------------------------------- 3b. forwards
+onestep = {}
+names_fwd = sorted(f[:-3] for f in os.listdir(f"{REF}/model_data/fwd_models"))
+names_rnn = sorted(f[:-3] for f in os.listdir(f"{REF}/model_data/rnn_models"))
+for name in names_fwd:
+    p = name.split("_")
+    ref_m = fwd.Basic_Model(8, int(p[1]), 6, int(p[2]), False).cpu()
+    ref_m.load_state_dict(torch.load(f"{REF}/model_data/fwd_models/{name}.pt", map_location="cpu"))
+    ref_m.eval()
+    mine, _ = R.build_from_name(name, ckpt(name))
+    with torch.no_grad():
+        yr, ym = ref_m(mfn), mine(mfn)
+    check(f"a2 {name} forward bit-identical on all {len(mfn)} rows", bit_equal(yr, ym))
+    onestep[name] = yr.numpy()
+    # a9: reference calc_error over the whole dataset (SAMPLE=False), batch 1
+    ev.SAMPLE = False
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        ev.calc_error(ref_ds, ref_m, name)
+    printed = [float(l.split(":")[1]) for l in buf.getvalue().splitlines() if ":" in l]
+    mae, rmse = R.calc_error(ym, mln)
+    check(f"a9 {name} calc_error {printed} vs oracle ({mae:.4f},{rmse:.4f})",
+          abs(printed[0] - mae) < 1e-4 and abs(printed[1] - rmse) < 1e-4)
+    onestep[name + "_err"] = np.asarray([mae, rmse])
+
+rnn.device = torch.device("cpu")   # init_hidden allocates on the module-global (deep_models.py:58)
+for name in names_rnn:
+    p = name.split("_")
+    cls = rnn.GRU_Model if p[0] == "GRU" else rnn.LSTM_Model
+    state_f = p[-1] == "True"
+    ref_m = cls(8, int(p[1]), 6, int(p[2]), state_f).cpu()
+    ref_m.load_state_dict(torch.load(f"{REF}/model_data/rnn_models/{name}.pt", map_location="cpu"))
+    ref_m.eval()
+    mine, meta = R.build_from_name(name, ckpt(name))
+    with torch.no_grad():
+        # stateless call: the reference zero-inits when not state_f or on the first call
+        ref_m.h_state = None
+        yr = ref_m(rfn)
+        ym, st1 = mine(rfn, mine.zero_state(len(rfn)))
+        ok = bit_equal(yr, ym)
+        if state_f:   # second call carries h_state (deep_models.py:61-65)
+            yr2 = ref_m(rfn)
+            ym2, _ = mine(rfn, st1)
+            ok = ok and bit_equal(yr2, ym2)
+            onestep[name + "_second"] = yr2.numpy()
+    check(f"a4/a5 {name} forward bit-identical on all {len(rfn)} windows (state_f={state_f})", ok)
+    onestep[name] = yr.numpy()
+    mae, rmse = R.calc_error(ym, rln)
+    onestep[name + "_err"] = np.asarray([mae, rmse])
+np.savez_compressed(f"{GOLD}/onestep.npz", **onestep)
+
+# ---------------------------------------------------------------------------- 3c. noise model
+import utils.pytorch_utils as ptu  # noqa: E402
+ptu.device = torch.device("cpu")
+torch.manual_seed(0)
+ref_noise = nm.FeedforwardNoiseModel(6, 2, 3, n_layers=2, size=32, activation="tanh",
+                                     output_activation="identity").eval()
+ref_noise.logger.setLevel("WARNING")   # forward() logs whole tensors at DEBUG (noise_model.py:38)
+my_noise = R.RefNoise(6, 2, 3, 2, 32, "tanh", "identity")
+my_noise.model.load_state_dict(ref_noise.model.state_dict())
+my_noise.eval()
+np.savez(f"{GOLD}/checkpoints/noise_seed0_h3_s32_l2.npz",
+         **{k: v.numpy() for k, v in ref_noise.model.state_dict().items()})
+qh = torch.as_tensor(np.asarray(bags[0]), dtype=torch.float32)[:512, R.Q_PERM].repeat(1, 3)
+uh = torch.as_tensor(np.asarray(bags[0]), dtype=torch.float32)[:512, 6:8].repeat(1, 3)
+with torch.no_grad():
+    torch.manual_seed(123)
+    nr = ref_noise(qh, uh)
+    torch.manual_seed(123)
+    eps = torch.randn(512, 6)
+    nmine = my_noise(qh, uh, eps)
+check("a6 noise forward bit-identical under a shared seed (eps = randn)", bit_equal(nr, nmine))
+
+dyn = nm.DynamicsNN(nominal_model=None, noise_model=ref_noise, dynamics_uses_frenet=False, history=3)
+hist = R._NoiseHistory(3)
+ok = True
+rows32 = torch.as_tensor(np.asarray(bags[0]), dtype=torch.float32)
+with torch.no_grad():
+    for t in range(6):
+        q, u = rows32[t, R.Q_PERM], rows32[t, 6:8]
+        torch.manual_seed(t)
+        pr = dyn.get_prediction(q.numpy(), u.numpy())
+        torch.manual_seed(t)
+        e = torch.randn(1, 6)
+        qq, uu = hist.push(q[None], u[None])
+        ok = ok and np.array_equal(pr, my_noise(qq, uu, e).numpy())
+check("a7 DynamicsNN.get_prediction history/left-pad semantics bit-identical (6 calls)", ok)
+
+# ---------------------------------------------------------------------------- 4. golden rollouts
+rows = synth.load_rows()
+gold = {}
+
+
+@torch.no_grad()
+def ref_loop_mlp(ref_m, st, s0, U, noise=None, seed=None):
+    """closed loop through the reference modules themselves (independent of oracle.rollout_*)."""
+    s, out = s0, []
+    dyn = nm.DynamicsNN(None, noise, False, history=3) if noise is not None else None
+    if seed is not None:
+        torch.manual_seed(seed)
+    for t in range(U.shape[1]):
+        x = (torch.cat([s, U[:, t]], -1) - st["f_mean"]) / st["f_std"]
+        nxt = ref_m(x) * st["l_std"] + st["l_mean"]
+        if noise is not None:   # batch 1 only: the reference's wrapper "does not support parallel"
+            res = dyn.get_prediction(s[0, R.Q_PERM].numpy(), U[0, t].numpy())
+            nxt = nxt + torch.from_numpy(res)[:, R.Q_INV]
+        out.append(nxt)
+        s = nxt
+    return torch.stack(out, 1)
+
+
+@torch.no_grad()
+def ref_loop_rnn(ref_m, st, win0, U):
+    win, out = win0, []
+    ref_m.h_state = None
+    for t in range(U.shape[1]):
+        y = ref_m((win - st["f_mean"]) / st["f_std"])
+        nxt = y * st["l_std"] + st["l_mean"]
+        out.append(nxt)
+        win = torch.cat([win[:, 1:], torch.cat([nxt, U[:, t]], -1)[:, None]], 1)
+    return torch.stack(out, 1)
+
+
+N, H = 64, 24
+s0, U = synth.make_inputs(rows, N, H, window=0, seed=0)
+win0, Uw = synth.make_inputs(rows, N, H, window=4, seed=0)
+gold["s0"], gold["U"], gold["win0"], gold["Uw"] = s0.numpy(), U.numpy(), win0.numpy(), Uw.numpy()
+for name in names_fwd:
+    p = name.split("_")
+    ref_m = fwd.Basic_Model(8, int(p[1]), 6, int(p[2]), False).cpu().eval()
+    ref_m.load_state_dict(torch.load(f"{REF}/model_data/fwd_models/{name}.pt", map_location="cpu"))
+    tr = ref_loop_mlp(ref_m, mst, s0, U)
+    mine, _ = R.build_from_name(name, ckpt(name))
+    to, _ = R.rollout_mlp(mine, mst, s0, U)
+    check(f"rollout {name} N={N} H={H}: oracle == reference loop (bit)", bit_equal(tr, to))
+    gold[name] = tr.numpy()
+for name in names_rnn:
+    p = name.split("_")
+    cls = rnn.GRU_Model if p[0] == "GRU" else rnn.LSTM_Model
+    state_f = p[-1] == "True"
+    ref_m = cls(8, int(p[1]), 6, int(p[2]), state_f).cpu().eval()
+    ref_m.load_state_dict(torch.load(f"{REF}/model_data/rnn_models/{name}.pt", map_location="cpu"))
+    tr = ref_loop_rnn(ref_m, rst, win0, Uw)
+    mine, _ = R.build_from_name(name, ckpt(name))
+    to, _, _ = R.rollout_rnn(mine, rst, win0, Uw, stateful=state_f)
+    check(f"rollout {name} N={N} H={H} stateful={state_f}: oracle == reference loop (bit)", bit_equal(tr, to))
+    gold[name] = tr.numpy()
+
+# noise-injected MLP rollout, batch 1 (the reference wrapper is batch-1 only), shared seed
+ref_m = fwd.Basic_Model(8, 64, 6, 4, False).cpu().eval()
+ref_m.load_state_dict(torch.load(f"{REF}/model_data/fwd_models/Basic_64_4_32.pt", map_location="cpu"))
+tr = ref_loop_mlp(ref_m, mst, s0[:1], U[:1], noise=ref_noise, seed=7)
+torch.manual_seed(7)
+eps1 = torch.stack([torch.randn(1, 6) for _ in range(H)], 1)
+mine, _ = R.build_from_name("Basic_64_4_32", ckpt("Basic_64_4_32"))
+to, _ = R.rollout_mlp(mine, mst, s0[:1], U[:1], noise=my_noise, eps=eps1)
+check("rollout Basic_64_4_32 + noise (batch 1, seed 7): oracle == reference loop (bit)", bit_equal(tr, to))
+gold["Basic_64_4_32_noise_b1"], gold["eps_b1"] = tr.numpy(), eps1.numpy()
+
+# batched noise + cost goldens come from the (now pinned) oracle
+eps = synth.make_eps(N, H, seed=1)
+cost = synth.make_cost(rows, H)
+gold["eps"] = eps.numpy()
+gold["cost_ref"], gold["cost_qw"], gold["cost_rw"] = (c.numpy() for c in cost)
+to, co = R.rollout_mlp(mine, mst, s0, U, noise=my_noise, eps=eps, cost=cost)
+gold["Basic_64_4_32_noise"], gold["Basic_64_4_32_noise_cost"] = to.numpy(), co.numpy()
+g, _ = R.build_from_name("GRU_64_4_4_16_False", ckpt("GRU_64_4_4_16_False"))
+to, co, _ = R.rollout_rnn(g, rst, win0, Uw, noise=my_noise, eps=eps, cost=cost)
+gold["GRU_64_4_4_16_False_noise"], gold["GRU_64_4_4_16_False_noise_cost"] = to.numpy(), co.numpy()
+np.savez_compressed(f"{GOLD}/rollouts.npz", **gold)
+
+bad = [n for n, ok in checks if not ok]
+print(f"{len(checks) - len(bad)}/{len(checks)} checks passed")
+print("PINNED" if not bad else "NOT PINNED: " + "; ".join(bad))
+sys.exit(0 if not bad else 1)
