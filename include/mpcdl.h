@@ -1,0 +1,119 @@
+/* mpcdl.h -- C ABI of the fused B200 (sm_100a) rollout kernels for the learned BARC vehicle-dynamics
+ * models of itsjoshzhang/MPC-deep-learning-sp24.
+ *
+ * The reference exposes this path only as Python nn.Modules (it has no C ABI and no batched or
+ * multi-step rollout).  Each entry point below names the reference interface
+ * it replaces (file:line relative to the reference repo).  All pointers marked "device" are CUDA
+ * device pointers owned by the caller; the library borrows them for the duration of the call,
+ * launches on the given stream and returns without synchronising.  Status: 0 = ok, < 0 = error
+ * (text via mpcdl_last_error(), thread-local).  There is no CPU fallback.
+ *
+ * Row / state conventions (scripts/setup_data.py:70-80):
+ *   frame   = [x, y, psi, w_psi, v_long, v_tran, u_a, u_steer]   state = frame[0:6], control = frame[6:8]
+ *   noise q = [v_long, v_tran, w_psi, x, y, psi]                  (model_scripts/noise_model.py:108)
+ */
+#ifndef MPCDL_H
+#define MPCDL_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPCDL_VERSION 100
+
+enum { MPCDL_MLP = 0, MPCDL_GRU = 1, MPCDL_LSTM = 2 };
+enum { MPCDL_ACT_IDENTITY = 0, MPCDL_ACT_RELU = 1, MPCDL_ACT_TANH = 2, MPCDL_ACT_SIGMOID = 3 };
+enum {
+    MPCDL_OK = 0,
+    MPCDL_ERR_ARG = -1,        /* bad shape / null pointer / unsupported size           */
+    MPCDL_ERR_UNSUPPORTED = -2,/* hidden size / layer count without a compiled kernel    */
+    MPCDL_ERR_CUDA = -3,       /* CUDA runtime error (text has cudaGetErrorString)       */
+    MPCDL_ERR_DEVICE = -4      /* not an sm_100 device                                   */
+};
+
+/* Architecture of a dynamics model.
+ *   MLP : Basic_Model(inputs=8, hidden, output=6, layers, do_drop)    model_scripts/basic_model.py:45-56
+ *   GRU : GRU_Model(8, hidden, 6, layers, state_f)                    model_scripts/deep_models.py:46-55
+ *   LSTM: LSTM_Model(8, hidden, 6, layers, state_f)                   model_scripts/deep_models.py:70-79
+ * window = FT_SIZE frames per sample for GRU/LSTM (deep_models.py:99), 0 for the MLP. */
+typedef struct {
+    int32_t kind, hidden, layers, window;
+} mpcdl_model_desc;
+
+/* Size in floats of the packed weight blob for `desc`, or 0 if unsupported. */
+size_t mpcdl_blob_floats(const mpcdl_model_desc* desc);
+
+/* Pack a Basic_Model state_dict (host pointers, torch layout W[out][in], FP32) into `blob` (host).
+ * W/b hold layers+2 entries: Linear(8,h), layers x Linear(h,h), Linear(h,6) -- the nn.Linear
+ * entries of `self.layers` in order, Dropout entries skipped (basic_model.py:48-56). */
+int mpcdl_pack_mlp(const mpcdl_model_desc* desc, const float* const* W, const float* const* b, float* blob);
+
+/* Pack a GRU_Model / LSTM_Model state_dict: w_ih[l] = {gru,lstm}.weight_ih_l{l} [G*h][in_l],
+ * w_hh[l] [G*h][h], b_ih[l], b_hh[l] [G*h] (G = 3: r,z,n / 4: i,f,g,o), fc_w = full_c.weight [6][h],
+ * fc_b [6]  (deep_models.py:54-55, 78-79; key names in SURVEY.md App. B). */
+int mpcdl_pack_rnn(const mpcdl_model_desc* desc, const float* const* w_ih, const float* const* w_hh,
+                   const float* const* b_ih, const float* const* b_hh, const float* fc_w, const float* fc_b,
+                   float* blob);
+
+/* Residual-noise net = utils/pytorch_utils.py:19-57 build_mlp((6+2)*history -> size x n_layers -> 12)
+ * as used by FeedforwardNoiseModel (model_scripts/noise_model.py:19-40).  W[i] [out][in], b[i] [out],
+ * n_layers+1 entries.  Returns floats written (mpcdl_noise_blob_floats gives the size). */
+size_t mpcdl_noise_blob_floats(int history, int size, int n_layers);
+int mpcdl_pack_noise(int history, int size, int n_layers, const float* const* W, const float* const* b, float* blob);
+
+typedef struct {
+    mpcdl_model_desc model;
+    int32_t stateful;          /* GRU/LSTM state_f: carry hidden state step to step (deep_models.py:61-65) */
+    const float* wblob;        /* device: mpcdl_pack_* output                                              */
+    const float* norm;         /* device: f_mean[T*8] f_std[T*8] l_mean[6] l_std[6], T = max(window,1)
+                                  (RobotData.norm statistics, basic_model.py:28-35 / deep_models.py:29-36) */
+    const float* init;         /* device: s0 [N,6] (MLP) or window [N,T,8] (GRU/LSTM)                      */
+    const float* U;            /* device: controls [N,H,2]                                                 */
+    float* states;             /* device: out [N,H,6] predicted states (states[:,t] = s_{t+1}), or NULL    */
+    float* costs;              /* device: out [N] accumulated cost, or NULL                                */
+    const float* cost_ref;     /* device: [H,6] reference path for the quadratic tracking cost, or NULL    */
+    float cost_qw[6], cost_rw[2];
+    /* residual-noise injection (noise_model.py:86-103): next = pred + mu + softplus(p) * eps */
+    const float* noise_wblob;  /* device: mpcdl_pack_noise output, or NULL = no noise                      */
+    int32_t noise_history, noise_size, noise_layers, noise_act;
+    const float* eps;          /* device: [N,H,6] standard-normal draws, or NULL = in-kernel Philox(seed)   */
+    uint64_t seed;
+    int64_t traj_offset;       /* global index of trajectory 0 of this shard (Philox key)                  */
+    float* carry;              /* device, stateful only: [L][N][hidden] h (+ [L][N][hidden] c for LSTM),
+                                  initial state in, final state out (deep_models.py h_state)               */
+    int64_t N;
+    int32_t H;
+    /* tuning overrides, 0 = automatic */
+    int32_t tune_rt, tune_ntg, tune_nslots, tune_kc;
+} mpcdl_rollout_args;
+
+/* The fused closed loop.  Replaces, batched over N trajectories and H steps in ONE launch:
+ *   Basic_Model.forward   basic_model.py:58-61      GRU_Model.forward  deep_models.py:60-66
+ *   LSTM_Model.forward    deep_models.py:85-92      z-score            basic_model.py:34 / deep_models.py:35
+ *   FeedforwardNoiseModel.forward noise_model.py:34-40, history buffering noise_model.py:95-103
+ *   the feedback loop of run_dynamics_model(open_loop=True)  scripts/test_model.py:67-87
+ * H = 1 with identity statistics is the Module.forward used by eval_models.calc_error
+ * (model_scripts/eval_models.py:86). `stream` is a cudaStream_t (NULL = default stream). */
+int mpcdl_rollout(const mpcdl_rollout_args* args, void* stream);
+
+/* What mpcdl_rollout would launch for these args (no launch): tile size, grid, smem, config. */
+typedef struct {
+    int32_t rt, rj, n_tg, tile_traj, threads, grid, smem_bytes, resident, nslots, slot_floats, ntiles;
+} mpcdl_plan;
+int mpcdl_rollout_plan(const mpcdl_rollout_args* args, mpcdl_plan* plan);
+
+/* FP32 FFMA peak micro-kernel (register-only FMA chains on every SM); used by bench.py to measure
+ * the FP32 roofline denominator on the box it runs on.  out: device buffer of >= grid*256 floats.
+ * FLOPs per launch = 2 * grid * 256 * iters * 64. */
+int mpcdl_ffma_peak(float* out_device, int iters, int grid, void* stream);
+
+const char* mpcdl_last_error(void);
+int mpcdl_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPCDL_H */

@@ -1,0 +1,330 @@
+// C ABI (include/mpcdl.h): weight packers, launch planning, argument checks, error strings.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "../../include/mpcdl.h"
+#include "launch.h"
+
+using namespace mpcdl;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+const int kMlpHid[] = {16, 32, 64, 128, 256};
+bool hid_supported(int hid) { return std::find(std::begin(kMlpHid), std::end(kMlpHid), hid) != std::end(kMlpHid); }
+
+int gates(int kind) { return kind == MPCDL_GRU ? 3 : kind == MPCDL_LSTM ? 4 : 1; }
+
+int check_desc(const mpcdl_model_desc* d) {
+    if (!d) return fail(MPCDL_ERR_ARG, "model desc is NULL");
+    if (d->kind < MPCDL_MLP || d->kind > MPCDL_LSTM) return fail(MPCDL_ERR_ARG, "unknown model kind %d", d->kind);
+    if (!hid_supported(d->hidden))
+        return fail(MPCDL_ERR_UNSUPPORTED, "hidden=%d has no compiled kernel (supported: 16,32,64,128,256)", d->hidden);
+    if (d->layers < 1 || d->layers > MAX_LAYERS) return fail(MPCDL_ERR_UNSUPPORTED, "layers=%d outside [1,%d]", d->layers, MAX_LAYERS);
+    if (d->kind != MPCDL_MLP && (d->window < 1 || d->window > MAX_WINDOW))
+        return fail(MPCDL_ERR_UNSUPPORTED, "window=%d outside [1,%d]", d->window, MAX_WINDOW);
+    return MPCDL_OK;
+}
+
+// blob layout: a pure function of the model description
+uint32_t build_parts(const mpcdl_model_desc& d, PartDesc* parts, int& nparts) {
+    uint32_t off = 0;
+    const int h = d.hidden;
+    nparts = 0;
+    auto add = [&](int nrows, int width, int bias) {
+        PartDesc p;
+        p.off = off; p.nrows = (uint16_t)nrows; p.width = (uint16_t)width; p.bias_floats = (uint32_t)bias;
+        parts[nparts++] = p;
+        off += bias + (uint32_t)nrows * width;
+    };
+    if (d.kind == MPCDL_MLP) {
+        add(8, h, h);
+        for (int l = 0; l < d.layers; ++l) add(h, h, h);
+        add(h, 8, 8);
+    } else {
+        const int G = gates(d.kind);
+        for (int l = 0; l < d.layers; ++l) {
+            add(l == 0 ? 8 : h, G * h, 4 * h);
+            add(h, G * h, 0);
+        }
+        add(h, 8, 8);
+    }
+    return off;
+}
+
+struct Plan {
+    int rt, rj, n_tg, TN, nct, grid, smem_bytes, resident, nslots, slot_floats, ntiles;
+};
+
+int g_num_sms = 0, g_cc_major = 0;
+int device_info() {
+    if (g_num_sms) return MPCDL_OK;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&g_cc_major, cudaDevAttrComputeCapabilityMajor, dev);
+    if (e != cudaSuccess) { g_num_sms = 0; return fail(MPCDL_ERR_CUDA, "CUDA device query failed: %s", cudaGetErrorString(e)); }
+    return MPCDL_OK;
+}
+
+void fill_model(ModelParams& m, const mpcdl_rollout_args& a, const Plan& pl, uint32_t total) {
+    m.blob = a.wblob;
+    m.hid = a.model.hidden; m.layers = a.model.layers;
+    m.window = a.model.kind == MPCDL_MLP ? 0 : a.model.window;
+    m.stateful = a.model.kind == MPCDL_MLP ? 0 : (a.stateful != 0);
+    m.data_off = 0; m.data_floats = total;
+    m.n_tg = pl.n_tg; m.TN = pl.TN; m.n_cthreads = pl.nct;
+    m.nslots = pl.nslots; m.slot_floats = pl.slot_floats; m.resident = pl.resident;
+}
+
+void fill_noise(NoiseParams& nz, const mpcdl_rollout_args& a) {
+    memset(&nz, 0, sizeof(nz));
+    if (!a.noise_wblob) return;
+    nz.blob = a.noise_wblob; nz.enabled = 1;
+    nz.hist = a.noise_history; nz.size = a.noise_size; nz.nlayers = a.noise_layers; nz.act = a.noise_act;
+    nz.in_dim = 8 * a.noise_history;
+    nz.blob_floats = (int)mpcdl_noise_blob_floats(a.noise_history, a.noise_size, a.noise_layers);
+}
+
+int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
+    const mpcdl_model_desc& d = a.model;
+    const bool rnn = d.kind != MPCDL_MLP;
+    PartDesc parts[MAX_PARTS];
+    int nparts;
+    const uint32_t total = build_parts(d, parts, nparts);
+    int width_max = 0, bias_max = 0;
+    for (int i = 0; i < nparts; ++i) { width_max = std::max<int>(width_max, parts[i].width); bias_max = std::max<int>(bias_max, parts[i].bias_floats); }
+
+    const int rts_mlp[] = {2, 4, 8}, rts_rnn[] = {2, 4, 8};
+    const int rj = rnn ? rnn_rj(d.hidden) : mlp_rj(d.hidden);
+    const int G = gates(d.kind), NGA = rnn ? 4 : 1;
+    double best_cost = 1e300;
+    bool found = false;
+    for (int rt : (rnn ? rts_rnn : rts_mlp)) {
+        // must match the instantiation lists in launch.h
+        if (!rnn && rt == 4 && d.hidden != 64) continue;
+        if (rnn && rt == 8 && d.hidden != 64) continue;
+        if (a.tune_rt && rt != a.tune_rt) continue;
+        const int n_jg = d.hidden / rj;
+        if (rt > n_jg) continue;                                   // owner threads: TN <= consumer threads
+        const int maxc = rnn ? rnn_max_consumers(rt, rj) : mlp_max_consumers();
+        const int ntg_max = maxc / n_jg;
+        for (int n_tg = ntg_max; n_tg >= 1; --n_tg) {
+            if (a.tune_ntg && n_tg != a.tune_ntg) continue;
+            Plan pl;
+            pl.rt = rt; pl.rj = rj; pl.n_tg = n_tg; pl.TN = n_tg * rt;
+            pl.nct = (n_tg * n_jg + 31) / 32 * 32;
+            pl.resident = (!a.tune_nslots && total <= 24576u) ? 1 : 0;
+            int kc_rows = a.tune_kc ? a.tune_kc : std::max(1, 4096 / width_max);
+            pl.slot_floats = std::max(kc_rows * width_max, bias_max);
+            pl.nslots = pl.resident ? 1 : (a.tune_nslots ? a.tune_nslots : 3);
+            ModelParams m;
+            memset(&m, 0, sizeof(m));
+            fill_model(m, a, pl, total);
+            NoiseParams nz;
+            fill_noise(nz, a);
+            SmemLayout L = make_layout(m, nz, rnn);
+            pl.smem_bytes = L.total * 4;
+            if (pl.smem_bytes > SMEM_LIMIT) continue;
+            pl.ntiles = (int)((a.N + pl.TN - 1) / pl.TN);
+            pl.grid = std::min(pl.ntiles, num_sms);
+            const int rounds = (pl.ntiles + num_sms - 1) / num_sms;
+            const double instr = NGA * rt * rj * (rnn ? (double)G / NGA * 1.0 : 1.0) + (rt + 3) / 4 + (G * rj + 3) / 4;
+            const double cost = rounds * instr * std::max(pl.nct / 128.0, 2.0) * (1.0 + 0.01 * (8 - rt));
+            if (cost < best_cost) { best_cost = cost; best = pl; found = true; }
+        }
+    }
+    if (!found) return fail(MPCDL_ERR_UNSUPPORTED, "no launch configuration fits (hidden=%d window=%d)", d.hidden, d.window);
+    return MPCDL_OK;
+}
+
+int check_args(const mpcdl_rollout_args* a) {
+    if (!a) return fail(MPCDL_ERR_ARG, "args is NULL");
+    int rc = check_desc(&a->model);
+    if (rc) return rc;
+    if (a->N < 1 || a->H < 1) return fail(MPCDL_ERR_ARG, "N=%lld H=%d must be >= 1", (long long)a->N, a->H);
+    if (!a->wblob || !a->norm || !a->init || !a->U) return fail(MPCDL_ERR_ARG, "wblob/norm/init/U must be non-NULL device pointers");
+    if (!a->states && !a->costs) return fail(MPCDL_ERR_ARG, "both outputs (states, costs) are NULL");
+    if (a->model.kind != MPCDL_MLP && a->stateful && !a->carry) return fail(MPCDL_ERR_ARG, "stateful rollout needs a carry buffer");
+    if (a->noise_wblob) {
+        if (a->noise_history < 1 || a->noise_history > 8) return fail(MPCDL_ERR_UNSUPPORTED, "noise history=%d outside [1,8]", a->noise_history);
+        if (a->noise_size < 4 || a->noise_size > 64 || a->noise_size % 4) return fail(MPCDL_ERR_UNSUPPORTED, "noise size=%d must be a multiple of 4 in [4,64]", a->noise_size);
+        if (a->noise_layers < 0 || a->noise_layers > MAX_NOISE_LAYERS) return fail(MPCDL_ERR_UNSUPPORTED, "noise n_layers=%d outside [0,%d]", a->noise_layers, MAX_NOISE_LAYERS);
+        if (a->noise_act < MPCDL_ACT_IDENTITY || a->noise_act > MPCDL_ACT_SIGMOID) return fail(MPCDL_ERR_UNSUPPORTED, "noise activation %d unsupported", a->noise_act);
+    }
+    return MPCDL_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------ C ABI
+extern "C" {
+
+const char* mpcdl_last_error(void) { return g_err; }
+int mpcdl_version(void) { return MPCDL_VERSION; }
+
+size_t mpcdl_blob_floats(const mpcdl_model_desc* desc) {
+    if (check_desc(desc)) return 0;
+    PartDesc parts[MAX_PARTS];
+    int n;
+    return build_parts(*desc, parts, n);
+}
+
+int mpcdl_pack_mlp(const mpcdl_model_desc* desc, const float* const* W, const float* const* b, float* blob) {
+    int rc = check_desc(desc);
+    if (rc) return rc;
+    if (desc->kind != MPCDL_MLP || !W || !b || !blob) return fail(MPCDL_ERR_ARG, "mpcdl_pack_mlp: bad arguments");
+    PartDesc parts[MAX_PARTS];
+    int n;
+    uint32_t total = build_parts(*desc, parts, n);
+    std::fill(blob, blob + total, 0.f);
+    const int h = desc->hidden;
+    for (int p = 0; p < n; ++p) {
+        const int in = p == 0 ? 8 : h, out = p == n - 1 ? 6 : h, width = parts[p].width;
+        float* bias = blob + parts[p].off;
+        float* rows = bias + parts[p].bias_floats;
+        for (int j = 0; j < out; ++j) {
+            bias[j] = b[p][j];
+            for (int k = 0; k < in; ++k) rows[k * width + j] = W[p][j * in + k];
+        }
+    }
+    return MPCDL_OK;
+}
+
+int mpcdl_pack_rnn(const mpcdl_model_desc* desc, const float* const* w_ih, const float* const* w_hh,
+                   const float* const* b_ih, const float* const* b_hh, const float* fc_w, const float* fc_b, float* blob) {
+    int rc = check_desc(desc);
+    if (rc) return rc;
+    if (desc->kind == MPCDL_MLP || !w_ih || !w_hh || !b_ih || !b_hh || !fc_w || !fc_b || !blob)
+        return fail(MPCDL_ERR_ARG, "mpcdl_pack_rnn: bad arguments");
+    PartDesc parts[MAX_PARTS];
+    int n;
+    uint32_t total = build_parts(*desc, parts, n);
+    std::fill(blob, blob + total, 0.f);
+    const int h = desc->hidden, G = gates(desc->kind), RJ = rnn_rj(h), n_jg = h / RJ;
+    for (int l = 0; l < desc->layers; ++l) {
+        const int in = l == 0 ? 8 : h;
+        const PartDesc& px = parts[2 * l];
+        const PartDesc& ph = parts[2 * l + 1];
+        float* bias = blob + px.off;                         // [jg][4][RJ]
+        float* xr = bias + px.bias_floats;                   // [k][jg][G][RJ]
+        float* hr = blob + ph.off;
+        for (int jg = 0; jg < n_jg; ++jg)
+            for (int r = 0; r < RJ; ++r) {
+                const int j = jg * RJ + r;
+                float* bb = bias + jg * 4 * RJ + r;
+                if (desc->kind == MPCDL_GRU) {
+                    bb[0 * RJ] = b_ih[l][j] + b_hh[l][j];
+                    bb[1 * RJ] = b_ih[l][h + j] + b_hh[l][h + j];
+                    bb[2 * RJ] = b_ih[l][2 * h + j];
+                    bb[3 * RJ] = b_hh[l][2 * h + j];
+                } else {
+                    for (int g = 0; g < 4; ++g) bb[g * RJ] = b_ih[l][g * h + j] + b_hh[l][g * h + j];
+                }
+                for (int g = 0; g < G; ++g) {
+                    for (int k = 0; k < in; ++k) xr[(size_t)k * G * h + (jg * G + g) * RJ + r] = w_ih[l][(size_t)(g * h + j) * in + k];
+                    for (int k = 0; k < h; ++k) hr[(size_t)k * G * h + (jg * G + g) * RJ + r] = w_hh[l][(size_t)(g * h + j) * h + k];
+                }
+            }
+    }
+    const PartDesc& pf = parts[2 * desc->layers];
+    float* bias = blob + pf.off;
+    float* rows = bias + pf.bias_floats;
+    for (int j = 0; j < 6; ++j) {
+        bias[j] = fc_b[j];
+        for (int k = 0; k < h; ++k) rows[k * 8 + j] = fc_w[j * h + k];
+    }
+    return MPCDL_OK;
+}
+
+size_t mpcdl_noise_blob_floats(int history, int size, int n_layers) {
+    size_t total = 0;
+    int K = 8 * history;
+    for (int i = 0; i <= n_layers; ++i) {
+        int out = i == n_layers ? 12 : size;
+        total += (size_t)(K + 1) * out;
+        K = size;
+    }
+    return total;
+}
+
+int mpcdl_pack_noise(int history, int size, int n_layers, const float* const* W, const float* const* b, float* blob) {
+    if (!W || !b || !blob || history < 1 || size < 1 || n_layers < 0) return fail(MPCDL_ERR_ARG, "mpcdl_pack_noise: bad arguments");
+    int K = 8 * history;
+    float* o = blob;
+    for (int i = 0; i <= n_layers; ++i) {
+        int out = i == n_layers ? 12 : size;
+        for (int k = 0; k < K; ++k)
+            for (int j = 0; j < out; ++j) o[k * out + j] = W[i][j * K + k];
+        for (int j = 0; j < out; ++j) o[K * out + j] = b[i][j];
+        o += (K + 1) * out;
+        K = size;
+    }
+    return MPCDL_OK;
+}
+
+int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
+    int rc = check_args(a);
+    if (rc) return rc;
+    if (!out) return fail(MPCDL_ERR_ARG, "plan is NULL");
+    int sms = g_num_sms ? g_num_sms : 148;                   // planning works without a device (B200 = 148 SMs)
+    Plan pl;
+    rc = make_plan(*a, pl, sms);
+    if (rc) return rc;
+    out->rt = pl.rt; out->rj = pl.rj; out->n_tg = pl.n_tg; out->tile_traj = pl.TN; out->threads = pl.nct + 32;
+    out->grid = pl.grid; out->smem_bytes = pl.smem_bytes; out->resident = pl.resident; out->nslots = pl.nslots;
+    out->slot_floats = pl.slot_floats; out->ntiles = pl.ntiles;
+    return MPCDL_OK;
+}
+
+int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
+    int rc = check_args(a);
+    if (rc) return rc;
+    rc = device_info();
+    if (rc) return rc;
+    if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    Plan pl;
+    rc = make_plan(*a, pl, g_num_sms);
+    if (rc) return rc;
+
+    RolloutParams p;
+    memset(&p, 0, sizeof(p));
+    const uint32_t total = build_parts(a->model, p.m.parts, p.m.nparts);
+    fill_model(p.m, *a, pl, total);
+    fill_noise(p.nz, *a);
+    p.io.norm = a->norm; p.io.init = a->init; p.io.U = a->U; p.io.states = a->states; p.io.costs = a->costs;
+    p.io.cost_ref = a->cost_ref;
+    for (int i = 0; i < 6; ++i) p.io.qw[i] = a->cost_qw[i];
+    for (int i = 0; i < 2; ++i) p.io.rw[i] = a->cost_rw[i];
+    p.io.eps = a->eps; p.io.seed = a->seed; p.io.traj_offset = a->traj_offset; p.io.carry = a->carry;
+    p.io.N = a->N; p.io.H = a->H; p.io.ntiles = pl.ntiles;
+
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    cudaError_t e;
+    if (a->model.kind == MPCDL_MLP) e = launch_mlp(p, pl.rt, pl.rj, pl.grid, pl.smem_bytes, st);
+    else e = launch_rnn(p, a->model.kind == MPCDL_GRU ? 0 : 1, pl.rt, pl.rj, pl.grid, pl.smem_bytes, st);
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "kernel launch failed: %s (rt=%d n_tg=%d smem=%d)", cudaGetErrorString(e), pl.rt, pl.n_tg, pl.smem_bytes);
+    return MPCDL_OK;
+}
+
+int mpcdl_ffma_peak(float* out_device, int iters, int grid, void* stream) {
+    if (!out_device || iters < 1 || grid < 1) return fail(MPCDL_ERR_ARG, "mpcdl_ffma_peak: bad arguments");
+    cudaError_t e = launch_ffma_peak(out_device, iters, grid, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "ffma_peak launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,30 @@
+// Kernel instantiation lists and launcher prototypes (host side of csrc/).
+#pragma once
+#include <cuda_runtime.h>
+#include "params.h"
+
+namespace mpcdl {
+
+// (hidden, RT, RJ): RT trajectories x RJ hidden units per thread.  RJ is fixed per (family,
+// hidden) because the packed blob interleaves gates in groups of RJ units.
+#define MPCDL_MLP_CONFIGS(X) \
+    X(16, 2, 2) X(16, 8, 2) X(32, 2, 4) X(32, 8, 4) X(64, 2, 4) X(64, 4, 4) X(64, 8, 4) \
+    X(128, 2, 4) X(128, 8, 4) X(256, 2, 8) X(256, 8, 8)
+#define MPCDL_RNN_CONFIGS(X) \
+    X(16, 2, 4) X(16, 4, 4) X(32, 2, 4) X(32, 4, 4) X(64, 2, 4) X(64, 4, 4) X(64, 8, 4) \
+    X(128, 2, 4) X(128, 4, 4) X(256, 2, 4) X(256, 4, 4)
+
+// CTA sizes are kept at 8 or 16 warps INCLUDING the producer warp: a 17th (or 9th) warp would put a
+// 5th (3rd) warp on one SM sub-partition and cut the per-thread register budget from 128 to 96.
+constexpr int MLP_MAX_THREADS = 512;                 // 480 consumers + producer warp, <= 128 regs
+__host__ __device__ constexpr int mlp_max_consumers() { return MLP_MAX_THREADS - 32; }
+__host__ __device__ constexpr int rnn_max_consumers(int rt, int rj) { return rt * rj * 4 > 64 ? 224 : 480; }
+
+inline int mlp_rj(int hid) { return hid <= 16 ? 2 : hid <= 128 ? 4 : 8; }
+inline int rnn_rj(int) { return 4; }
+
+cudaError_t launch_mlp(const RolloutParams& p, int rt, int rj, int grid, int smem_bytes, cudaStream_t st);
+cudaError_t launch_rnn(const RolloutParams& p, int cell, int rt, int rj, int grid, int smem_bytes, cudaStream_t st);
+cudaError_t launch_ffma_peak(float* out, int iters, int grid, cudaStream_t st);
+
+}  // namespace mpcdl

@@ -1,0 +1,91 @@
+// Kernel parameter blocks and the shared-memory carve-up (host + device).
+#pragma once
+#include <cstdint>
+#include "tile.cuh"
+
+namespace mpcdl {
+
+constexpr int MAX_LAYERS = 8;
+constexpr int MAX_WINDOW = 8;
+constexpr int MAX_PARTS = 2 * MAX_LAYERS + 2;
+constexpr int MAX_NOISE_LAYERS = 4;
+constexpr int SMEM_LIMIT = 232448;          // 227 KB opt-in maximum per CTA on sm_100
+
+struct NoiseParams {
+    const float* blob;       // gmem: per layer W^T[K][ldw] + bias[ldw]
+    int enabled, hist, size, nlayers, act;
+    int blob_floats;
+    int in_dim;              // 8*hist
+};
+
+struct IoParams {
+    const float* norm;       // f_mean[T*8] f_std[T*8] l_mean[6] l_std[6]   (T = max(window,1))
+    const float* init;       // [N,6] or [N,T,8]
+    const float* U;          // [N,H,2]
+    float* states;           // [N,H,6] or null
+    float* costs;            // [N] or null
+    const float* cost_ref;   // [H,6] or null
+    float qw[6], rw[2];
+    const float* eps;        // [N,H,6] or null (-> Philox(seed))
+    unsigned long long seed;
+    long long traj_offset;   // global index of trajectory 0 (shard invariance of the Philox stream)
+    float* carry;            // stateful RNN: [L][N][HID] h (+ [L][N][HID] c for LSTM), in/out
+    long long N;
+    int H;
+    int ntiles;
+};
+
+struct ModelParams {
+    const float* blob;
+    PartDesc parts[MAX_PARTS];
+    int nparts;
+    int hid, layers, window, stateful;
+    uint32_t data_off, data_floats;          // ring-streamed region of the blob
+    int n_tg, TN;                            // trajectory groups / trajectories per CTA tile
+    int n_cthreads;                          // consumer threads (multiple of 32); producer warp follows
+    int nslots, slot_floats, resident;
+};
+
+struct RolloutParams {
+    ModelParams m;
+    IoParams io;
+    NoiseParams nz;
+};
+
+// ------------------------------------------------------------------ shared-memory layout (float offsets)
+struct SmemLayout {
+    int bars;        // 2*nslots uint64
+    int ring;
+    int norm;        // 2*T*8 + 12
+    int xin;         // MLP: [8][TN]      RNN: xn [T][8][TN]
+    int xwin;        // RNN: raw window [T][8][TN]
+    int act0, act1;  // MLP: [HID][TN] x2  RNN: act0 = seq [T][HID][TN], act1 = hc [HID][TN] (stateful)
+    int ybuf;        // [8][TN]
+    int nblob, nin, nact0, nact1, nzb;   // noise net
+    int total;       // floats
+};
+
+__host__ __device__ inline int align_up(int x, int a) { return (x + a - 1) / a * a; }
+
+__host__ __device__ inline SmemLayout make_layout(const ModelParams& m, const NoiseParams& nz, bool rnn) {
+    SmemLayout L;
+    int o = 0;
+    const int T = m.window > 0 ? m.window : 1, TN = m.TN;
+    L.bars = o;   o += align_up(4 * m.nslots, 32);                       // 2*nslots u64 = 4*nslots floats
+    L.ring = o;   o += align_up(m.resident ? (int)m.data_floats : m.nslots * m.slot_floats, 32);
+    L.norm = o;   o += align_up(2 * T * 8 + 12, 32);
+    L.xin = o;    o += (rnn ? T : 1) * 8 * TN;
+    L.xwin = o;   o += rnn ? T * 8 * TN : 0;
+    L.act0 = o;   o += (rnn ? T : 1) * m.hid * TN;
+    L.act1 = o;   o += (rnn ? (m.stateful ? 1 : 0) : 1) * m.hid * TN;
+    L.ybuf = o;   o += 8 * TN;
+    L.nblob = o;  o += nz.enabled ? align_up(nz.blob_floats, 32) : 0;
+    L.nin = o;    o += nz.enabled ? nz.in_dim * TN : 0;
+    L.nact0 = o;  o += nz.enabled ? nz.size * TN : 0;
+    L.nact1 = o;  o += nz.enabled ? nz.size * TN : 0;
+    L.nzb = o;    o += nz.enabled ? 12 * TN : 0;
+    L.total = o;
+    return L;
+}
+
+}  // namespace mpcdl

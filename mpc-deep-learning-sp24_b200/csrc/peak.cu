@@ -1,0 +1,38 @@
+// FP32 FFMA peak micro-kernel: 64 independent register accumulators per thread, 8+8 operands,
+// no memory traffic in the loop.  bench.py times it to obtain the FP32 roofline denominator on
+// the box it runs on (MEASURED_PEAKS.json carries HBM and BF16 peaks only).
+#include "launch.h"
+
+namespace mpcdl {
+
+__global__ void __launch_bounds__(256) ffma_peak_kernel(float* out, int iters, float seed) {
+    float a[8], w[8], acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        a[i] = seed + threadIdx.x * 1e-6f + i * 1e-3f;
+        w[i] = seed * 0.5f + i * 1e-3f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += acc[i][j];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+cudaError_t launch_ffma_peak(float* out, int iters, int grid, cudaStream_t st) {
+    ffma_peak_kernel<<<grid, 256, 0, st>>>(out, iters, 1.0f);
+    return cudaGetLastError();
+}
+
+}  // namespace mpcdl

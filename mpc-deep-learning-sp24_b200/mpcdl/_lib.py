@@ -1,0 +1,100 @@
+"""ctypes binding of the C ABI in include/mpcdl.h (libmpcdl.so, built by csrc/Makefile).
+
+The library is the product: there is no Python / PyTorch / CPU fallback.  If the shared object is
+missing or fails to load, importing this module raises immediately.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmpcdl.so")
+
+MLP, GRU, LSTM = 0, 1, 2
+ACT = {"identity": 0, "relu": 1, "tanh": 2, "sigmoid": 3}
+
+
+class ModelDesc(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("hidden", C.c_int32), ("layers", C.c_int32), ("window", C.c_int32)]
+
+
+class RolloutArgs(C.Structure):
+    _fields_ = [
+        ("model", ModelDesc),
+        ("stateful", C.c_int32),
+        ("wblob", C.c_void_p),
+        ("norm", C.c_void_p),
+        ("init", C.c_void_p),
+        ("U", C.c_void_p),
+        ("states", C.c_void_p),
+        ("costs", C.c_void_p),
+        ("cost_ref", C.c_void_p),
+        ("cost_qw", C.c_float * 6),
+        ("cost_rw", C.c_float * 2),
+        ("noise_wblob", C.c_void_p),
+        ("noise_history", C.c_int32),
+        ("noise_size", C.c_int32),
+        ("noise_layers", C.c_int32),
+        ("noise_act", C.c_int32),
+        ("eps", C.c_void_p),
+        ("seed", C.c_uint64),
+        ("traj_offset", C.c_int64),
+        ("carry", C.c_void_p),
+        ("N", C.c_int64),
+        ("H", C.c_int32),
+        ("tune_rt", C.c_int32),
+        ("tune_ntg", C.c_int32),
+        ("tune_nslots", C.c_int32),
+        ("tune_kc", C.c_int32),
+    ]
+
+
+class Plan(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("rt", "rj", "n_tg", "tile_traj", "threads", "grid", "smem_bytes",
+                                         "resident", "nslots", "slot_floats", "ntiles")]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
+           "mpcdl_rollout", "mpcdl_rollout_plan", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version")
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with `make -C mpc-deep-learning-sp24_b200/csrc` "
+                          "(or __graft_entry__.build()); mpcdl has no fallback path")
+    lib = C.CDLL(LIB_PATH)
+    fpp = C.POINTER(C.POINTER(C.c_float))
+    fp = C.POINTER(C.c_float)
+    lib.mpcdl_blob_floats.restype = C.c_size_t
+    lib.mpcdl_blob_floats.argtypes = [C.POINTER(ModelDesc)]
+    lib.mpcdl_pack_mlp.restype = C.c_int
+    lib.mpcdl_pack_mlp.argtypes = [C.POINTER(ModelDesc), fpp, fpp, fp]
+    lib.mpcdl_pack_rnn.restype = C.c_int
+    lib.mpcdl_pack_rnn.argtypes = [C.POINTER(ModelDesc), fpp, fpp, fpp, fpp, fp, fp, fp]
+    lib.mpcdl_noise_blob_floats.restype = C.c_size_t
+    lib.mpcdl_noise_blob_floats.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.mpcdl_pack_noise.restype = C.c_int
+    lib.mpcdl_pack_noise.argtypes = [C.c_int, C.c_int, C.c_int, fpp, fpp, fp]
+    lib.mpcdl_rollout.restype = C.c_int
+    lib.mpcdl_rollout.argtypes = [C.POINTER(RolloutArgs), C.c_void_p]
+    lib.mpcdl_rollout_plan.restype = C.c_int
+    lib.mpcdl_rollout_plan.argtypes = [C.POINTER(RolloutArgs), C.POINTER(Plan)]
+    lib.mpcdl_ffma_peak.restype = C.c_int
+    lib.mpcdl_ffma_peak.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.mpcdl_last_error.restype = C.c_char_p
+    lib.mpcdl_version.restype = C.c_int
+    return lib
+
+
+lib = _load()
+
+
+def check(rc: int):
+    """Status -> exception, mirroring the reference's error behaviour (torch raises RuntimeError on
+    shape/device mismatch)."""
+    if rc != 0:
+        raise RuntimeError(f"mpcdl error {rc}: {lib.mpcdl_last_error().decode()}")

@@ -1,0 +1,272 @@
+"""Drop-in nn.Modules with the reference's constructors, attributes and state_dict keys whose
+forward / rollout run on the fused sm_100a kernels.
+
+    Basic_Model(inputs, hidden, output, layers, do_drop)        model_scripts/basic_model.py:43-61
+    GRU_Model / LSTM_Model(inputs, hidden, output, layers, state_f)   model_scripts/deep_models.py:44-92
+    FeedforwardNoiseModel(state_size, action_size, history, **params) model_scripts/noise_model.py:19-52
+
+The torch sub-modules (``layers``, ``gru``/``lstm``, ``full_c``, ``model``) are kept purely as parameter
+containers so ``load_state_dict(torch.load(file))`` of the shipped checkpoints works unchanged
+(eval_models.py:27-28, 54-55); no torch kernel runs in forward()/rollout().  Inputs must be CUDA
+tensors: there is no CPU path (the dispatcher raises for CPU tensors).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from . import _lib, ops, pack
+
+_ACT_MODULES = {"relu": nn.ReLU, "tanh": nn.Tanh, "leaky_relu": nn.LeakyReLU, "sigmoid": nn.Sigmoid,
+                "selu": nn.SELU, "softplus": nn.Softplus, "identity": nn.Identity}
+
+
+class _Packed:
+    """Device-resident packed blob, rebuilt when any parameter changes (version counter / device)."""
+
+    def __init__(self):
+        self._key, self._blob = None, None
+
+    def get(self, params, device, build):
+        key = (str(device),) + tuple((p.data_ptr(), p._version) for p in params)
+        if key != self._key:
+            self._blob = build().to(device)
+            self._key = key
+        return self._blob
+
+
+class _RolloutMixin:
+    KIND = None
+
+    def _desc(self):
+        raise NotImplementedError
+
+    def _blob(self, device):
+        raise NotImplementedError
+
+    def _norm(self, stats, device):
+        if stats is None:
+            key = ("identity", str(device))
+            if getattr(self, "_norm_key", None) != key:
+                self._norm_buf = pack.identity_norm(self._desc()[2]).to(device)
+                self._norm_key = key
+            return self._norm_buf
+        buf = pack.pack_norm(stats)
+        key = (buf.numpy().tobytes(), str(device))
+        if getattr(self, "_norm_key", None) != key:
+            self._norm_buf = buf.to(device)
+            self._norm_key = key
+        return self._norm_buf
+
+    @torch.no_grad()
+    def rollout(self, init, U, stats=None, *, noise=None, eps=None, seed=0, traj_offset=0, cost=None,
+                return_states=True, stateful=None, carry=None, tune=()):
+        """Closed-loop rollout of N trajectories over H steps in one kernel launch.
+
+        init  s0 [N,6] (MLP) or window [N,T,8] (GRU/LSTM), raw units; U [N,H,2] controls.
+        stats dict(f_mean,f_std,l_mean,l_std) from ``mpcdl.data.zscore_stats`` (None = identity).
+        noise FeedforwardNoiseModel (residual injection); eps [N,H,6] draws or None -> Philox(seed).
+        cost  (ref [H,6], qw [6], rw [2]) -> per-trajectory quadratic tracking cost.
+        Returns (states [N,H,6] or None, costs [N] or None[, carry if stateful])."""
+        hidden, layers, window = self._desc()
+        dev = U.device
+        stateful = bool(getattr(self, "state_f", False)) if stateful is None else bool(stateful)
+        stateful = stateful and self.KIND != _lib.MLP
+        if stateful and carry is None:
+            planes = layers * (2 if self.KIND == _lib.LSTM else 1)
+            carry = torch.zeros(planes, U.shape[0], hidden, device=dev)
+        nblob, ncfg = None, []
+        if noise is not None:
+            nblob, ncfg = noise.packed(dev), noise.cfg()
+        cref, cw = None, []
+        if cost is not None:
+            cref = cost[0].to(dev, torch.float32).contiguous()
+            cw = [float(v) for v in cost[1]] + [float(v) for v in cost[2]]
+        states, costs = ops.OPS[self.KIND](self._blob(dev), self._norm(stats, dev), init, U, hidden, layers, window,
+                                           stateful, carry if stateful else None, nblob, ncfg, eps, int(seed),
+                                           int(traj_offset), cref, cw, bool(return_states), cost is not None,
+                                           list(tune))
+        out = (states if return_states else None, costs if cost is not None else None)
+        return out + (carry,) if stateful else out
+
+
+class Basic_Model(_RolloutMixin, nn.Module):
+    KIND = _lib.MLP
+
+    def __init__(self, inputs, hidden, output, layers, do_drop):
+        super().__init__()
+        if inputs != 8 or output != 6:
+            raise RuntimeError("mpcdl: the fused kernels implement the BARC shape inputs=8, output=6")
+        self.layers = nn.ModuleList()
+        self.layers.append(nn.Linear(inputs, hidden))
+        for _ in range(layers):
+            self.layers.append(nn.Linear(hidden, hidden))
+            if do_drop:
+                self.layers.append(nn.Dropout(0.1))       # shifts the Linear indices (basic_model.py:53-54)
+        self.layers.append(nn.Linear(hidden, output))
+        self._hidden, self._nlayers = hidden, layers
+        self._packed = _Packed()
+
+    def _desc(self):
+        return self._hidden, self._nlayers, 0
+
+    def _blob(self, device):
+        return self._packed.get(list(self.parameters()), device,
+                                lambda: pack.pack_mlp(self.state_dict(), self._hidden, self._nlayers))
+
+    def forward(self, x):
+        """x [B,8] z-scored features -> [B,6] z-scored next state (one fused launch, H = 1).
+        Dropout (do_drop) is the identity in eval mode, which is the only mode the rollout path has."""
+        if self.training and any(isinstance(m, nn.Dropout) for m in self.layers):
+            raise RuntimeError("mpcdl: training-mode dropout is outside the fused inference path; call .eval()")
+        x = x.contiguous()
+        states, _ = self.rollout(x[:, :6].contiguous(), x[:, None, 6:8].contiguous(), None)
+        return states[:, 0, :]
+
+
+class _RNNBase(_RolloutMixin, nn.Module):
+    def __init__(self, inputs, hidden, output, layers, state_f):
+        super().__init__()
+        if inputs != 8 or output != 6:
+            raise RuntimeError("mpcdl: the fused kernels implement the BARC shape inputs=8, output=6")
+        self.hidden = hidden
+        self.layers = layers
+        self.state_f = state_f
+        self.h_state = None
+        self._packed = _Packed()
+        self._window = None
+
+    def _rnn(self):
+        raise NotImplementedError
+
+    def _desc(self):
+        return self.hidden, self.layers, self._window
+
+    def _blob(self, device):
+        return self._packed.get(list(self.parameters()), device,
+                                lambda: pack.pack_rnn(self.state_dict(), self.KIND, self.hidden, self.layers, self._window))
+
+    def rollout(self, init, U, stats=None, **kw):
+        self._window = int(init.shape[1])
+        return super().rollout(init, U, stats, **kw)
+
+    def forward(self, x):
+        """x [B,T,8] z-scored window -> [B,6].  state_f: h_state carries across calls and has a fixed
+        batch size (deep_models.py:61-65); it is allocated on x.device (the reference allocates on a
+        module-global device)."""
+        if not self.state_f or self.h_state is None:
+            self.init_hidden(x.size(0), x.device)
+        x = x.contiguous()
+        B = x.size(0)
+        carry = self._carry_in(B)
+        U = torch.zeros(B, 1, 2, device=x.device)
+        states, _, carry = self.rollout(x, U, None, stateful=True, carry=carry)
+        self._carry_out(carry)
+        return states[:, 0, :]
+
+
+class GRU_Model(_RNNBase):
+    KIND = _lib.GRU
+
+    def __init__(self, inputs, hidden, output, layers, state_f):
+        super().__init__(inputs, hidden, output, layers, state_f)
+        self.gru = nn.GRU(inputs, hidden, layers, batch_first=True)
+        self.full_c = nn.Linear(hidden, output)
+
+    def init_hidden(self, batch_s, device=None):
+        device = device if device is not None else self.full_c.weight.device
+        self.h_state = torch.zeros(self.layers, batch_s, self.hidden, device=device)
+
+    def _carry_in(self, B):
+        if self.h_state.shape[1] != B:
+            raise RuntimeError(f"Expected hidden size {(self.layers, B, self.hidden)}, got {list(self.h_state.shape)}")
+        return self.h_state.detach().clone().contiguous()
+
+    def _carry_out(self, carry):
+        self.h_state = carry
+
+
+class LSTM_Model(_RNNBase):
+    KIND = _lib.LSTM
+
+    def __init__(self, inputs, hidden, output, layers, state_f):
+        super().__init__(inputs, hidden, output, layers, state_f)
+        self.lstm = nn.LSTM(inputs, hidden, layers, batch_first=True)
+        self.full_c = nn.Linear(hidden, output)
+
+    def init_hidden(self, batch_s, device=None):
+        device = device if device is not None else self.full_c.weight.device
+        self.h_state = (torch.zeros(self.layers, batch_s, self.hidden, device=device),
+                        torch.zeros(self.layers, batch_s, self.hidden, device=device))
+
+    def _carry_in(self, B):
+        if self.h_state[0].shape[1] != B:
+            raise RuntimeError(f"Expected hidden[0] size {(self.layers, B, self.hidden)}, got {list(self.h_state[0].shape)}")
+        return torch.cat([self.h_state[0].detach(), self.h_state[1].detach()], dim=0).contiguous()
+
+    def _carry_out(self, carry):
+        self.h_state = (carry[:self.layers], carry[self.layers:])
+
+
+def build_mlp(input_size, output_size, n_layers, size, activation="tanh", output_activation="identity", **params):
+    """Same module indices as utils/pytorch_utils.py:19-57 (Linear at even positions)."""
+    seq, d = [], input_size
+    for _ in range(n_layers):
+        seq += [nn.Linear(d, size), _ACT_MODULES[activation]()]
+        d = size
+    seq += [nn.Linear(d, output_size), _ACT_MODULES[output_activation]()]
+    return nn.Sequential(*seq)
+
+
+class FeedforwardNoiseModel(nn.Module):
+    """Residual-noise net; inside ``rollout(noise=...)`` it is evaluated by the fused kernel with the
+    history buffering of CasadiDynamicCLBicycleNoise.get_prediction (noise_model.py:95-103)."""
+
+    def __init__(self, state_size, action_size, history, **params):
+        super().__init__()
+        if state_size != 6 or action_size != 2:
+            raise RuntimeError("mpcdl: the fused kernels implement state_size=6, action_size=2")
+        self.state_size, self.action_size, self.history = state_size, action_size, history
+        self.n_layers, self.size = params["n_layers"], params["size"]
+        self.activation = params.get("activation", "tanh")
+        if self.activation not in _lib.ACT or params.get("output_activation", "identity") != "identity":
+            raise RuntimeError("mpcdl: fused noise net supports hidden activation tanh/relu/sigmoid/identity and "
+                               "identity output activation")
+        self.model = build_mlp(input_size=(state_size + action_size) * history, output_size=state_size * 2, **params)
+        self._packed = _Packed()
+
+    def cfg(self):
+        return [self.history, self.size, self.n_layers, _lib.ACT[self.activation]]
+
+    def packed(self, device):
+        return self._packed.get(list(self.model.parameters()), device,
+                                lambda: pack.pack_noise(self.model.state_dict(), self.history, self.size, self.n_layers))
+
+    def export(self, path="../model_data", name="noise_model.pkl"):
+        import os
+        torch.save(self.model.state_dict(), os.path.join(path, name))
+
+    def load(self, path="../model_data", name="noise_model.pkl"):
+        import os
+        self.model.load_state_dict(torch.load(os.path.join(path, name), map_location="cpu"))
+
+
+def from_checkpoint_name(name, sd=None, device=None):
+    """File-name schema is the config (eval_models.py:19-25, 43-52):
+    Basic_{h}_{L}_{batch} | {GRU,LSTM}_{h}_{L}_{ft}_{batch}_{state_f}."""
+    p = name.replace(".pt", "").replace(".npz", "").split("_")
+    kind, hidden, layers = p[0], int(p[1]), int(p[2])
+    if kind == "Basic":
+        m, meta = Basic_Model(8, hidden, 6, layers, False), dict(kind="mlp", window=0, state_f=False)
+    else:
+        state_f = p[-1] == "True"
+        m = (GRU_Model if kind == "GRU" else LSTM_Model)(8, hidden, 6, layers, state_f)
+        m._window = int(p[3])
+        meta = dict(kind=kind.lower(), window=int(p[3]), state_f=state_f)
+    meta.update(hidden=hidden, layers=layers)
+    if sd is not None:
+        m.load_state_dict({k: torch.as_tensor(v) for k, v in sd.items()})
+    m.eval()
+    if device is not None:
+        m.to(device)
+    return m, meta

@@ -1,0 +1,158 @@
+"""torch.ops.mpcdl.* -- the operator boundary of the fused rollout path.
+
+``torch.ops.mpcdl.rollout_{mlp,gru,lstm}`` are registered for the CUDA dispatch key only and call
+``mpcdl_rollout`` (include/mpcdl.h) through ctypes with raw device pointers on the current CUDA
+stream.  CPU tensors therefore fail in the dispatcher ("no kernel for CPU"): there is no fallback.
+
+Reference surface replaced: ``Basic_Model.forward`` model_scripts/basic_model.py:58-61,
+``GRU_Model.forward`` / ``LSTM_Model.forward`` model_scripts/deep_models.py:60-66 / 85-92,
+``FeedforwardNoiseModel.forward`` model_scripts/noise_model.py:34-40 and the feedback loop of
+``run_dynamics_model`` scripts/test_model.py:67-87, batched over N trajectories and fused over H steps.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Tuple
+
+import torch
+
+from . import _lib
+
+_SCHEMA = ("(Tensor wblob, Tensor norm, Tensor init, Tensor U, int hidden, int layers, int window, bool stateful, "
+           "Tensor(a!)? carry, Tensor? noise_wblob, int[] noise_cfg, Tensor? eps, int seed, int traj_offset, "
+           "Tensor? cost_ref, float[] cost_w, bool return_states, bool return_costs, int[] tune) -> (Tensor, Tensor)")
+
+_libdef = torch.library.Library("mpcdl", "DEF")
+for _name in ("rollout_mlp", "rollout_gru", "rollout_lstm"):
+    _libdef.define(_name + _SCHEMA)
+
+
+def _f32c(t: Optional[torch.Tensor], name: str, dev=None) -> int:
+    if t is None:
+        return 0
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"mpcdl: {name} must be float32, got {t.dtype}")
+    if not t.is_cuda:
+        raise RuntimeError(f"mpcdl: {name} must be a CUDA tensor (no CPU fallback), got {t.device}")
+    if dev is not None and t.device != dev:
+        raise RuntimeError(f"mpcdl: {name} is on {t.device}, expected {dev}")
+    if not t.is_contiguous():
+        raise RuntimeError(f"mpcdl: {name} must be contiguous")
+    return t.data_ptr()
+
+
+def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob, noise_cfg,
+                  eps, seed, traj_offset, cost_ref, cost_w, return_states, return_costs, tune):
+    dev = U.device
+    if U.dim() != 3 or U.shape[2] != 2:
+        raise RuntimeError(f"mpcdl: U must be [N,H,2], got {tuple(U.shape)}")
+    N, H = int(U.shape[0]), int(U.shape[1])
+    T = window if kind != _lib.MLP else 0
+    want = (N, 6) if kind == _lib.MLP else (N, T, 8)
+    if tuple(init.shape) != want:
+        raise RuntimeError(f"mpcdl: init must be {want}, got {tuple(init.shape)}")
+    nt = max(T, 1)
+    if norm.numel() != 2 * nt * 8 + 12:
+        raise RuntimeError(f"mpcdl: norm must hold {2 * nt * 8 + 12} floats (f_mean,f_std [{nt},8]; l_mean,l_std [6])")
+    a = _lib.RolloutArgs()
+    a.model = _lib.ModelDesc(kind, hidden, layers, T)
+    need = _lib.lib.mpcdl_blob_floats(C.byref(a.model))
+    if need == 0:
+        _lib.check(-2)
+    if wblob.numel() != need:
+        raise RuntimeError(f"mpcdl: wblob has {wblob.numel()} floats, model needs {need}")
+    a.stateful = int(bool(stateful) and kind != _lib.MLP)
+    a.wblob = _f32c(wblob, "wblob", dev)
+    a.norm = _f32c(norm, "norm", dev)
+    a.init = _f32c(init, "init", dev)
+    a.U = _f32c(U, "U", dev)
+    states = torch.empty((N, H, 6), device=dev, dtype=torch.float32) if return_states else torch.empty(0, device=dev)
+    costs = torch.empty((N,), device=dev, dtype=torch.float32) if return_costs else torch.empty(0, device=dev)
+    a.states = states.data_ptr() if return_states else 0
+    a.costs = costs.data_ptr() if return_costs else 0
+    if cost_ref is not None:
+        if tuple(cost_ref.shape) != (H, 6) or len(cost_w) != 8:
+            raise RuntimeError("mpcdl: cost_ref must be [H,6] and cost_w = qw[6] + rw[2]")
+        a.cost_ref = _f32c(cost_ref, "cost_ref", dev)
+    if len(cost_w) == 8:
+        a.cost_qw = (C.c_float * 6)(*cost_w[:6])
+        a.cost_rw = (C.c_float * 2)(*cost_w[6:])
+    if noise_wblob is not None:
+        hist, size, nl, act = noise_cfg
+        if noise_wblob.numel() != _lib.lib.mpcdl_noise_blob_floats(hist, size, nl):
+            raise RuntimeError("mpcdl: noise_wblob size does not match noise_cfg")
+        a.noise_wblob = _f32c(noise_wblob, "noise_wblob", dev)
+        a.noise_history, a.noise_size, a.noise_layers, a.noise_act = hist, size, nl, act
+        if eps is not None:
+            if tuple(eps.shape) != (N, H, 6):
+                raise RuntimeError(f"mpcdl: eps must be [N,H,6], got {tuple(eps.shape)}")
+            a.eps = _f32c(eps, "eps", dev)
+    a.seed = seed & 0xFFFFFFFFFFFFFFFF
+    a.traj_offset = traj_offset
+    if a.stateful:
+        planes = layers * (2 if kind == _lib.LSTM else 1)
+        if carry is None or tuple(carry.shape) != (planes, N, hidden):
+            raise RuntimeError(f"mpcdl: stateful rollout needs carry [{planes},{N},{hidden}]")
+        a.carry = _f32c(carry, "carry", dev)
+    a.N, a.H = N, H
+    if len(tune) == 4:
+        a.tune_rt, a.tune_ntg, a.tune_nslots, a.tune_kc = tune
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(_lib.lib.mpcdl_rollout(C.byref(a), C.c_void_p(stream)))
+    return states, costs
+
+
+def _make(kind):
+    def impl(wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob, noise_cfg, eps, seed,
+             traj_offset, cost_ref, cost_w, return_states, return_costs, tune):
+        return _rollout_impl(kind, wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob,
+                             noise_cfg, eps, seed, traj_offset, cost_ref, cost_w, return_states, return_costs, tune)
+    return impl
+
+
+_libimpl = torch.library.Library("mpcdl", "IMPL", "CUDA")
+_libimpl.impl("rollout_mlp", _make(_lib.MLP))
+_libimpl.impl("rollout_gru", _make(_lib.GRU))
+_libimpl.impl("rollout_lstm", _make(_lib.LSTM))
+
+OPS = {_lib.MLP: torch.ops.mpcdl.rollout_mlp, _lib.GRU: torch.ops.mpcdl.rollout_gru, _lib.LSTM: torch.ops.mpcdl.rollout_lstm}
+
+
+def plan(kind, hidden, layers, window, N, H, stateful=False, noise_cfg=None, tune=()):
+    """Launch plan the library would use (works without a GPU): tile size, grid, smem, ring mode."""
+    a = _lib.RolloutArgs()
+    a.model = _lib.ModelDesc(kind, hidden, layers, window if kind != _lib.MLP else 0)
+    a.stateful = int(stateful)
+    for f in ("wblob", "norm", "init", "U", "states"):
+        setattr(a, f, 16)           # never dereferenced by the planner
+    if stateful:
+        a.carry = 16
+    if noise_cfg is not None:
+        a.noise_wblob = 16
+        a.noise_history, a.noise_size, a.noise_layers, a.noise_act = noise_cfg
+    a.N, a.H = N, H
+    if len(tune) == 4:
+        a.tune_rt, a.tune_ntg, a.tune_nslots, a.tune_kc = tune
+    p = _lib.Plan()
+    _lib.check(_lib.lib.mpcdl_rollout_plan(C.byref(a), C.byref(p)))
+    return p.as_dict()
+
+
+def ffma_peak_tflops(device=None, iters=20000, reps=5) -> float:
+    """Measured FP32 FFMA peak of the current GPU (TFLOP/s), CUDA events, best of `reps`."""
+    dev = torch.device(device or "cuda")
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    grid = sms * 2
+    out = torch.empty(grid * 256, device=dev, dtype=torch.float32)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    best = float("inf")
+    for r in range(reps + 1):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(_lib.lib.mpcdl_ffma_peak(C.c_void_p(out.data_ptr()), iters, grid, C.c_void_p(st)))
+        e1.record()
+        e1.synchronize()
+        if r:
+            best = min(best, e0.elapsed_time(e1))
+    return 2.0 * grid * 256 * iters * 64 / (best * 1e-3) / 1e12

@@ -1,0 +1,56 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "mpc-deep-learning-sp24_b200"))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+FWD = ["Basic_16_1_32", "Basic_16_2_16", "Basic_16_2_32", "Basic_16_4_32",
+       "Basic_64_1_32", "Basic_64_2_32", "Basic_64_2_64", "Basic_64_4_32"]
+RNN = [f"{k}_64_4_4_{b}_{s}" for k in ("GRU", "LSTM") for b in (16, 64) for s in ("False", "True")]
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (B200, sm_100a)")
+
+
+def pytest_collection_modifyitems(config, items):
+    if torch.cuda.is_available():
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)
+
+
+def load_ckpt(name):
+    return {k: torch.from_numpy(v) for k, v in np.load(os.path.join(GOLD, "checkpoints", f"{name}.npz")).items()}
+
+
+@pytest.fixture(scope="session")
+def gold_stats():
+    z = np.load(os.path.join(GOLD, "stats.npz"))
+    mlp = {k[4:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("mlp_")}
+    rnn = {k[5:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("rnn4_")}
+    return mlp, rnn
+
+
+@pytest.fixture(scope="session")
+def gold_onestep():
+    return np.load(os.path.join(GOLD, "onestep.npz"))
+
+
+@pytest.fixture(scope="session")
+def gold_rollouts():
+    return np.load(os.path.join(GOLD, "rollouts.npz"))
+
+
+@pytest.fixture(scope="session")
+def bags():
+    from mpcdl import synth
+    return synth.load_bags("mpc_data_clean")

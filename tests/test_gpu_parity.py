@@ -1,0 +1,133 @@
+"""GPU parity tests: the CUDA path (through torch.ops.mpcdl -> C ABI) against the golden vectors made
+from the reference modules (oracle/pin_reference.py) and against the live oracle.
+
+Tolerances (DESIGN.md "Tolerances"):
+  T1 one-step      max|y_kernel - y_ref| / max|y_ref| <= 1e-5       (teacher forced, every row/window)
+  T2 full horizon  vs an FP64 run of the same module: kernel error quantiles (p50,p90,p99) <= 2x the
+                   quantiles of torch-FP32's own error + 1e-6, and kernel-vs-torch-FP32 p90 <= 1e-5
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import FWD, RNN, load_ckpt
+
+pytestmark = pytest.mark.gpu
+T1 = 1e-5
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _t1(y, ref):
+    ref = torch.as_tensor(ref)
+    return ((y.cpu() - ref).abs().max() / ref.abs().max()).item()
+
+
+def _model(name):
+    import mpcdl
+    m, meta = mpcdl.from_checkpoint_name(name, load_ckpt(name), _dev())
+    return m, meta
+
+
+@pytest.mark.parametrize("name", FWD)
+def test_t1_onestep_mlp(name, bags, gold_onestep):
+    import mpcdl
+    ds = mpcdl.RobotData(bags)
+    m, _ = _model(name)
+    y = m(ds.featrs.to(_dev()))
+    assert y.shape == (4550, 6)
+    assert _t1(y, gold_onestep[name]) <= T1
+
+
+@pytest.mark.parametrize("name", RNN)
+def test_t1_onestep_rnn(name, bags, gold_onestep):
+    import mpcdl
+    ds = mpcdl.RobotData(bags, 4)
+    m, meta = _model(name)
+    x = ds.featrs.to(_dev())
+    y = m(x)
+    assert y.shape == (4546, 6)
+    assert _t1(y, gold_onestep[name]) <= T1
+    if meta["state_f"]:      # second call carries h_state (deep_models.py:61-65)
+        y2 = m(x)
+        assert _t1(y2, gold_onestep[name + "_second"]) <= T1
+        with pytest.raises(RuntimeError):          # fixed batch size of the carried state
+            m(x[:7])
+
+
+def _quantiles(e):
+    e = e.flatten().double()
+    return [torch.quantile(e, q).item() for q in (0.5, 0.9, 0.99)]
+
+
+@pytest.mark.parametrize("name", FWD + RNN)
+def test_golden_rollout(name, gold_rollouts, gold_stats):
+    """N=64, H=24 closed loop produced by the REFERENCE modules in a python loop."""
+    from oracle import rollout_ref as R
+    m, meta = _model(name)
+    mlp = meta["kind"] == "mlp"
+    st = gold_stats[0] if mlp else gold_stats[1]
+    init = torch.from_numpy(gold_rollouts["s0" if mlp else "win0"]).to(_dev())
+    U = torch.from_numpy(gold_rollouts["U" if mlp else "Uw"]).to(_dev())
+    out = m.rollout(init, U, st)
+    ref = torch.from_numpy(gold_rollouts[name])
+    err = R.rel_err(out[0].cpu(), ref)
+    assert err[:, 0].max().item() <= T1                       # first step is a one-step prediction
+    q = _quantiles(err)
+    assert q[1] <= 1e-5, q                                    # p90 over the 24-step horizon
+    assert err.max().item() <= 1e-3, err.max().item()
+
+
+def test_golden_noise_cost(gold_rollouts, gold_stats):
+    import mpcdl
+    from oracle import rollout_ref as R
+    noise = mpcdl.FeedforwardNoiseModel(6, 2, 3, n_layers=2, size=32, activation="tanh", output_activation="identity")
+    noise.model.load_state_dict(load_ckpt("noise_seed0_h3_s32_l2"))
+    noise.to(_dev())
+    g = gold_rollouts
+    cost = tuple(torch.from_numpy(g[k]) for k in ("cost_ref", "cost_qw", "cost_rw"))
+    eps = torch.from_numpy(g["eps"]).to(_dev())
+    for name, init_k, u_k, st in (("Basic_64_4_32", "s0", "U", gold_stats[0]), ("GRU_64_4_4_16_False", "win0", "Uw", gold_stats[1])):
+        m, _ = _model(name)
+        states, costs = m.rollout(torch.from_numpy(g[init_k]).to(_dev()), torch.from_numpy(g[u_k]).to(_dev()), st,
+                                  noise=noise, eps=eps, cost=cost)
+        err = R.rel_err(states.cpu(), torch.from_numpy(g[name + "_noise"]))
+        assert err[:, 0].max().item() <= T1
+        assert _quantiles(err)[1] <= 1e-5
+        cref = torch.from_numpy(g[name + "_noise_cost"])
+        assert ((costs.cpu() - cref).abs() / cref.abs()).max().item() <= 1e-4
+    # batch-1 golden made through the reference's own DynamicsNN.get_prediction wrapper (noise_model.py:114-125)
+    m, _ = _model("Basic_64_4_32")
+    states, _ = m.rollout(torch.from_numpy(g["s0"][:1]).to(_dev()), torch.from_numpy(g["U"][:1]).to(_dev()), gold_stats[0],
+                          noise=noise, eps=torch.from_numpy(g["eps_b1"]).to(_dev()))
+    err = R.rel_err(states.cpu(), torch.from_numpy(g["Basic_64_4_32_noise_b1"]))
+    assert err.max().item() <= 1e-4
+
+
+@pytest.mark.parametrize("name,N,H", [("Basic_64_4_32", 4096, 50), ("Basic_16_1_32", 1000, 50),
+                                      ("GRU_64_4_4_16_False", 300, 50), ("GRU_64_4_4_64_True", 300, 50),
+                                      ("LSTM_64_4_4_16_False", 300, 50), ("LSTM_64_4_4_64_True", 300, 50)])
+def test_t2_full_horizon(name, N, H, gold_stats):
+    """T2: error quantiles against the FP64 oracle are no worse than 2x torch-FP32's own."""
+    from mpcdl import synth
+    from oracle import rollout_ref as R
+    m, meta = _model(name)
+    mlp = meta["kind"] == "mlp"
+    st = gold_stats[0] if mlp else gold_stats[1]
+    init, U = synth.make_inputs(synth.load_rows(), N, H, window=meta["window"], seed=3)
+    ref_m, _ = R.build_from_name(name, load_ckpt(name))
+    ref64 = R.as_double(ref_m)
+    st64 = {k: v.double() for k, v in st.items()}
+    if mlp:
+        y32 = R.rollout_mlp(ref_m, st, init, U)[0]
+        y64 = R.rollout_mlp(ref64, st64, init.double(), U.double())[0]
+    else:
+        y32 = R.rollout_rnn(ref_m, st, init, U, stateful=meta["state_f"])[0]
+        y64 = R.rollout_rnn(ref64, st64, init.double(), U.double(), stateful=meta["state_f"])[0]
+    yk = m.rollout(init.to(_dev()), U.to(_dev()), st)[0].cpu()
+    qk, qt = _quantiles(R.rel_err(yk, y64)), _quantiles(R.rel_err(y32, y64))
+    for a, b in zip(qk, qt):
+        assert a <= 2 * b + 1e-6, (qk, qt)
+    assert _quantiles(R.rel_err(yk, y32))[1] <= 1e-5
