@@ -1,0 +1,185 @@
+"""CPU: host-side logic of the drop-in boundary -- dataset/statistics mirror, weight packers,
+checkpoint-name schema, state_dict compatibility, error behaviour without a device."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import FWD, RNN, load_ckpt
+from oracle import rollout_ref as R
+
+
+def test_robotdata_matches_oracle_bitwise(bags, gold_stats):
+    import mpcdl
+    ds = mpcdl.RobotData(bags)
+    f, l = R.mlp_dataset(bags)
+    fn, ln = R.apply_zscore(f, l, R.zscore_stats(f, l))
+    assert torch.equal(ds.featrs, fn) and torch.equal(ds.labels, ln) and len(ds) == 4550
+    for k in ("f_mean", "f_std", "l_mean", "l_std"):
+        assert torch.equal(ds.stats[k], gold_stats[0][k])
+    dr = mpcdl.RobotData(bags, 4)
+    f, l = R.rnn_dataset(bags, 4)
+    fn, ln = R.apply_zscore(f, l, R.zscore_stats(f, l))
+    assert torch.equal(dr.featrs, fn) and torch.equal(dr.labels, ln) and len(dr) == 4546
+    assert tuple(dr.stats["f_mean"].shape) == (4, 8)
+    x, y = dr[3]
+    assert x.shape == (4, 8) and y.shape == (6,)
+
+
+def test_robotdata_ragged_and_short_bags():
+    import mpcdl
+    rows = mpcdl.synth.load_rows()[:40].tolist()
+    bags = [rows[:10], rows[10:13], rows[13:14], rows[14:40]]       # a 1-row bag contributes nothing
+    ds = mpcdl.RobotData(bags)
+    f, l = R.mlp_dataset(bags)
+    assert len(ds) == len(f) == 9 + 2 + 0 + 25
+    dr = mpcdl.RobotData(bags, 4)
+    f, l = R.rnn_dataset(bags, 4)                                   # bags shorter than size+2 rows are skipped
+    assert len(dr) == len(f) == 5 + 0 + 0 + 21
+    fn, ln = R.apply_zscore(f, l, R.zscore_stats(f, l))
+    assert torch.equal(dr.featrs, fn) and torch.equal(dr.labels, ln)
+
+
+def _mlp_from_blob(blob, hidden, layers, x):
+    """numpy interpreter of the packed MLP blob: per layer [bias(width)] [k][width]."""
+    o, widths = 0, [(8, hidden)] + [(hidden, hidden)] * layers + [(hidden, 8)]
+    for i, (k, w) in enumerate(widths):
+        b = blob[o:o + w]; o += w
+        W = blob[o:o + k * w].reshape(k, w); o += k * w
+        x = x @ W + b
+        if i < len(widths) - 1:
+            x = np.maximum(x, 0)
+    assert o == blob.size
+    return x[:, :6]
+
+
+@pytest.mark.parametrize("name", FWD)
+def test_pack_mlp_roundtrip(name, bags):
+    from mpcdl import pack
+    sd = load_ckpt(name)
+    h, L = int(name.split("_")[1]), int(name.split("_")[2])
+    blob = pack.pack_mlp(sd, h, L).numpy().astype(np.float64)
+    m, _ = R.build_from_name(name, sd)
+    x = torch.randn(64, 8, generator=torch.Generator().manual_seed(0))
+    with torch.no_grad():
+        ref = m(x).numpy()
+    got = _mlp_from_blob(blob, h, L, x.numpy().astype(np.float64))
+    assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-5
+
+
+def test_pack_mlp_skips_dropout_entries():
+    import mpcdl
+    from mpcdl import pack
+    torch.manual_seed(0)
+    m = mpcdl.Basic_Model(8, 16, 6, 2, True)                       # Linear indices 0,1,3,5 (basic_model.py:53-54)
+    keys = sorted({int(k.split(".")[1]) for k in m.state_dict()})
+    assert keys == [0, 1, 3, 5]
+    blob = pack.pack_mlp(m.state_dict(), 16, 2).numpy().astype(np.float64)
+    ref = R.RefBasic(8, 16, 6, 2, True)
+    ref.load_state_dict(m.state_dict())
+    x = torch.randn(32, 8)
+    with torch.no_grad():
+        want = ref.eval()(x).numpy()
+    got = _mlp_from_blob(blob, 16, 2, x.numpy().astype(np.float64))
+    assert np.abs(got - want).max() < 1e-5
+
+
+def _sig(x):
+    return 1 / (1 + np.exp(-x))
+
+
+def _rnn_from_blob(blob, kind, h, L, X, RJ=4):
+    """numpy interpreter of the packed GRU/LSTM blob (gate-interleaved columns [jg][G][RJ],
+    bias block [jg][4][RJ]); X [B,T,8] -> [B,6], zero initial state."""
+    G = 3 if kind == "GRU" else 4
+    njg = h // RJ
+    o, seq = 0, [X[:, t] for t in range(X.shape[1])]
+
+    def cols(M):      # [..., jg, G, RJ] -> per gate [..., h]
+        M = M.reshape(M.shape[:-1] + (njg, G, RJ))
+        return [M[..., g, :].reshape(M.shape[:-3] + (h,)) for g in range(G)]
+
+    for l in range(L):
+        k = 8 if l == 0 else h
+        bias = blob[o:o + 4 * h].reshape(njg, 4, RJ); o += 4 * h
+        b = [bias[:, g, :].reshape(h) for g in range(4)]
+        Wx = cols(blob[o:o + k * G * h].reshape(k, G * h)); o += k * G * h
+        Wh = cols(blob[o:o + h * G * h].reshape(h, G * h)); o += h * G * h
+        hs, c, out = np.zeros((X.shape[0], h)), np.zeros((X.shape[0], h)), []
+        for x in seq:
+            if kind == "GRU":      # bias blocks: r (ih+hh), z (ih+hh), n_x (ih), n_h (hh)
+                r = _sig(x @ Wx[0] + hs @ Wh[0] + b[0]); z = _sig(x @ Wx[1] + hs @ Wh[1] + b[1])
+                n = np.tanh(x @ Wx[2] + b[2] + r * (hs @ Wh[2] + b[3]))
+                hs = (1 - z) * n + z * hs
+            else:
+                i, f, g, og = (x @ Wx[q] + hs @ Wh[q] + b[q] for q in range(4))
+                c = _sig(f) * c + _sig(i) * np.tanh(g)
+                hs = _sig(og) * np.tanh(c)
+            out.append(hs)
+        seq = out
+    bfc = blob[o:o + 8]; o += 8
+    Wfc = blob[o:o + h * 8].reshape(h, 8); o += h * 8
+    assert o == blob.size
+    return (seq[-1] @ Wfc + bfc)[:, :6]
+
+
+@pytest.mark.parametrize("name", [RNN[0], RNN[4]])
+def test_pack_rnn_roundtrip(name, bags):
+    from mpcdl import _lib, pack
+    sd = load_ckpt(name)
+    kind = name.split("_")[0]
+    blob = pack.pack_rnn(sd, _lib.GRU if kind == "GRU" else _lib.LSTM, 64, 4, 4).numpy().astype(np.float64)
+    m, _ = R.build_from_name(name, sd)
+    X = torch.randn(32, 4, 8, generator=torch.Generator().manual_seed(1))
+    with torch.no_grad():
+        ref = m(X, m.zero_state(32))[0].numpy()
+    got = _rnn_from_blob(blob, kind, 64, 4, X.numpy().astype(np.float64))
+    assert np.abs(got - ref).max() / np.abs(ref).max() < 1e-5
+
+
+def test_pack_noise_layout():
+    from mpcdl import pack
+    sd = load_ckpt("noise_seed0_h3_s32_l2")
+    blob = pack.pack_noise(sd, 3, 32, 2).numpy()
+    assert blob.size == (24 + 1) * 32 + (32 + 1) * 32 + (32 + 1) * 12
+    W0 = blob[:24 * 32].reshape(24, 32)
+    assert np.array_equal(W0, sd["0.weight"].numpy().T) and np.array_equal(blob[24 * 32:25 * 32], sd["0.bias"].numpy())
+
+
+@pytest.mark.parametrize("name", [FWD[-1], RNN[0], RNN[5]])
+def test_dropin_modules_load_reference_state_dicts(name):
+    import mpcdl
+    sd = load_ckpt(name)
+    m, meta = mpcdl.from_checkpoint_name(name + ".pt", sd)
+    ref, rmeta = R.build_from_name(name, sd)
+    assert list(m.state_dict().keys()) == list(ref.state_dict().keys()) == list(sd.keys())
+    assert meta["hidden"] == 64 and meta["layers"] == 4
+    if meta["kind"] != "mlp":
+        assert (m.hidden, m.layers, m.state_f) == (64, 4, name.endswith("True"))
+        m.init_hidden(5)
+        hs = m.h_state if meta["kind"] == "gru" else m.h_state[0]
+        assert tuple(hs.shape) == (4, 5, 64)
+
+
+def test_no_cpu_fallback():
+    """CPU tensors must fail loudly: the op is registered for the CUDA dispatch key only."""
+    import mpcdl
+    m, _ = mpcdl.from_checkpoint_name("Basic_16_1_32", load_ckpt("Basic_16_1_32"))
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        m(torch.zeros(4, 8))
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        m.rollout(torch.zeros(4, 6), torch.zeros(4, 3, 2))
+    with pytest.raises(RuntimeError):
+        mpcdl.Basic_Model(7, 16, 6, 1, False)
+    with pytest.raises(RuntimeError):
+        mpcdl.pack.pack_mlp(load_ckpt("Basic_16_1_32"), 64, 1)
+
+
+def test_synth_inputs_are_deterministic_and_bounded():
+    from mpcdl import synth
+    rows = synth.load_rows()
+    a = synth.make_inputs(rows, 100, 30, window=4, seed=9)
+    b = synth.make_inputs(rows, 100, 30, window=4, seed=9)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    assert a[0].shape == (100, 4, 8) and a[1].shape == (100, 30, 2)
+    u = torch.as_tensor(rows[:, 6:8], dtype=torch.float32)
+    assert (a[1] >= u.amin(0)).all() and (a[1] <= u.amax(0)).all()

@@ -1,0 +1,32 @@
+#!/bin/bash
+# One GPU-box visit: parity tests, smoke, bench, timing sweep, ncu launch list + full capture.
+# usage: gpurun --timeout 1500 -- 'bash tools/gpu_round.sh [tests] [bench] [sweep] [ncu]'
+set -u
+mkdir -p gpurun_out
+what="${*:-tests bench sweep ncu}"
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw,memory.total --format=csv > gpurun_out/gpu.csv 2>&1
+if [[ $what == *tests* ]]; then
+  timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/pytest_gpu.log
+  timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke exit $?" | tee -a gpurun_out/smoke.log
+fi
+if [[ $what == *bench* ]]; then
+  timeout 600 python bench.py > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err; echo "bench c2 exit $?"
+  timeout 600 python bench.py --impl reference --steps 10 --warmup 2 > gpurun_out/bench_c2_ref.json 2>> gpurun_out/bench_c2.err
+  for wl in c5 c3 c3l c5g c4; do
+    timeout 600 python bench.py --workload $wl --steps 5 --warmup 3 > gpurun_out/bench_$wl.json 2> gpurun_out/bench_$wl.err; echo "bench $wl exit $?"
+  done
+fi
+if [[ $what == *sweep* ]]; then
+  timeout 600 python tools/gpu_quick.py > gpurun_out/sweep.log 2>&1; echo "sweep exit $?"
+fi
+if [[ $what == *ncu* ]]; then
+  timeout 300 python bench.py --steps 3 --warmup 3 --skip-cpu > gpurun_out/plain_c2.log 2>&1 &&
+  timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_c2.csv \
+      python bench.py --steps 3 --warmup 3 --skip-cpu > gpurun_out/ncu_launches_c2.log 2>&1
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:rollout_mlp -s 3 -c 2 -f -o gpurun_out/prof_c2 \
+      python bench.py --steps 3 --warmup 3 --skip-cpu > gpurun_out/ncu_full_c2.log 2>&1
+  timeout 300 python bench.py --workload c3 --steps 2 --warmup 3 --skip-cpu > gpurun_out/plain_c3.log 2>&1 &&
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:rollout_rnn -s 1 -c 1 -f -o gpurun_out/prof_c3 \
+      python bench.py --workload c3 --steps 2 --warmup 3 --skip-cpu > gpurun_out/ncu_full_c3.log 2>&1
+fi
+ls -la gpurun_out
