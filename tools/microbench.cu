@@ -159,8 +159,6 @@ int main() {
     run_lds(4, 48, 256, "8 groups x16B (stride 48B)");
     run_lds(2, 48, 256, "16 groups x16B (stride 48B)");
     run_lds(1, 16, 256, "32 distinct x16B (512B)");
-    run_lds(32, 0, 512, "all lanes same 16B");
-    run_lds(1, 16, 512, "32 distinct x16B (512B)");
     run_tile<8, 8, 4, false>(256, 1); run_tile<8, 8, 4, true>(256, 1);
     run_tile<8, 8, 4, true>(128, 1);  run_tile<8, 8, 4, true>(128, 2);
     run_tile<8, 8, 2, true>(256, 1);  run_tile<8, 8, 8, true>(256, 1);
@@ -169,7 +167,8 @@ int main() {
     run_tile<4, 8, 8, true>(256, 1);  run_tile<4, 8, 8, true>(256, 2);
     run_tile<4, 12, 8, true>(256, 1); run_tile<4, 16, 8, true>(256, 1);
     run_tile<4, 4, 8, true>(256, 2);  run_tile<4, 4, 8, false>(256, 2);
-    run_tile<4, 4, 8, true>(128, 1);  run_tile<4, 4, 8, true>(128, 4);
+    run_tile<4, 4, 8, true>(128, 1);  run_tile<4, 4, 8, false>(128, 1); run_tile<4, 4, 8, true>(128, 4);
+    run_tile<4, 8, 8, true>(128, 1); run_tile<4, 8, 8, false>(128, 1); run_tile<8, 8, 4, false>(128, 1);
     run_tile<8, 4, 4, true>(256, 2);
     printf("done\n");
     return 0;
