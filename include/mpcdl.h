@@ -86,7 +86,7 @@ typedef struct {
                                   initial state in, final state out (deep_models.py h_state)               */
     int64_t N;
     int32_t H;
-    /* tuning overrides, 0 = automatic */
+    /* tuning overrides, 0 = automatic; tune_kc < 0 forces the generic ring-fed kernel */
     int32_t tune_rt, tune_ntg, tune_nslots, tune_kc;
 } mpcdl_rollout_args;
 
@@ -102,6 +102,8 @@ int mpcdl_rollout(const mpcdl_rollout_args* args, void* stream);
 /* What mpcdl_rollout would launch for these args (no launch): tile size, grid, smem, config. */
 typedef struct {
     int32_t rt, rj, n_tg, tile_traj, threads, grid, smem_bytes, resident, nslots, slot_floats, ntiles;
+    int32_t variant;           /* 0 = generic ring-fed kernel, 2 = weight-resident MLP kernel               */
+    int32_t ksplit;            /* K slices of a hidden layer (weight-resident MLP kernel)                   */
 } mpcdl_plan;
 int mpcdl_rollout_plan(const mpcdl_rollout_args* args, mpcdl_plan* plan);
 

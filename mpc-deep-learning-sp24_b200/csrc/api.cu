@@ -67,7 +67,22 @@ uint32_t build_parts(const mpcdl_model_desc& d, PartDesc* parts, int& nparts) {
 
 struct Plan {
     int rt, rj, n_tg, TN, nct, grid, smem_bytes, resident, nslots, slot_floats, ntiles;
+    int variant, ks;      // variant 0 = generic ring kernel, 2 = weight-resident MLP kernel (rollout_mlp2.cu)
 };
+
+// weight-resident MLP kernel: candidate tiles and their measured cost (cycles per dependent 64x64 layer,
+// profiles/r01a/mb_layer.log); must match MPCDL_MLP2_CONFIGS in launch.h
+struct Mlp2Cand { int hid, rt, rj, ks, tn_lo, tn_hi, tn_step; };
+const Mlp2Cand kMlp2[] = {
+    {64, 4, 4, 2, 32, 32, 32}, {64, 8, 8, 2, 64, 64, 32}, {64, 8, 8, 1, 128, 256, 32},
+    {32, 4, 4, 2, 32, 64, 32}, {32, 8, 4, 1, 128, 256, 32},
+    {16, 4, 4, 2, 32, 64, 32}, {16, 8, 2, 1, 128, 512, 32},
+};
+double mlp2_cycles(const Mlp2Cand& c, int TN) {
+    if (c.ks == 2 && c.rt == 4) return 2009.0 * TN / 32;
+    if (c.ks == 2) return 4029.0 * TN / 64;
+    return 6596.0 + (TN - 128) * 39.3;
+}
 
 int g_num_sms = 0, g_cc_major = 0;
 int device_info() {
@@ -108,6 +123,30 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
     int width_max = 0, bias_max = 0;
     for (int i = 0; i < nparts; ++i) { width_max = std::max<int>(width_max, parts[i].width); bias_max = std::max<int>(bias_max, parts[i].bias_floats); }
 
+    if (!rnn && !a.noise_wblob && !a.tune_nslots && a.tune_kc >= 0 && d.hidden <= 64) {
+        double best2 = 1e300;
+        bool found2 = false;
+        for (const Mlp2Cand& c : kMlp2) {
+            if (c.hid != d.hidden || (a.tune_rt && a.tune_rt != c.rt)) continue;
+            for (int TN = c.tn_lo; TN <= c.tn_hi; TN += c.tn_step) {
+                if (a.tune_ntg && a.tune_ntg * c.rt != TN) continue;
+                if (a.tune_kc && a.tune_kc != c.ks) continue;
+                Plan pl;
+                memset(&pl, 0, sizeof(pl));
+                pl.variant = 2; pl.ks = c.ks; pl.rt = c.rt; pl.rj = c.rj; pl.TN = TN; pl.n_tg = TN / c.rt;
+                pl.nct = pl.n_tg * (d.hidden / c.rj) * c.ks;
+                if (pl.nct % 32 || pl.nct > ((d.hidden == 16 && c.rt == 8) ? 512 : 256) || pl.nct < TN) continue;
+                pl.resident = 1; pl.nslots = 1; pl.slot_floats = 0;
+                pl.smem_bytes = mlp2_smem_bytes((int)total, d.hidden, TN, c.ks, c.rt, c.rj);
+                if (pl.smem_bytes > SMEM_LIMIT) continue;
+                pl.ntiles = (int)((a.N + TN - 1) / TN);
+                pl.grid = std::min(pl.ntiles, num_sms);
+                const double cost = (double)((pl.ntiles + num_sms - 1) / num_sms) * mlp2_cycles(c, TN);
+                if (cost < best2) { best2 = cost; best = pl; found2 = true; }
+            }
+        }
+        if (found2) return MPCDL_OK;
+    }
     const int rts_mlp[] = {2, 4, 8}, rts_rnn[] = {2, 4, 8};
     const int rj = rnn ? rnn_rj(d.hidden) : mlp_rj(d.hidden);
     const int G = gates(d.kind), NGA = rnn ? 4 : 1;
@@ -125,10 +164,11 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
         for (int n_tg = ntg_max; n_tg >= 1; --n_tg) {
             if (a.tune_ntg && n_tg != a.tune_ntg) continue;
             Plan pl;
+            pl.variant = 0; pl.ks = 1;
             pl.rt = rt; pl.rj = rj; pl.n_tg = n_tg; pl.TN = n_tg * rt;
             pl.nct = (n_tg * n_jg + 31) / 32 * 32;
             pl.resident = (!a.tune_nslots && total <= 24576u) ? 1 : 0;
-            int kc_rows = a.tune_kc ? a.tune_kc : std::max(1, 4096 / width_max);
+            int kc_rows = a.tune_kc > 0 ? a.tune_kc : std::max(1, 4096 / width_max);
             pl.slot_floats = std::max(kc_rows * width_max, bias_max);
             pl.nslots = pl.resident ? 1 : (a.tune_nslots ? a.tune_nslots : 3);
             ModelParams m;
@@ -284,9 +324,9 @@ int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
     Plan pl;
     rc = make_plan(*a, pl, sms);
     if (rc) return rc;
-    out->rt = pl.rt; out->rj = pl.rj; out->n_tg = pl.n_tg; out->tile_traj = pl.TN; out->threads = pl.nct + 32;
+    out->rt = pl.rt; out->rj = pl.rj; out->n_tg = pl.n_tg; out->tile_traj = pl.TN; out->threads = pl.nct + (pl.variant == 2 ? 0 : 32);
     out->grid = pl.grid; out->smem_bytes = pl.smem_bytes; out->resident = pl.resident; out->nslots = pl.nslots;
-    out->slot_floats = pl.slot_floats; out->ntiles = pl.ntiles;
+    out->slot_floats = pl.slot_floats; out->ntiles = pl.ntiles; out->variant = pl.variant; out->ksplit = pl.ks;
     return MPCDL_OK;
 }
 
@@ -314,7 +354,8 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     cudaError_t e;
-    if (a->model.kind == MPCDL_MLP) e = launch_mlp(p, pl.rt, pl.rj, pl.grid, pl.smem_bytes, st);
+    if (pl.variant == 2) e = launch_mlp2(p, pl.rt, pl.rj, pl.ks, pl.grid, pl.smem_bytes, st);
+    else if (a->model.kind == MPCDL_MLP) e = launch_mlp(p, pl.rt, pl.rj, pl.grid, pl.smem_bytes, st);
     else e = launch_rnn(p, a->model.kind == MPCDL_GRU ? 0 : 1, pl.rt, pl.rj, pl.grid, pl.smem_bytes, st);
     if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "kernel launch failed: %s (rt=%d n_tg=%d smem=%d)", cudaGetErrorString(e), pl.rt, pl.n_tg, pl.smem_bytes);
     return MPCDL_OK;

@@ -14,6 +14,10 @@ namespace mpcdl {
     X(16, 2, 4) X(16, 4, 4) X(32, 2, 4) X(32, 4, 4) X(64, 2, 4) X(64, 4, 4) X(64, 8, 4) \
     X(128, 2, 4) X(128, 4, 4) X(256, 2, 4) X(256, 4, 4)
 
+// weight-resident MLP kernel (rollout_mlp2.cu): (hidden, RT, RJ, KSPLIT)
+#define MPCDL_MLP2_CONFIGS(X) \
+    X(64, 4, 4, 2) X(64, 8, 8, 2) X(64, 8, 8, 1) X(32, 4, 4, 2) X(32, 8, 4, 1) X(16, 4, 4, 2) X(16, 8, 2, 1)
+
 // CTA sizes are kept at 8 or 16 warps INCLUDING the producer warp: a 17th (or 9th) warp would put a
 // 5th (3rd) warp on one SM sub-partition and cut the per-thread register budget from 128 to 96.
 constexpr int MLP_MAX_THREADS = 512;                 // 480 consumers + producer warp, <= 128 regs
@@ -24,6 +28,8 @@ inline int mlp_rj(int hid) { return hid <= 16 ? 2 : hid <= 128 ? 4 : 8; }
 inline int rnn_rj(int) { return 4; }
 
 cudaError_t launch_mlp(const RolloutParams& p, int rt, int rj, int grid, int smem_bytes, cudaStream_t st);
+cudaError_t launch_mlp2(const RolloutParams& p, int rt, int rj, int ks, int grid, int smem_bytes, cudaStream_t st);
+int mlp2_smem_bytes(int blob_floats, int hid, int TN, int ks, int rt, int rj);
 cudaError_t launch_rnn(const RolloutParams& p, int cell, int rt, int rj, int grid, int smem_bytes, cudaStream_t st);
 cudaError_t launch_ffma_peak(float* out, int iters, int grid, cudaStream_t st);
 

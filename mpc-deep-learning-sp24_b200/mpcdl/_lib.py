@@ -52,7 +52,7 @@ class RolloutArgs(C.Structure):
 
 class Plan(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("rt", "rj", "n_tg", "tile_traj", "threads", "grid", "smem_bytes",
-                                         "resident", "nslots", "slot_floats", "ntiles")]
+                                         "resident", "nslots", "slot_floats", "ntiles", "variant", "ksplit")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

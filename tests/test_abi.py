@@ -30,7 +30,7 @@ def test_struct_layout_matches_header():
     # mpcdl_rollout_args: 4 ints model + stateful + 7 pointers ... the ctypes mirror must agree with the
     # compiler's layout; the library reports its own sizeof through the planner accepting our struct.
     assert C.sizeof(_lib.ModelDesc) == 16
-    assert C.sizeof(_lib.Plan) == 44
+    assert C.sizeof(_lib.Plan) == 52
     assert C.sizeof(_lib.RolloutArgs) % 8 == 0
 
 
