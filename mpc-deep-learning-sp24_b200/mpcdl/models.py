@@ -44,19 +44,35 @@ class _RolloutMixin:
     def _blob(self, device):
         raise NotImplementedError
 
+    @staticmethod
+    def _tkey(t):
+        return (t.data_ptr(), t._version, str(t.device)) if isinstance(t, torch.Tensor) else id(t)
+
     def _norm(self, stats, device):
+        """Device copy of the statistics vector, cached on the identity/version of the stats tensors
+        (no per-call host work: the planner calls rollout() in a tight loop)."""
         if stats is None:
-            key = ("identity", str(device))
+            key = ("identity", str(device), self._desc()[2])
             if getattr(self, "_norm_key", None) != key:
                 self._norm_buf = pack.identity_norm(self._desc()[2]).to(device)
                 self._norm_key = key
             return self._norm_buf
-        buf = pack.pack_norm(stats)
-        key = (buf.numpy().tobytes(), str(device))
+        key = (str(device),) + tuple(self._tkey(stats[k]) for k in ("f_mean", "f_std", "l_mean", "l_std"))
         if getattr(self, "_norm_key", None) != key:
-            self._norm_buf = buf.to(device)
+            self._norm_buf = pack.pack_norm({k: torch.as_tensor(v).detach().cpu() for k, v in stats.items()}).to(device)
             self._norm_key = key
         return self._norm_buf
+
+    def _cost(self, cost, device):
+        """(ref [H,6], qw [6], rw [2]) -> (device ref, 8 python floats), cached like the statistics so
+        weights that live on the GPU are read back (a device sync) once, not on every call."""
+        key = (str(device),) + tuple(self._tkey(c) for c in cost)
+        if getattr(self, "_cost_key", None) != key:
+            cref = torch.as_tensor(cost[0]).to(device, torch.float32).contiguous()
+            cw = [float(v) for v in torch.as_tensor(cost[1]).detach().cpu().reshape(-1)] + \
+                 [float(v) for v in torch.as_tensor(cost[2]).detach().cpu().reshape(-1)]
+            self._cost_val, self._cost_key = (cref, cw), key
+        return self._cost_val
 
     @torch.no_grad()
     def rollout(self, init, U, stats=None, *, noise=None, eps=None, seed=0, traj_offset=0, cost=None,
@@ -80,8 +96,7 @@ class _RolloutMixin:
             nblob, ncfg = noise.packed(dev), noise.cfg()
         cref, cw = None, []
         if cost is not None:
-            cref = cost[0].to(dev, torch.float32).contiguous()
-            cw = [float(v) for v in cost[1]] + [float(v) for v in cost[2]]
+            cref, cw = self._cost(cost, dev)
         states, costs = ops.OPS[self.KIND](self._blob(dev), self._norm(stats, dev), init, U, hidden, layers, window,
                                            stateful, carry if stateful else None, nblob, ncfg, eps, int(seed),
                                            int(traj_offset), cref, cw, bool(return_states), cost is not None,
