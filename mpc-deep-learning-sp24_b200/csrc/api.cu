@@ -105,6 +105,15 @@ void fill_model(ModelParams& m, const mpcdl_rollout_args& a, const Plan& pl, uin
     m.nslots = pl.nslots; m.slot_floats = pl.slot_floats; m.resident = pl.resident;
 }
 
+void fill_io(IoParams& io, const mpcdl_rollout_args& a, int ntiles) {
+    io.norm = a.norm; io.init = a.init; io.U = a.U; io.states = a.states; io.costs = a.costs;
+    io.cost_ref = a.cost_ref;
+    for (int i = 0; i < 6; ++i) io.qw[i] = a.cost_qw[i];
+    for (int i = 0; i < 2; ++i) io.rw[i] = a.cost_rw[i];
+    io.eps = a.eps; io.seed = a.seed; io.traj_offset = a.traj_offset; io.carry = a.carry;
+    io.N = a.N; io.H = a.H; io.ntiles = ntiles;
+}
+
 void fill_noise(NoiseParams& nz, const mpcdl_rollout_args& a) {
     memset(&nz, 0, sizeof(nz));
     if (!a.noise_wblob) return;
@@ -112,6 +121,66 @@ void fill_noise(NoiseParams& nz, const mpcdl_rollout_args& a) {
     nz.hist = a.noise_history; nz.size = a.noise_size; nz.nlayers = a.noise_layers; nz.act = a.noise_act;
     nz.in_dim = 8 * a.noise_history;
     nz.blob_floats = (int)mpcdl_noise_blob_floats(a.noise_history, a.noise_size, a.noise_layers);
+}
+
+
+// ---------------------------------------------------------------------------- tensor-core (tcgen05) path
+bool tc_supported(const mpcdl_model_desc& d) { return d.kind != MPCDL_MLP && d.hidden == TC_HID && d.window == TC_T; }
+
+// blob: [bias L*64*4][fc 64*8+8][pad to 32 floats][per layer: x chunks, h chunks]
+uint32_t build_tc_parts(const mpcdl_model_desc& d, TcPart* parts, uint32_t& bias_off, uint32_t& fc_off) {
+    const int G = gates(d.kind);
+    uint32_t off = 0;
+    bias_off = off; off += (uint32_t)d.layers * TC_HID * 4;
+    fc_off = off;   off += TC_HID * 8 + 8;
+    off = (off + 31u) / 32u * 32u;
+    for (int l = 0; l < d.layers; ++l)
+        for (int part = 0; part < 2; ++part) {
+            TcPart& p = parts[2 * l + part];
+            p.K = (uint16_t)((part == 0 && l == 0) ? 8 : TC_HID);
+            p.kc = (uint16_t)std::min<int>(p.K, TC_KS);
+            p.nchunks = (uint16_t)(p.K / p.kc);
+            p.N = (uint16_t)(G * TC_HID);
+            p.chunk_floats = 2u * p.kc * p.N;
+            p.off = off;
+            off += p.nchunks * p.chunk_floats;
+        }
+    return off;
+}
+
+float tf32_rna_host(float x) {          // cvt.rna.tf32.f32: round to nearest, ties away, 10 explicit mantissa bits
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    u = (u + 0x1000u) & 0xFFFFE000u;
+    float r;
+    memcpy(&r, &u, 4);
+    return r;
+}
+
+struct TcPlan { int nslots, slot_floats, resident, smem_bytes, ntiles, grid; };
+
+int make_tc_plan(const mpcdl_rollout_args& a, TcPlan& pl, int num_sms) {
+    const mpcdl_model_desc& d = a.model;
+    TcPart parts[2 * MAX_LAYERS];
+    uint32_t bo, fo;
+    build_tc_parts(d, parts, bo, fo);
+    uint32_t chunk_max = 0;
+    for (int i = 0; i < 2 * d.layers; ++i) chunk_max = std::max(chunk_max, parts[i].chunk_floats);
+    pl.slot_floats = (int)(a.precision == MPCDL_PREC_TF32X3 ? chunk_max : chunk_max / 2);
+    NoiseParams nz;
+    fill_noise(nz, a);
+    const int fixed = tc_layout(0, 0, d.layers, TC_T, nz).total * 4;
+    int nslots = (SMEM_LIMIT - fixed) / (pl.slot_floats * 4);
+    nslots = std::min(nslots, TC_MAX_SLOTS);
+    if (a.tune_nslots > 0) nslots = std::min(nslots, a.tune_nslots);
+    if (nslots < 2) return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core rollout: shared memory holds only %d weight slots (noise net too large?)", nslots);
+    const int per_layer = d.layers > 1 ? 2 * (TC_HID / TC_KS) : 1 + TC_HID / TC_KS;
+    pl.resident = (nslots >= per_layer && a.tune_kc >= 0) ? 1 : 0;
+    pl.nslots = nslots;
+    pl.smem_bytes = std::max(tc_layout(nslots, pl.slot_floats, d.layers, TC_T, nz).total * 4, 120 * 1024);   // > half an SM: one CTA (one TMEM owner) per SM
+    pl.ntiles = (int)((a.N + TC_TN - 1) / TC_TN);
+    pl.grid = std::min(pl.ntiles, num_sms);
+    return MPCDL_OK;
 }
 
 int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
@@ -191,14 +260,23 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
     return MPCDL_OK;
 }
 
+bool tc_supported(const mpcdl_model_desc& d);
 int check_args(const mpcdl_rollout_args* a) {
     if (!a) return fail(MPCDL_ERR_ARG, "args is NULL");
     int rc = check_desc(&a->model);
     if (rc) return rc;
     if (a->N < 1 || a->H < 1) return fail(MPCDL_ERR_ARG, "N=%lld H=%d must be >= 1", (long long)a->N, a->H);
-    if (!a->wblob || !a->norm || !a->init || !a->U) return fail(MPCDL_ERR_ARG, "wblob/norm/init/U must be non-NULL device pointers");
+    if ((!a->wblob && a->precision == MPCDL_PREC_FP32) || !a->norm || !a->init || !a->U)
+        return fail(MPCDL_ERR_ARG, "wblob/norm/init/U must be non-NULL device pointers");
     if (!a->states && !a->costs) return fail(MPCDL_ERR_ARG, "both outputs (states, costs) are NULL");
     if (a->model.kind != MPCDL_MLP && a->stateful && !a->carry) return fail(MPCDL_ERR_ARG, "stateful rollout needs a carry buffer");
+    if (a->precision != MPCDL_PREC_FP32) {
+        if (a->precision != MPCDL_PREC_TF32X3 && a->precision != MPCDL_PREC_TF32) return fail(MPCDL_ERR_ARG, "unknown precision %d", a->precision);
+        if (!tc_supported(a->model))
+            return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core precision needs a GRU/LSTM with hidden=%d window=%d (got kind=%d hidden=%d window=%d); use MPCDL_PREC_FP32",
+                        TC_HID, TC_T, a->model.kind, a->model.hidden, a->model.window);
+        if (!a->wblob_tc) return fail(MPCDL_ERR_ARG, "tensor-core precision needs wblob_tc (mpcdl_pack_rnn_tc)");
+    }
     if (a->noise_wblob) {
         if (a->noise_history < 1 || a->noise_history > 8) return fail(MPCDL_ERR_UNSUPPORTED, "noise history=%d outside [1,8]", a->noise_history);
         if (a->noise_size < 4 || a->noise_size > 64 || a->noise_size % 4) return fail(MPCDL_ERR_UNSUPPORTED, "noise size=%d must be a multiple of 4 in [4,64]", a->noise_size);
@@ -290,6 +368,62 @@ int mpcdl_pack_rnn(const mpcdl_model_desc* desc, const float* const* w_ih, const
     return MPCDL_OK;
 }
 
+
+size_t mpcdl_blob_floats_tc(const mpcdl_model_desc* desc) {
+    if (check_desc(desc)) return 0;
+    if (!tc_supported(*desc)) { fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: GRU/LSTM with hidden=%d window=%d only", TC_HID, TC_T); return 0; }
+    TcPart parts[2 * MAX_LAYERS];
+    uint32_t bo, fo;
+    return build_tc_parts(*desc, parts, bo, fo);
+}
+
+int mpcdl_pack_rnn_tc(const mpcdl_model_desc* desc, const float* const* w_ih, const float* const* w_hh,
+                      const float* const* b_ih, const float* const* b_hh, const float* fc_w, const float* fc_b, float* blob) {
+    int rc = check_desc(desc);
+    if (rc) return rc;
+    if (!tc_supported(*desc)) return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: GRU/LSTM with hidden=%d window=%d only", TC_HID, TC_T);
+    if (!w_ih || !w_hh || !b_ih || !b_hh || !fc_w || !fc_b || !blob) return fail(MPCDL_ERR_ARG, "mpcdl_pack_rnn_tc: bad arguments");
+    TcPart parts[2 * MAX_LAYERS];
+    uint32_t bias_off, fc_off;
+    const uint32_t total = build_tc_parts(*desc, parts, bias_off, fc_off);
+    std::fill(blob, blob + total, 0.f);
+    const int h = TC_HID;
+    for (int l = 0; l < desc->layers; ++l) {
+        float* bb = blob + bias_off + (size_t)l * h * 4;
+        for (int j = 0; j < h; ++j) {
+            if (desc->kind == MPCDL_GRU) {       // b_r, b_z (ih + hh summed), b_in, b_hn (kept apart: r gates h_n + b_hn)
+                bb[j * 4 + 0] = b_ih[l][j] + b_hh[l][j];
+                bb[j * 4 + 1] = b_ih[l][h + j] + b_hh[l][h + j];
+                bb[j * 4 + 2] = b_ih[l][2 * h + j];
+                bb[j * 4 + 3] = b_hh[l][2 * h + j];
+            } else {
+                for (int g = 0; g < 4; ++g) bb[j * 4 + g] = b_ih[l][g * h + j] + b_hh[l][g * h + j];
+            }
+        }
+        for (int part = 0; part < 2; ++part) {
+            const TcPart& p = parts[2 * l + part];
+            const float* W = part == 0 ? w_ih[l] : w_hh[l];          // torch layout [N = G*h rows][K]
+            const int K = p.K, N = p.N, kc = p.kc;
+            for (int n = 0; n < N; ++n)
+                for (int k = 0; k < K; ++k) {
+                    const float w = W[(size_t)n * K + k];
+                    const float hi = tf32_rna_host(w), lo = tf32_rna_host(w - hi);
+                    const int c = k / kc, kk = k % kc;
+                    const size_t e = (size_t)(kk / 4) * (N / 8) * 32 + (size_t)(n / 8) * 32 + (n % 8) * 4 + (kk % 4);
+                    float* chunk = blob + p.off + (size_t)c * p.chunk_floats;
+                    chunk[e] = hi;
+                    chunk[(size_t)kc * N + e] = lo;
+                }
+        }
+    }
+    float* fc = blob + fc_off;                                         // [j][8] then bias[8]
+    for (int d = 0; d < 6; ++d) {
+        fc[h * 8 + d] = fc_b[d];
+        for (int j = 0; j < h; ++j) fc[j * 8 + d] = fc_w[d * h + j];
+    }
+    return MPCDL_OK;
+}
+
 size_t mpcdl_noise_blob_floats(int history, int size, int n_layers) {
     size_t total = 0;
     int K = 8 * history;
@@ -321,6 +455,16 @@ int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
     if (rc) return rc;
     if (!out) return fail(MPCDL_ERR_ARG, "plan is NULL");
     int sms = g_num_sms ? g_num_sms : 148;                   // planning works without a device (B200 = 148 SMs)
+    if (a->precision != MPCDL_PREC_FP32) {
+        TcPlan tp;
+        rc = make_tc_plan(*a, tp, sms);
+        if (rc) return rc;
+        memset(out, 0, sizeof(*out));
+        out->rt = 1; out->rj = 32; out->n_tg = TC_TN; out->tile_traj = TC_TN; out->threads = TC_THREADS; out->grid = tp.grid;
+        out->smem_bytes = tp.smem_bytes; out->resident = tp.resident; out->nslots = tp.nslots; out->slot_floats = tp.slot_floats;
+        out->ntiles = tp.ntiles; out->variant = 4; out->ksplit = 1;
+        return MPCDL_OK;
+    }
     Plan pl;
     rc = make_plan(*a, pl, sms);
     if (rc) return rc;
@@ -336,6 +480,24 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     rc = device_info();
     if (rc) return rc;
     if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (a->precision != MPCDL_PREC_FP32) {
+        TcPlan tp;
+        rc = make_tc_plan(*a, tp, g_num_sms);
+        if (rc) return rc;
+        TcRolloutParams q;
+        memset(&q, 0, sizeof(q));
+        build_tc_parts(a->model, q.m.parts, q.m.bias_off, q.m.fc_off);
+        q.m.blob = a->wblob_tc;
+        q.m.cell = a->model.kind == MPCDL_GRU ? 0 : 1;
+        q.m.prec = a->precision; q.m.layers = a->model.layers; q.m.window = a->model.window; q.m.stateful = a->stateful != 0;
+        q.m.nslots = tp.nslots; q.m.slot_floats = tp.slot_floats; q.m.resident = tp.resident;
+        fill_noise(q.nz, *a);
+        fill_io(q.io, *a, tp.ntiles);
+        cudaError_t e = launch_rnn_tc(q, tp.grid, tp.smem_bytes, st);
+        if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "tensor-core kernel launch failed: %s (smem=%d nslots=%d)", cudaGetErrorString(e), tp.smem_bytes, tp.nslots);
+        return MPCDL_OK;
+    }
     Plan pl;
     rc = make_plan(*a, pl, g_num_sms);
     if (rc) return rc;
@@ -345,14 +507,7 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     const uint32_t total = build_parts(a->model, p.m.parts, p.m.nparts);
     fill_model(p.m, *a, pl, total);
     fill_noise(p.nz, *a);
-    p.io.norm = a->norm; p.io.init = a->init; p.io.U = a->U; p.io.states = a->states; p.io.costs = a->costs;
-    p.io.cost_ref = a->cost_ref;
-    for (int i = 0; i < 6; ++i) p.io.qw[i] = a->cost_qw[i];
-    for (int i = 0; i < 2; ++i) p.io.rw[i] = a->cost_rw[i];
-    p.io.eps = a->eps; p.io.seed = a->seed; p.io.traj_offset = a->traj_offset; p.io.carry = a->carry;
-    p.io.N = a->N; p.io.H = a->H; p.io.ntiles = pl.ntiles;
-
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    fill_io(p.io, *a, pl.ntiles);
     cudaError_t e;
     if (pl.variant == 2) e = launch_mlp2(p, pl.rt, pl.rj, pl.ks, pl.grid, pl.smem_bytes, st);
     else if (a->model.kind == MPCDL_MLP) e = launch_mlp(p, pl.rt, pl.rj, pl.grid, pl.smem_bytes, st);

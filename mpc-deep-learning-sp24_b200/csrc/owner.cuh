@@ -39,7 +39,8 @@ __device__ __forceinline__ void noise_push(float* nin, int TN, int pos, int hist
 }
 
 // y (normalised network output, column `pos` of ybuf) -> next raw state; optional noise, cost, store.
-__device__ __forceinline__ void owner_finish(const RolloutParams& p, const float* norm_l /* l_mean[6] l_std[6] */,
+template <class P>
+__device__ __forceinline__ void owner_finish(const P& p, const float* norm_l /* l_mean[6] l_std[6] */,
                                              const float* ybuf, const float* nzb, int TN, int pos, long long n,
                                              bool valid, int t, const float (&u)[2], float (&nxt)[6], float& cost) {
 #pragma unroll

@@ -1,0 +1,249 @@
+// K4: tensor-core (tcgen05 / TMEM) fused whole-horizon rollout of the GRU / LSTM window models.
+//   reference: GRU_Model.forward   model_scripts/deep_models.py:57-66
+//              LSTM_Model.forward  model_scripts/deep_models.py:81-92
+//              per-position z-score model_scripts/deep_models.py:29-36
+//              closed loop         oracle/rollout_ref.py rollout_rnn
+// ncu on the FP32 kernel (profiles/r01b/ncu_c3.txt) shows the step is a dense contraction
+// ([128 x 64] . [64 x 192|256] per cell, fma pipe 43 % active), so the gate GEMMs move to tcgen05:
+//   * one CTA owns a tile of 128 trajectories = the MMA M dimension = one TMEM lane per trajectory;
+//   * D[128 x 256] (gate pre-activations, FP32) lives in TMEM columns 0..255; the A operands (layer input
+//     x_f and recurrent h_{f-1}, 64 tf32 columns each, hi and lo parts) live in TMEM columns 256..511 and
+//     are written by the epilogue threads straight from registers (tcgen05.st) -- activations never
+//     touch shared memory;
+//   * B = the layer's weight rows, pre-split on the host into tf32 hi/lo and pre-arranged in the canonical
+//     K-major UMMA layout, streamed from L2 through a TMA ring (or kept resident per layer when it fits);
+//   * precision TF32X3: D = A_lo.B_hi + A_hi.B_lo + A_hi.B_hi (FP32-class accuracy, stated bound in
+//     DESIGN.md); precision TF32: one pass + MUFU.TANH activations;
+//   * 8 epilogue warps (lane quarter = warp % 4, hidden-unit half = warp / 4) turn D into the new hidden
+//     state with the layer's whole output sequence seq[T][32] held in REGISTERS, and re-publish it as
+//     the next A operands; one control thread issues TMA and MMA.
+#include "owner.cuh"
+#include "umma.cuh"
+#include "tc_params.h"
+#include "launch.h"
+
+namespace mpcdl {
+
+enum { CELL_GRU = 0, CELL_LSTM = 1 };
+
+constexpr uint32_t TC_D = 0, TC_AX_HI = 256, TC_AX_LO = 320, TC_AH_HI = 384, TC_AH_LO = 448;
+
+__device__ __forceinline__ float tanh_fast(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+template <bool FAST> __device__ __forceinline__ float act_tanh(float x) { return FAST ? tanh_fast(x) : tanh_f(x); }
+template <bool FAST> __device__ __forceinline__ float act_sigmoid(float x) {
+    return FAST ? fmaf(tanh_fast(0.5f * x), 0.5f, 0.5f) : sigmoid_f(x);
+}
+
+// registers -> A operand columns [col, col+16) of this thread's TMEM lane, as tf32 hi (and lo)
+template <bool X3>
+__device__ __forceinline__ void stage16(uint32_t t_hi, uint32_t t_lo, const float* v) {
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        hi[i] = umma::tf32_rna(v[i]);
+        lo[i] = X3 ? umma::tf32_rna(v[i] - __uint_as_float(hi[i])) : 0u;
+    }
+    umma::tmem_st16(t_hi, hi);
+    if (X3) umma::tmem_st16(t_lo, lo);
+}
+template <bool X3>
+__device__ __forceinline__ void stage8(uint32_t t_hi, uint32_t t_lo, const float (&v)[8]) {
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        hi[i] = umma::tf32_rna(v[i]);
+        lo[i] = X3 ? umma::tf32_rna(v[i] - __uint_as_float(hi[i])) : 0u;
+    }
+    umma::tmem_st8(t_hi, hi);
+    if (X3) umma::tmem_st8(t_lo, lo);
+}
+
+// ------------------------------------------------------------------ control thread: ring + MMA issue
+struct TcCtl {
+    const TcModel& m;
+    float* ring;
+    uint64_t *full, *empty;
+    uint32_t ld_issued = 0, rel_issued = 0;
+    // load iterator
+    int li_it = 0, li_t = 0, li_l = 0, li_f = 0, li_part = 0, li_c = 0;
+    bool li_done;
+    int my_tiles, H;
+
+    __device__ TcCtl(const TcModel& m_, float* ring_, uint64_t* full_, uint64_t* empty_, int my_tiles_, int H_)
+        : m(m_), ring(ring_), full(full_), empty(empty_), my_tiles(my_tiles_), H(H_) {
+        li_done = my_tiles_ == 0;
+    }
+    __device__ bool part_used(int f, int part) const { return part == 0 || f > 0 || m.stateful; }
+    __device__ void li_advance() {
+        const TcPart& p = m.parts[2 * li_l + li_part];
+        if (++li_c < p.nchunks) return;
+        li_c = 0;
+        if (m.resident) {                       // per layer visit: x chunks, then h chunks (if ever used)
+            if (li_part == 0 && (m.window > 1 || m.stateful)) { li_part = 1; return; }
+            li_part = 0;
+        } else {                                // per cell: x chunks, then h chunks (if used by this frame)
+            if (li_part == 0 && part_used(li_f, 1)) { li_part = 1; return; }
+            li_part = 0;
+            if (++li_f < m.window) return;
+            li_f = 0;
+        }
+        if (++li_l < m.layers) return;
+        li_l = 0;
+        if (++li_t < H) return;
+        li_t = 0;
+        if (++li_it < my_tiles) return;
+        li_done = true;
+    }
+    // Issue ring loads while slots are free.  `need` = load index the caller is about to wait for (that one
+    // is waited for; loads beyond it are only issued when their slot is already free, so MMA issue never
+    // stalls behind a slot whose MMAs are still in flight).
+    __device__ void top_up(uint32_t need) {
+        while (!li_done && ld_issued - rel_issued < (uint32_t)m.nslots) {
+            const uint32_t slot = ld_issued % m.nslots;
+            if (ld_issued >= (uint32_t)m.nslots) {
+                const uint32_t par = ((ld_issued / m.nslots) - 1u) & 1u;
+                if (need != 0xFFFFFFFFu && ld_issued <= need) mbar_wait(&empty[slot], par);
+                else if (!mbar_try_wait(&empty[slot], par)) break;
+            }
+            const TcPart& p = m.parts[2 * li_l + li_part];
+            const uint32_t bytes = (m.prec == PREC_TF32X3 ? p.chunk_floats : p.chunk_floats / 2) * 4u;
+            mbar_expect_tx(&full[slot], bytes);
+            bulk_g2s(ring + (size_t)slot * m.slot_floats, m.blob + p.off + (size_t)li_c * p.chunk_floats, bytes, &full[slot]);
+            ++ld_issued;
+            li_advance();
+        }
+    }
+};
+
+template <int CELL, int PREC>
+__global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __grid_constant__ TcRolloutParams p) {
+    constexpr bool X3 = PREC == PREC_TF32X3;
+    constexpr bool FAST = PREC == PREC_TF32;
+    constexpr int T = TC_T, HID = TC_HID, TN = TC_TN;
+    constexpr int NG = CELL == CELL_GRU ? 3 : 4;
+    extern __shared__ __align__(1024) float sm[];
+    const TcModel& m = p.m;
+    const TcSmem L = tc_layout(m.nslots, m.slot_floats, m.layers, T, p.nz);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int H = p.io.H, NL = m.layers;
+    const long long N = p.io.N;
+    const bool stateful = m.stateful != 0;
+
+    uint64_t* full = reinterpret_cast<uint64_t*>(sm + L.bars);
+    uint64_t* empty = full + TC_MAX_SLOTS;
+    uint64_t* opnd_ready = empty + TC_MAX_SLOTS;
+    uint64_t* acc_ready = opnd_ready + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_ready + 1);
+
+    if (tid == 0) {
+        for (int i = 0; i < m.nslots; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        mbar_init(opnd_ready, TC_EPI_THREADS);
+        mbar_init(acc_ready, 1);
+        mbar_fence_init();
+    }
+    if (warp == 8) { umma::tmem_alloc(tmem_slot, 512); umma::tmem_relinquish(); }
+    // tile-invariant constants -> shared memory
+    for (int i = tid; i < NL * HID * 4; i += blockDim.x) sm[L.bias + i] = m.blob[m.bias_off + i];
+    for (int i = tid; i < HID * 8 + 8; i += blockDim.x) sm[L.fc + i] = m.blob[m.fc_off + i];
+    for (int i = tid; i < 2 * T * 8 + 12; i += blockDim.x) sm[L.norm + i] = p.io.norm[i];
+    if (p.nz.enabled)
+        for (int i = tid; i < p.nz.blob_floats; i += blockDim.x) sm[L.nblob + i] = p.nz.blob[i];
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+    const uint32_t tbase = *tmem_slot;
+    const int my_tiles = (p.io.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+    if (warp >= 8) {
+        // ============================================================== control warpgroup (one active thread)
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == 8 && lane == 0) {
+            TcCtl c(m, sm + L.ring, full, empty, my_tiles, H);
+            uint32_t use_ctr = 0, layer_base = 0, cellpar = 0;
+            const uint32_t ring_s = smem_u32(sm + L.ring);
+            for (int it = 0; it < my_tiles; ++it)
+                for (int t = 0; t < H; ++t)
+                    for (int l = 0; l < NL; ++l) {
+                        const int nkx = m.parts[2 * l].nchunks, nkh = m.parts[2 * l + 1].nchunks;
+                        for (int f = 0; f < T; ++f) {
+                            c.top_up(0xFFFFFFFFu);
+                            mbar_wait(opnd_ready, cellpar);
+                            cellpar ^= 1u;
+                            umma::fence_after_sync();
+                            uint32_t acc_main = 0, acc_nh = 0;
+                            const int nparts = c.part_used(f, 1) ? 2 : 1;
+                            for (int part = 0; part < nparts; ++part) {
+                                const TcPart& pt = m.parts[2 * l + part];
+                                const uint32_t lbo = (pt.N / 8) * 128u;
+                                const uint32_t blk_bytes = (pt.kc / 4) * lbo;
+                                const uint32_t a_hi = tbase + (part ? TC_AH_HI : TC_AX_HI), a_lo = tbase + (part ? TC_AH_LO : TC_AX_LO);
+                                for (int ch = 0; ch < pt.nchunks; ++ch) {
+                                    const uint32_t ld = m.resident ? layer_base + (part ? nkx : 0) + ch : use_ctr++;
+                                    c.top_up(ld);
+                                    const uint32_t slot = ld % m.nslots;
+                                    mbar_wait(&full[slot], (ld / m.nslots) & 1u);
+                                    umma::fence_after_sync();
+                                    const uint32_t sb = ring_s + slot * m.slot_floats * 4u;
+#pragma unroll
+                                    for (int pass = X3 ? 0 : 2; pass < 3; ++pass) {
+                                        const uint32_t a_col = (pass == 0 ? a_lo : a_hi) + ch * pt.kc;
+                                        const uint32_t b0 = sb + (pass == 1 ? blk_bytes : 0u);
+                                        for (int kk = 0; kk < pt.kc / 8; ++kk) {
+                                            const uint32_t bk = b0 + kk * 2u * lbo;
+                                            if (CELL == CELL_GRU && part == 1) {
+                                                umma::mma_tf32_ts(tbase + TC_D, a_col + kk * 8, umma::smem_desc_kmajor(bk, lbo, 128u),
+                                                                  umma::idesc_tf32(128, 128), acc_main);
+                                                umma::mma_tf32_ts(tbase + TC_D + 192, a_col + kk * 8,
+                                                                  umma::smem_desc_kmajor(bk + 16u * 128u, lbo, 128u),
+                                                                  umma::idesc_tf32(128, 64), acc_nh);
+                                                acc_nh = 1;
+                                            } else {
+                                                umma::mma_tf32_ts(tbase + TC_D, a_col + kk * 8, umma::smem_desc_kmajor(bk, lbo, 128u),
+                                                                  umma::idesc_tf32(128, NG * 64), acc_main);
+                                            }
+                                            acc_main = 1;
+                                        }
+                                    }
+                                    if (!m.resident || f == T - 1) { umma::mma_commit(&empty[slot]); ++c.rel_issued; }
+                                }
+                            }
+                            umma::mma_commit(acc_ready);
+                        }
+                        if (m.resident) layer_base += nkx + ((T > 1 || stateful) ? nkh : 0);
+                    }
+        }
+        __syncwarp();
+    } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+#include "rollout_rnn_tc_epi.inl"
+    }
+    // ------------------------------------------------------------------ teardown
+    umma::fence_before_sync();
+    __syncthreads();
+    if (warp == 8) umma::tmem_dealloc(tbase, 512);
+}
+
+// ------------------------------------------------------------------ launcher
+template <int CELL, int PREC>
+static cudaError_t launch_rnn_tc_t(const TcRolloutParams& p, int grid, int smem_bytes, cudaStream_t st) {
+    auto k = rollout_rnn_tc_kernel<CELL, PREC>;
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    if (e != cudaSuccess) return e;
+    k<<<grid, TC_THREADS, smem_bytes, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rnn_tc(const TcRolloutParams& p, int grid, int smem_bytes, cudaStream_t st) {
+    const bool gru = p.m.cell == CELL_GRU;
+    if (p.m.prec == PREC_TF32X3)
+        return gru ? launch_rnn_tc_t<CELL_GRU, PREC_TF32X3>(p, grid, smem_bytes, st) : launch_rnn_tc_t<CELL_LSTM, PREC_TF32X3>(p, grid, smem_bytes, st);
+    if (p.m.prec == PREC_TF32)
+        return gru ? launch_rnn_tc_t<CELL_GRU, PREC_TF32>(p, grid, smem_bytes, st) : launch_rnn_tc_t<CELL_LSTM, PREC_TF32>(p, grid, smem_bytes, st);
+    return cudaErrorInvalidConfiguration;
+}
+
+}  // namespace mpcdl

@@ -1,0 +1,210 @@
+// Epilogue warps of rollout_rnn_tc_kernel (included inside the kernel body; warps 0..7).
+// Thread <-> data: TMEM lane / trajectory row = 32*(warp%4) + lane; hidden units [32*uh, 32*uh+32), uh = warp/4.
+{
+    const int q = warp & 3, uh = warp >> 2;
+    const int row = q * 32 + lane;
+    const int u0 = uh * 32;
+    const bool owner = uh == 0;
+    const uint32_t tlane = tbase + (static_cast<uint32_t>(q * 32) << 16);
+    float* const normS = sm + L.norm;                  // f_mean[T*8] f_std[T*8] l_mean[6] l_std[6]
+    float* const xwin = sm + L.xwin;                   // raw window [T][8][TN]
+    float* const ypart = sm + L.ypart;                 // [2][8][TN]
+    float* const ybuf = sm + L.ybuf;                   // [8][TN]
+    float* const nin = sm + L.nin;
+    float* const nact0 = sm + L.nact0;
+    const int nact_flip = L.nact1 - L.nact0;
+    float* const nzb = sm + L.nzb;
+    const float4* const biasS = reinterpret_cast<const float4*>(sm + L.bias);
+    const float* const fcS = sm + L.fc;
+    uint32_t cellpar = 0;
+
+    for (int tile = blockIdx.x; tile < p.io.ntiles; tile += gridDim.x) {
+        long long n = (long long)tile * TN + row;
+        const bool valid = n < N;
+        if (n >= N) n = N - 1;
+        float cost = 0.f;
+        if (owner) {                                   // initial window -> xwin[f][k][row] (own column only)
+            const float4* w4 = reinterpret_cast<const float4*>(p.io.init + n * T * 8);
+#pragma unroll
+            for (int f = 0; f < T; ++f) {
+                float4 a = __ldg(w4 + 2 * f), b = __ldg(w4 + 2 * f + 1);
+                float* d = xwin + f * 8 * TN + row;
+                d[0] = a.x; d[TN] = a.y; d[2 * TN] = a.z; d[3 * TN] = a.w;
+                d[4 * TN] = b.x; d[5 * TN] = b.y; d[6 * TN] = b.z; d[7 * TN] = b.w;
+            }
+        }
+        int base = 0;                                  // physical slot of logical frame 0
+        float seq[T][32];                              // current layer's output sequence, this thread's 32 units
+        for (int t = 0; t < H; ++t) {
+            float u[2] = {0.f, 0.f};
+            if (owner) {
+                float2 uu = __ldg(reinterpret_cast<const float2*>(p.io.U + (n * H + t) * 2));
+                u[0] = uu.x; u[1] = uu.y;
+                if (p.nz.enabled) {                    // newest frame feeds the noise history
+                    int pf = base + T - 1; if (pf >= T) pf -= T;
+                    float s[6], uf[2];
+#pragma unroll
+                    for (int d = 0; d < 6; ++d) s[d] = xwin[(pf * 8 + d) * TN + row];
+                    uf[0] = xwin[(pf * 8 + 6) * TN + row]; uf[1] = xwin[(pf * 8 + 7) * TN + row];
+                    noise_push(nin, TN, row, p.nz.hist, t == 0, s, uf);
+                }
+            }
+            for (int l = 0; l < NL; ++l) {
+                float cst[32];                         // LSTM cell state (register resident across the frames)
+#pragma unroll
+                for (int j = 0; j < 32; ++j) cst[j] = 0.f;
+                const float* carry_h = nullptr;
+                float* carry_c = nullptr;
+                if (stateful) {
+                    carry_h = p.io.carry + ((long long)l * N + n) * HID + u0;
+                    if (CELL == CELL_LSTM) {
+                        carry_c = p.io.carry + ((long long)(NL + l) * N + n) * HID + u0;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            float4 v = *reinterpret_cast<const float4*>(carry_c + j);
+                            cst[j] = v.x; cst[j + 1] = v.y; cst[j + 2] = v.z; cst[j + 3] = v.w;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int f = 0; f < T; ++f) {
+                    const bool has_h = f > 0 || stateful;
+                    // ---- publish the A operands of cell (l, f)
+                    if (l == 0) {
+                        if (owner) {                   // per-position z-score of frame f (deep_models.py:35)
+                            int pf = base + f; if (pf >= T) pf -= T;
+                            float xn[8];
+#pragma unroll
+                            for (int k = 0; k < 8; ++k)
+                                xn[k] = __fdiv_rn(__fsub_rn(xwin[(pf * 8 + k) * TN + row], normS[f * 8 + k]), normS[T * 8 + f * 8 + k]);
+                            stage8<X3>(tlane + TC_AX_HI, tlane + TC_AX_LO, xn);
+                        }
+                    } else {
+                        stage16<X3>(tlane + TC_AX_HI + u0, tlane + TC_AX_LO + u0, &seq[f][0]);
+                        stage16<X3>(tlane + TC_AX_HI + u0 + 16, tlane + TC_AX_LO + u0 + 16, &seq[f][16]);
+                    }
+                    if (has_h) {
+                        if (f > 0) {
+                            stage16<X3>(tlane + TC_AH_HI + u0, tlane + TC_AH_LO + u0, &seq[f > 0 ? f - 1 : 0][0]);
+                            stage16<X3>(tlane + TC_AH_HI + u0 + 16, tlane + TC_AH_LO + u0 + 16, &seq[f > 0 ? f - 1 : 0][16]);
+                        } else {
+                            float hv[16];
+#pragma unroll
+                            for (int hb = 0; hb < 2; ++hb) {
+#pragma unroll
+                                for (int j = 0; j < 16; j += 4) {
+                                    float4 v = *reinterpret_cast<const float4*>(carry_h + hb * 16 + j);
+                                    hv[j] = v.x; hv[j + 1] = v.y; hv[j + 2] = v.z; hv[j + 3] = v.w;
+                                }
+                                stage16<X3>(tlane + TC_AH_HI + u0 + hb * 16, tlane + TC_AH_LO + u0 + hb * 16, hv);
+                            }
+                        }
+                    }
+                    umma::wait_st();
+                    umma::fence_before_sync();
+                    mbar_arrive(opnd_ready);
+                    // ---- gate pre-activations of this cell
+                    mbar_wait(acc_ready, cellpar);
+                    cellpar ^= 1u;
+                    umma::fence_after_sync();
+#pragma unroll
+                    for (int ub = 0; ub < 4; ++ub) {
+                        float g0[8], g1[8], g2[8], g3[8], hold[8];
+                        const uint32_t c0 = tlane + TC_D + u0 + ub * 8;
+                        umma::tmem_ld8(c0, g0);
+                        umma::tmem_ld8(c0 + 64, g1);
+                        umma::tmem_ld8(c0 + 128, g2);
+                        if (CELL == CELL_LSTM || has_h) umma::tmem_ld8(c0 + 192, g3);
+                        umma::wait_ld();
+                        if (f > 0) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) hold[i] = seq[f > 0 ? f - 1 : 0][ub * 8 + i];
+                        } else if (stateful) {
+                            float4 v0 = *reinterpret_cast<const float4*>(carry_h + ub * 8), v1 = *reinterpret_cast<const float4*>(carry_h + ub * 8 + 4);
+                            hold[0] = v0.x; hold[1] = v0.y; hold[2] = v0.z; hold[3] = v0.w;
+                            hold[4] = v1.x; hold[5] = v1.y; hold[6] = v1.z; hold[7] = v1.w;
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) hold[i] = 0.f;
+                        }
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int j = ub * 8 + i;
+                            const float4 b = biasS[l * HID + u0 + j];
+                            if (CELL == CELL_GRU) {
+                                // torch GRU cell: n = tanh(i_n + b_in + r*(h_n + b_hn)); h' = (h - n)*z + n
+                                const float rg = act_sigmoid<FAST>(g0[i] + b.x);
+                                const float zg = act_sigmoid<FAST>(g1[i] + b.y);
+                                const float hn = has_h ? g3[i] + b.w : b.w;
+                                const float ng = act_tanh<FAST>(fmaf(rg, hn, g2[i] + b.z));
+                                seq[f][j] = fmaf(hold[i] - ng, zg, ng);
+                            } else {
+                                // torch LSTM cell: c' = f*c + i*g; h' = o*tanh(c')
+                                const float ig = act_sigmoid<FAST>(g0[i] + b.x);
+                                const float fg = act_sigmoid<FAST>(g1[i] + b.y);
+                                const float gg = act_tanh<FAST>(g2[i] + b.z);
+                                const float og = act_sigmoid<FAST>(g3[i] + b.w);
+                                const float cn = fmaf(fg, cst[j], ig * gg);
+                                cst[j] = cn;
+                                seq[f][j] = og * act_tanh<FAST>(cn);
+                            }
+                        }
+                    }
+                    umma::fence_before_sync();         // D reads are ordered before the next cell's MMAs
+                    if (stateful && f == T - 1 && valid) {
+                        float* ch = p.io.carry + ((long long)l * N + n) * HID + u0;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            *reinterpret_cast<float4*>(ch + j) = make_float4(seq[f][j], seq[f][j + 1], seq[f][j + 2], seq[f][j + 3]);
+                            if (CELL == CELL_LSTM)
+                                *reinterpret_cast<float4*>(carry_c + j) = make_float4(cst[j], cst[j + 1], cst[j + 2], cst[j + 3]);
+                        }
+                    }
+                }
+            }
+            // ---- head: full_c(out[:, -1, :]) partial sums over this thread's 32 units
+            {
+                float y[8];
+#pragma unroll
+                for (int d = 0; d < 8; ++d) y[d] = 0.f;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const float4 w0 = *reinterpret_cast<const float4*>(fcS + (u0 + j) * 8);
+                    const float4 w1 = *reinterpret_cast<const float4*>(fcS + (u0 + j) * 8 + 4);
+                    const float a = seq[T - 1][j];
+                    y[0] = fmaf(a, w0.x, y[0]); y[1] = fmaf(a, w0.y, y[1]); y[2] = fmaf(a, w0.z, y[2]); y[3] = fmaf(a, w0.w, y[3]);
+                    y[4] = fmaf(a, w1.x, y[4]); y[5] = fmaf(a, w1.y, y[5]);
+                }
+#pragma unroll
+                for (int d = 0; d < 6; ++d) ypart[(uh * 8 + d) * TN + row] = y[d];
+            }
+            named_bar_sync(1, TC_EPI_THREADS);
+            if (p.nz.enabled) {                        // residual-noise net on the CUDA cores (noise_model.py:34-40)
+                const float* W = sm + L.nblob;
+                int K = p.nz.in_dim;
+                for (int ph = 0; ph <= p.nz.nlayers; ++ph) {
+                    const bool last = ph == p.nz.nlayers;
+                    const int outw = last ? 12 : p.nz.size;
+                    dense_resident<4, 4>(ph == 0 ? nin : nact0 + ((ph - 1) & 1) * nact_flip, K, W, outw, outw,
+                                         last ? ACT_IDENTITY : p.nz.act, last ? nzb : nact0 + (ph & 1) * nact_flip, TN, tid, TC_EPI_THREADS);
+                    W += (K + 1) * outw; K = p.nz.size;
+                    named_bar_sync(1, TC_EPI_THREADS);
+                }
+            }
+            // ---- owner: next state, shift the window (overwrite the oldest physical frame)
+            if (owner) {
+#pragma unroll
+                for (int d = 0; d < 6; ++d)
+                    ybuf[d * TN + row] = (fcS[HID * 8 + d] + ypart[d * TN + row]) + ypart[(8 + d) * TN + row];
+                float nxt[6];
+                owner_finish(p, normS + 2 * T * 8, ybuf, nzb, TN, row, n, valid, t, u, nxt, cost);
+                float* d = xwin + base * 8 * TN + row;
+#pragma unroll
+                for (int k = 0; k < 6; ++k) d[k * TN] = nxt[k];
+                d[6 * TN] = u[0]; d[7 * TN] = u[1];
+            }
+            base = base + 1 == T ? 0 : base + 1;
+        }
+        if (owner && valid && p.io.costs) p.io.costs[n] = cost;
+    }
+}

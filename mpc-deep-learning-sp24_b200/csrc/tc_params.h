@@ -1,0 +1,71 @@
+// Parameter block and shared-memory carve-up of the tcgen05 (tensor-core) GRU/LSTM rollout kernel
+// (rollout_rnn_tc.cu).  Host + device.
+#pragma once
+#include <cstdint>
+#include "params.h"
+
+namespace mpcdl {
+
+constexpr int TC_TN = 128;            // trajectories per CTA tile = MMA M (one TMEM lane per trajectory)
+constexpr int TC_HID = 64;            // hidden units (the shipped GRU/LSTM checkpoints)
+constexpr int TC_T = 4;               // window frames (deep_models.py:99 FT_SIZE)
+constexpr int TC_EPI_THREADS = 256;   // 8 epilogue warps: lane quarter = warp % 4, unit half = warp / 4
+constexpr int TC_THREADS = 384;       // + 1 control warpgroup (TMA producer + MMA issuer = one elected lane of warp 8);
+                                      //   a whole warpgroup so that setmaxnreg can move its registers to the epilogue warps
+constexpr int TC_KS = 16;             // K rows per weight chunk (2 tf32 MMA k-steps)
+
+enum { PREC_FP32 = 0, PREC_TF32X3 = 1, PREC_TF32 = 2 };
+
+// One weight matrix of the packed tensor-core blob: W[N rows = gate units][K] stored as `nchunks`
+// K-slices; a chunk is [hi block][lo block], a block is the canonical K-major no-swizzle UMMA layout
+// [k/4][n/8][8 rows][4 k] (core matrix = 8 rows x 16 B).  hi = tf32(w), lo = tf32(w - hi).
+struct TcPart {
+    uint32_t off;            // float offset of chunk 0 in the blob
+    uint32_t chunk_floats;   // hi + lo
+    uint16_t K, kc;          // total K, K per chunk
+    uint16_t nchunks, N;
+};
+
+struct TcModel {
+    const float* blob;
+    uint32_t bias_off;       // [L][HID][4] per-unit gate biases (GRU: b_r, b_z, b_in, b_hn; LSTM: i, f, g, o)
+    uint32_t fc_off;         // full_c: [HID][8] (W^T, cols 6..7 zero) then bias[8]
+    TcPart parts[2 * MAX_LAYERS];      // [2l] = weight_ih_l{l}, [2l+1] = weight_hh_l{l}
+    int cell, prec, layers, window, stateful;
+    int nslots, slot_floats, resident; // ring geometry; resident = a layer's chunks stay for all T frames
+};
+
+struct TcRolloutParams {
+    TcModel m;
+    IoParams io;
+    NoiseParams nz;
+};
+
+struct TcSmem {       // float offsets
+    int bars, ring, bias, fc, norm, xwin, ypart, ybuf, nblob, nin, nact0, nact1, nzb, total;
+};
+
+__host__ __device__ inline TcSmem tc_layout(int nslots, int slot_floats, int layers, int window, const NoiseParams& nz) {
+    TcSmem L;
+    int o = 0;
+    L.bars = o;   o += 64;                                   // full[16] empty[16]... as uint64 + tmem ptr: 256 B
+    o = align_up(o, 32);
+    // barrier block is 64 floats = 32 uint64: full[<=12], empty[<=12], opnd, acc, tmem slot
+    L.ring = o;   o += nslots * slot_floats;
+    L.bias = o;   o += layers * TC_HID * 4;
+    L.fc = o;     o += TC_HID * 8 + 8;
+    L.norm = o;   o += align_up(2 * window * 8 + 12, 4);
+    L.xwin = o;   o += window * 8 * TC_TN;
+    L.ypart = o;  o += 2 * 8 * TC_TN;
+    L.ybuf = o;   o += 8 * TC_TN;
+    L.nblob = o;  o += nz.enabled ? align_up(nz.blob_floats, 4) : 0;
+    L.nin = o;    o += nz.enabled ? nz.in_dim * TC_TN : 0;
+    L.nact0 = o;  o += nz.enabled ? nz.size * TC_TN : 0;
+    L.nact1 = o;  o += nz.enabled ? nz.size * TC_TN : 0;
+    L.nzb = o;    o += nz.enabled ? 12 * TC_TN : 0;
+    L.total = o;
+    return L;
+}
+constexpr int TC_MAX_SLOTS = 12;
+
+}  // namespace mpcdl

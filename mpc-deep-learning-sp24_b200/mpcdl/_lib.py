@@ -12,6 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmpcdl.so")
 
 MLP, GRU, LSTM = 0, 1, 2
+PRECISION = {"fp32": 0, "tf32x3": 1, "tf32": 2}
 ACT = {"identity": 0, "relu": 1, "tanh": 2, "sigmoid": 3}
 
 
@@ -47,6 +48,8 @@ class RolloutArgs(C.Structure):
         ("tune_ntg", C.c_int32),
         ("tune_nslots", C.c_int32),
         ("tune_kc", C.c_int32),
+        ("precision", C.c_int32),
+        ("wblob_tc", C.c_void_p),
     ]
 
 
@@ -58,7 +61,7 @@ class Plan(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
-EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
+EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
            "mpcdl_rollout", "mpcdl_rollout_plan", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version")
 
 
@@ -75,6 +78,10 @@ def _load():
     lib.mpcdl_pack_mlp.argtypes = [C.POINTER(ModelDesc), fpp, fpp, fp]
     lib.mpcdl_pack_rnn.restype = C.c_int
     lib.mpcdl_pack_rnn.argtypes = [C.POINTER(ModelDesc), fpp, fpp, fpp, fpp, fp, fp, fp]
+    lib.mpcdl_blob_floats_tc.restype = C.c_size_t
+    lib.mpcdl_blob_floats_tc.argtypes = [C.POINTER(ModelDesc)]
+    lib.mpcdl_pack_rnn_tc.restype = C.c_int
+    lib.mpcdl_pack_rnn_tc.argtypes = [C.POINTER(ModelDesc), fpp, fpp, fpp, fpp, fp, fp, fp]
     lib.mpcdl_noise_blob_floats.restype = C.c_size_t
     lib.mpcdl_noise_blob_floats.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.mpcdl_pack_noise.restype = C.c_int

@@ -76,13 +76,15 @@ class _RolloutMixin:
 
     @torch.no_grad()
     def rollout(self, init, U, stats=None, *, noise=None, eps=None, seed=0, traj_offset=0, cost=None,
-                return_states=True, stateful=None, carry=None, tune=()):
+                return_states=True, stateful=None, carry=None, tune=(), precision="fp32"):
         """Closed-loop rollout of N trajectories over H steps in one kernel launch.
 
         init  s0 [N,6] (MLP) or window [N,T,8] (GRU/LSTM), raw units; U [N,H,2] controls.
         stats dict(f_mean,f_std,l_mean,l_std) from ``mpcdl.data.zscore_stats`` (None = identity).
         noise FeedforwardNoiseModel (residual injection); eps [N,H,6] draws or None -> Philox(seed).
         cost  (ref [H,6], qw [6], rw [2]) -> per-trajectory quadratic tracking cost.
+        precision "fp32" (FFMA kernels, the parity path) | "tf32x3" | "tf32" (tcgen05 tensor-core kernels,
+              GRU/LSTM hidden 64 window 4 only; anything else raises -- there is no silent fallback).
         Returns (states [N,H,6] or None, costs [N] or None[, carry if stateful])."""
         hidden, layers, window = self._desc()
         dev = U.device
@@ -97,10 +99,15 @@ class _RolloutMixin:
         cref, cw = None, []
         if cost is not None:
             cref, cw = self._cost(cost, dev)
+        if precision not in _lib.PRECISION:
+            raise RuntimeError(f"mpcdl: unknown precision {precision!r} (fp32 | tf32x3 | tf32)")
+        prec = _lib.PRECISION[precision]
+        if prec and self.KIND == _lib.MLP:
+            raise RuntimeError("mpcdl: the tensor-core precisions cover the GRU/LSTM models; Basic_Model runs the FP32 kernels")
         states, costs = ops.OPS[self.KIND](self._blob(dev), self._norm(stats, dev), init, U, hidden, layers, window,
                                            stateful, carry if stateful else None, nblob, ncfg, eps, int(seed),
                                            int(traj_offset), cref, cw, bool(return_states), cost is not None,
-                                           list(tune))
+                                           list(tune), prec, self._blob_tc(dev) if prec else None)
         out = (states if return_states else None, costs if cost is not None else None)
         return out + (carry,) if stateful else out
 
@@ -160,6 +167,13 @@ class _RNNBase(_RolloutMixin, nn.Module):
     def _blob(self, device):
         return self._packed.get(list(self.parameters()), device,
                                 lambda: pack.pack_rnn(self.state_dict(), self.KIND, self.hidden, self.layers, self._window))
+
+    def _blob_tc(self, device):
+        if not hasattr(self, "_packed_tc"):
+            self._packed_tc = _Packed()
+        return self._packed_tc.get(list(self.parameters()), device,
+                                   lambda: pack.pack_rnn(self.state_dict(), self.KIND, self.hidden, self.layers, self._window,
+                                                         tensor_core=True))
 
     def rollout(self, init, U, stats=None, **kw):
         self._window = int(init.shape[1])

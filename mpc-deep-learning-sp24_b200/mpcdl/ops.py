@@ -20,7 +20,8 @@ from . import _lib
 
 _SCHEMA = ("(Tensor wblob, Tensor norm, Tensor init, Tensor U, int hidden, int layers, int window, bool stateful, "
            "Tensor(a!)? carry, Tensor? noise_wblob, int[] noise_cfg, Tensor? eps, int seed, int traj_offset, "
-           "Tensor? cost_ref, float[] cost_w, bool return_states, bool return_costs, int[] tune) -> (Tensor, Tensor)")
+           "Tensor? cost_ref, float[] cost_w, bool return_states, bool return_costs, int[] tune, int precision, "
+           "Tensor? wblob_tc) -> (Tensor, Tensor)")
 
 _libdef = torch.library.Library("mpcdl", "DEF")
 for _name in ("rollout_mlp", "rollout_gru", "rollout_lstm"):
@@ -42,7 +43,7 @@ def _f32c(t: Optional[torch.Tensor], name: str, dev=None) -> int:
 
 
 def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob, noise_cfg,
-                  eps, seed, traj_offset, cost_ref, cost_w, return_states, return_costs, tune):
+                  eps, seed, traj_offset, cost_ref, cost_w, return_states, return_costs, tune, precision=0, wblob_tc=None):
     dev = U.device
     if U.dim() != 3 or U.shape[2] != 2:
         raise RuntimeError(f"mpcdl: U must be [N,H,2], got {tuple(U.shape)}")
@@ -56,13 +57,22 @@ def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, state
         raise RuntimeError(f"mpcdl: norm must hold {2 * nt * 8 + 12} floats (f_mean,f_std [{nt},8]; l_mean,l_std [6])")
     a = _lib.RolloutArgs()
     a.model = _lib.ModelDesc(kind, hidden, layers, T)
-    need = _lib.lib.mpcdl_blob_floats(C.byref(a.model))
-    if need == 0:
-        _lib.check(-2)
-    if wblob.numel() != need:
-        raise RuntimeError(f"mpcdl: wblob has {wblob.numel()} floats, model needs {need}")
+    a.precision = int(precision)
+    if a.precision != 0:
+        need = _lib.lib.mpcdl_blob_floats_tc(C.byref(a.model))
+        if need == 0:
+            _lib.check(-2)
+        if wblob_tc is None or wblob_tc.numel() != need:
+            raise RuntimeError(f"mpcdl: tensor-core precision needs wblob_tc with {need} floats (pack_rnn(..., tensor_core=True))")
+        a.wblob_tc = _f32c(wblob_tc, "wblob_tc", dev)
+    else:
+        need = _lib.lib.mpcdl_blob_floats(C.byref(a.model))
+        if need == 0:
+            _lib.check(-2)
+        if wblob.numel() != need:
+            raise RuntimeError(f"mpcdl: wblob has {wblob.numel()} floats, model needs {need}")
+        a.wblob = _f32c(wblob, "wblob", dev)
     a.stateful = int(bool(stateful) and kind != _lib.MLP)
-    a.wblob = _f32c(wblob, "wblob", dev)
     a.norm = _f32c(norm, "norm", dev)
     a.init = _f32c(init, "init", dev)
     a.U = _f32c(U, "U", dev)
@@ -105,9 +115,10 @@ def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, state
 
 def _make(kind):
     def impl(wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob, noise_cfg, eps, seed,
-             traj_offset, cost_ref, cost_w, return_states, return_costs, tune):
+             traj_offset, cost_ref, cost_w, return_states, return_costs, tune, precision, wblob_tc):
         return _rollout_impl(kind, wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob,
-                             noise_cfg, eps, seed, traj_offset, cost_ref, cost_w, return_states, return_costs, tune)
+                             noise_cfg, eps, seed, traj_offset, cost_ref, cost_w, return_states, return_costs, tune,
+                             precision, wblob_tc)
     return impl
 
 
@@ -119,13 +130,14 @@ _libimpl.impl("rollout_lstm", _make(_lib.LSTM))
 OPS = {_lib.MLP: torch.ops.mpcdl.rollout_mlp, _lib.GRU: torch.ops.mpcdl.rollout_gru, _lib.LSTM: torch.ops.mpcdl.rollout_lstm}
 
 
-def plan(kind, hidden, layers, window, N, H, stateful=False, noise_cfg=None, tune=()):
+def plan(kind, hidden, layers, window, N, H, stateful=False, noise_cfg=None, tune=(), precision=0):
     """Launch plan the library would use (works without a GPU): tile size, grid, smem, ring mode."""
     a = _lib.RolloutArgs()
     a.model = _lib.ModelDesc(kind, hidden, layers, window if kind != _lib.MLP else 0)
     a.stateful = int(stateful)
-    for f in ("wblob", "norm", "init", "U", "states"):
+    for f in ("wblob", "wblob_tc", "norm", "init", "U", "states"):
         setattr(a, f, 16)           # never dereferenced by the planner
+    a.precision = _lib.PRECISION[precision] if isinstance(precision, str) else int(precision)
     if stateful:
         a.carry = 16
     if noise_cfg is not None:

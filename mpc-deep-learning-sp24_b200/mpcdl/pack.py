@@ -52,7 +52,9 @@ def pack_mlp(sd, hidden: int, layers: int) -> torch.Tensor:
     return torch.from_numpy(blob)
 
 
-def pack_rnn(sd, kind: int, hidden: int, layers: int, window: int) -> torch.Tensor:
+def pack_rnn(sd, kind: int, hidden: int, layers: int, window: int, tensor_core: bool = False) -> torch.Tensor:
+    """GRU_Model / LSTM_Model state_dict -> blob of the FP32 kernels, or (tensor_core=True) the tf32 hi/lo
+    UMMA-layout blob of the tcgen05 kernel (mpcdl_pack_rnn_tc)."""
     pre = "gru" if kind == _lib.GRU else "lstm"
     G = 3 if kind == _lib.GRU else 4
     w_ih = [_np(sd[f"{pre}.weight_ih_l{l}"]) for l in range(layers)]
@@ -64,6 +66,14 @@ def pack_rnn(sd, kind: int, hidden: int, layers: int, window: int) -> torch.Tens
             raise RuntimeError(f"mpcdl: layer {l} weight shapes {w_ih[l].shape}/{w_hh[l].shape} do not match hidden={hidden}")
     fc_w, fc_b = _np(sd["full_c.weight"]), _np(sd["full_c.bias"])
     desc = _lib.ModelDesc(kind, hidden, layers, window)
+    if tensor_core:
+        n = _lib.lib.mpcdl_blob_floats_tc(C.byref(desc))
+        if n == 0:
+            _lib.check(-2)
+        blob = np.empty(n, dtype=np.float32)
+        _lib.check(_lib.lib.mpcdl_pack_rnn_tc(C.byref(desc), _ptrs(w_ih), _ptrs(w_hh), _ptrs(b_ih), _ptrs(b_hh),
+                                              fc_w.ctypes.data_as(_FP), fc_b.ctypes.data_as(_FP), blob.ctypes.data_as(_FP)))
+        return torch.from_numpy(blob)
     blob = _blob(desc)
     _lib.check(_lib.lib.mpcdl_pack_rnn(C.byref(desc), _ptrs(w_ih), _ptrs(w_hh), _ptrs(b_ih), _ptrs(b_hh),
                                        fc_w.ctypes.data_as(_FP), fc_b.ctypes.data_as(_FP), blob.ctypes.data_as(_FP)))
