@@ -406,7 +406,9 @@ int mpcdl_pack_rnn_tc(const mpcdl_model_desc* desc, const float* const* w_ih, co
             const int K = p.K, N = p.N, kc = p.kc;
             for (int n = 0; n < N; ++n)
                 for (int k = 0; k < K; ++k) {
-                    const float w = W[(size_t)n * K + k];
+                    // GRU weight_ih rows are packed [n; r; z] (D columns [nx | r | z | nh], rollout_rnn_tc.cu issue_chunk)
+                    const int src = (desc->kind == MPCDL_GRU && part == 0) ? ((n / h + 2) % 3) * h + n % h : n;
+                    const float w = W[(size_t)src * K + k];
                     const float hi = tf32_rna_host(w), lo = tf32_rna_host(w - hi);
                     const int c = k / kc, kk = k % kc;
                     const size_t e = (size_t)(kk / 4) * (N / 8) * 32 + (size_t)(n / 8) * 32 + (n % 8) * 4 + (kk % 4);

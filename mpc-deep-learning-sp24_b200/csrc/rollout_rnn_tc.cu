@@ -33,9 +33,14 @@ __device__ __forceinline__ float tanh_fast(float x) {
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
-template <bool FAST> __device__ __forceinline__ float act_tanh(float x) { return FAST ? tanh_fast(x) : tanh_f(x); }
-template <bool FAST> __device__ __forceinline__ float act_sigmoid(float x) {
-    return FAST ? fmaf(tanh_fast(0.5f * x), 0.5f, 0.5f) : sigmoid_f(x);
+// activations on PRE-SCALED arguments (the scale is folded into the bias FMA of the epilogue):
+//   accurate: t = -log2e x -> sigmoid = 1/(1 + 2^t);  t = 2 log2e x -> tanh = 1 - 2/(1 + 2^t)   (abs err ~1e-7)
+//   FAST    : t = x/2 -> sigmoid = 0.5 tanh(t) + 0.5; t = x -> MUFU.TANH                        (abs err ~5e-4)
+template <bool FAST> __device__ __forceinline__ float act_sig_scaled(float t) {
+    return FAST ? fmaf(tanh_fast(t), 0.5f, 0.5f) : rcp_approx(1.0f + ex2_approx(t));
+}
+template <bool FAST> __device__ __forceinline__ float act_tanh_scaled(float t) {
+    return FAST ? tanh_fast(t) : fmaf(-2.0f, rcp_approx(1.0f + ex2_approx(t)), 1.0f);
 }
 
 // registers -> A operand columns [col, col+16) of this thread's TMEM lane, as tf32 hi (and lo)
@@ -63,13 +68,15 @@ __device__ __forceinline__ void stage8(uint32_t t_hi, uint32_t t_lo, const float
 }
 
 // ------------------------------------------------------------------ control thread: ring + MMA issue
+// All ring bookkeeping is incremental (slot / parity counters that wrap): the control thread is ONE scalar
+// thread, and a 32-bit division per chunk costs more than the chunk's MMAs.
 struct TcCtl {
     const TcModel& m;
     float* ring;
     uint64_t *full, *empty;
-    uint32_t ld_issued = 0, rel_issued = 0;
-    // load iterator
-    int li_it = 0, li_t = 0, li_l = 0, li_f = 0, li_part = 0, li_c = 0;
+    uint32_t ld_count = 0, outstanding = 0;             // loads issued; loads issued and not yet released
+    uint32_t ld_slot = 0, ld_par = 0, ld_wrapped = 0;   // next load's slot, parity of its empty barrier
+    int li_it = 0, li_t = 0, li_l = 0, li_f = 0, li_part = 0, li_c = 0;   // load iterator
     bool li_done;
     int my_tiles, H;
 
@@ -98,33 +105,54 @@ struct TcCtl {
         if (++li_it < my_tiles) return;
         li_done = true;
     }
-    // Issue ring loads while slots are free.  `need` = load index the caller is about to wait for (that one
-    // is waited for; loads beyond it are only issued when their slot is already free, so MMA issue never
-    // stalls behind a slot whose MMAs are still in flight).
+    // Issue ring loads while slots are free.  Loads up to index `need` are waited for; loads beyond it are only
+    // issued when their slot is already free, so MMA issue never stalls behind MMAs that are still in flight.
     __device__ void top_up(uint32_t need) {
-        while (!li_done && ld_issued - rel_issued < (uint32_t)m.nslots) {
-            const uint32_t slot = ld_issued % m.nslots;
-            if (ld_issued >= (uint32_t)m.nslots) {
-                const uint32_t par = ((ld_issued / m.nslots) - 1u) & 1u;
-                if (need != 0xFFFFFFFFu && ld_issued <= need) mbar_wait(&empty[slot], par);
-                else if (!mbar_try_wait(&empty[slot], par)) break;
+        while (!li_done && outstanding < (uint32_t)m.nslots) {
+            if (ld_wrapped) {
+                if (need != 0xFFFFFFFFu && ld_count <= need) mbar_wait(&empty[ld_slot], ld_par);
+                else if (!mbar_try_wait(&empty[ld_slot], ld_par)) break;
             }
             const TcPart& p = m.parts[2 * li_l + li_part];
             const uint32_t bytes = (m.prec == PREC_TF32X3 ? p.chunk_floats : p.chunk_floats / 2) * 4u;
-            mbar_expect_tx(&full[slot], bytes);
-            bulk_g2s(ring + (size_t)slot * m.slot_floats, m.blob + p.off + (size_t)li_c * p.chunk_floats, bytes, &full[slot]);
-            ++ld_issued;
+            mbar_expect_tx(&full[ld_slot], bytes);
+            bulk_g2s(ring + ld_slot * m.slot_floats, m.blob + p.off + li_c * p.chunk_floats, bytes, &full[ld_slot]);
+            ++ld_count;
+            ++outstanding;
+            if (++ld_slot == (uint32_t)m.nslots) { ld_slot = 0; ld_par ^= ld_wrapped; ld_wrapped = 1; }
             li_advance();
         }
     }
 };
+
+// All MMAs of one weight chunk (KC rows of K, both operands' hi/lo parts): D[:, DCOL..DCOL+N) (+)= A . W^T.
+//   GRU D columns: [nx | r | z | nh]; weight_ih rows are packed [n; r; z] -> DCOL 0, weight_hh rows [r; z; n]
+//   -> DCOL 64, so each part is ONE N = 192 instruction per k-step (nh is zeroed by the epilogue after it
+//   is read, which lets the recurrent part always accumulate).  LSTM: [i | f | g | o], N = 256, DCOL 0.
+// Pass order lo.hi, hi.lo, hi.hi: the small terms are summed first.
+template <int CELL, bool X3, int PART, int KC>
+__device__ __forceinline__ void issue_chunk(uint32_t tbase, uint32_t sb, uint32_t a_hi, uint32_t a_lo, uint32_t& acc) {
+    constexpr int N = (CELL == CELL_GRU ? 3 : 4) * 64;
+    constexpr uint32_t LBO = N / 8 * 128, BLK = KC / 4 * LBO;
+    constexpr uint32_t DCOL = (CELL == CELL_GRU && PART == 1) ? 64 : 0;
+    constexpr uint32_t IDESC = umma::idesc_tf32(128, N);
+    const uint64_t d0 = umma::smem_desc_kmajor(sb, LBO, 128u);
+#pragma unroll
+    for (int pass = X3 ? 0 : 2; pass < 3; ++pass) {
+#pragma unroll
+        for (int kk = 0; kk < KC / 8; ++kk) {
+            const uint64_t bd = d0 + (((pass == 1 ? BLK : 0u) + kk * 2u * LBO) >> 4);
+            umma::mma_tf32_ts(tbase + TC_D + DCOL, (pass == 0 ? a_lo : a_hi) + kk * 8, bd, IDESC, acc);
+            acc = 1;
+        }
+    }
+}
 
 template <int CELL, int PREC>
 __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __grid_constant__ TcRolloutParams p) {
     constexpr bool X3 = PREC == PREC_TF32X3;
     constexpr bool FAST = PREC == PREC_TF32;
     constexpr int T = TC_T, HID = TC_HID, TN = TC_TN;
-    constexpr int NG = CELL == CELL_GRU ? 3 : 4;
     extern __shared__ __align__(1024) float sm[];
     const TcModel& m = p.m;
     const TcSmem L = tc_layout(m.nslots, m.slot_floats, m.layers, T, p.nz);
@@ -146,8 +174,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
         mbar_fence_init();
     }
     if (warp == 8) { umma::tmem_alloc(tmem_slot, 512); umma::tmem_relinquish(); }
-    // tile-invariant constants -> shared memory
-    for (int i = tid; i < NL * HID * 4; i += blockDim.x) sm[L.bias + i] = m.blob[m.bias_off + i];
+    // tile-invariant constants -> shared memory.  Gate biases are pre-scaled for the exp2-based activations:
+    //   sigmoid(g + b) = 1 / (1 + 2^(-log2e g - log2e b)),  tanh(g + b) = 1 - 2 / (1 + 2^(2 log2e g + 2 log2e b));
+    //   the MUFU.TANH mode (TF32) uses sigmoid(x) = 0.5 tanh(0.5 x) + 0.5 -> 0.5 b for sigmoid gates, b for tanh gates.
+    for (int i = tid; i < NL * HID * 4; i += blockDim.x) {
+        const int g = i & 3;
+        const bool tanh_gate = CELL == CELL_GRU ? g >= 2 : g == 2;
+        const float sc = FAST ? (tanh_gate ? 1.0f : 0.5f) : (tanh_gate ? 2.8853900817779268f : -1.4426950408889634f);
+        sm[L.bias + i] = m.blob[m.bias_off + i] * sc;
+    }
     for (int i = tid; i < HID * 8 + 8; i += blockDim.x) sm[L.fc + i] = m.blob[m.fc_off + i];
     for (int i = tid; i < 2 * T * 8 + 12; i += blockDim.x) sm[L.norm + i] = p.io.norm[i];
     if (p.nz.enabled)
@@ -163,57 +198,45 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == 8 && lane == 0) {
             TcCtl c(m, sm + L.ring, full, empty, my_tiles, H);
-            uint32_t use_ctr = 0, layer_base = 0, cellpar = 0;
+            uint32_t use_count = 0, cellpar = 0;
+            uint32_t us = 0, up = 0;                         // slot / full-barrier parity of the next chunk to use
             const uint32_t ring_s = smem_u32(sm + L.ring);
+            const uint32_t slot_bytes = m.slot_floats * 4u;
+            const uint32_t nslots = m.nslots;
+            const bool resident = m.resident != 0;
             for (int it = 0; it < my_tiles; ++it)
                 for (int t = 0; t < H; ++t)
                     for (int l = 0; l < NL; ++l) {
                         const int nkx = m.parts[2 * l].nchunks, nkh = m.parts[2 * l + 1].nchunks;
+                        const uint32_t layer_s = us, layer_p = up, layer_count = use_count;
                         for (int f = 0; f < T; ++f) {
+                            if (resident) { us = layer_s; up = layer_p; use_count = layer_count; }
                             c.top_up(0xFFFFFFFFu);
                             mbar_wait(opnd_ready, cellpar);
                             cellpar ^= 1u;
                             umma::fence_after_sync();
-                            uint32_t acc_main = 0, acc_nh = 0;
-                            const int nparts = c.part_used(f, 1) ? 2 : 1;
-                            for (int part = 0; part < nparts; ++part) {
-                                const TcPart& pt = m.parts[2 * l + part];
-                                const uint32_t lbo = (pt.N / 8) * 128u;
-                                const uint32_t blk_bytes = (pt.kc / 4) * lbo;
-                                const uint32_t a_hi = tbase + (part ? TC_AH_HI : TC_AX_HI), a_lo = tbase + (part ? TC_AH_LO : TC_AX_LO);
-                                for (int ch = 0; ch < pt.nchunks; ++ch) {
-                                    const uint32_t ld = m.resident ? layer_base + (part ? nkx : 0) + ch : use_ctr++;
-                                    c.top_up(ld);
-                                    const uint32_t slot = ld % m.nslots;
-                                    mbar_wait(&full[slot], (ld / m.nslots) & 1u);
-                                    umma::fence_after_sync();
-                                    const uint32_t sb = ring_s + slot * m.slot_floats * 4u;
-#pragma unroll
-                                    for (int pass = X3 ? 0 : 2; pass < 3; ++pass) {
-                                        const uint32_t a_col = (pass == 0 ? a_lo : a_hi) + ch * pt.kc;
-                                        const uint32_t b0 = sb + (pass == 1 ? blk_bytes : 0u);
-                                        for (int kk = 0; kk < pt.kc / 8; ++kk) {
-                                            const uint32_t bk = b0 + kk * 2u * lbo;
-                                            if (CELL == CELL_GRU && part == 1) {
-                                                umma::mma_tf32_ts(tbase + TC_D, a_col + kk * 8, umma::smem_desc_kmajor(bk, lbo, 128u),
-                                                                  umma::idesc_tf32(128, 128), acc_main);
-                                                umma::mma_tf32_ts(tbase + TC_D + 192, a_col + kk * 8,
-                                                                  umma::smem_desc_kmajor(bk + 16u * 128u, lbo, 128u),
-                                                                  umma::idesc_tf32(128, 64), acc_nh);
-                                                acc_nh = 1;
-                                            } else {
-                                                umma::mma_tf32_ts(tbase + TC_D, a_col + kk * 8, umma::smem_desc_kmajor(bk, lbo, 128u),
-                                                                  umma::idesc_tf32(128, NG * 64), acc_main);
-                                            }
-                                            acc_main = 1;
-                                        }
-                                    }
-                                    if (!m.resident || f == T - 1) { umma::mma_commit(&empty[slot]); ++c.rel_issued; }
+                            uint32_t acc = 0;
+                            const bool release = !resident || f == T - 1;
+                            const int nch = nkx + (c.part_used(f, 1) ? nkh : 0);
+                            for (int ch = 0; ch < nch; ++ch) {
+                                c.top_up(use_count);
+                                mbar_wait(&full[us], up);
+                                umma::fence_after_sync();
+                                const uint32_t sb = ring_s + us * slot_bytes;
+                                if (ch < nkx) {              // input part: weight_ih_l{l} . x_f
+                                    if (l == 0) issue_chunk<CELL, X3, 0, 8>(tbase, sb, tbase + TC_AX_HI, tbase + TC_AX_LO, acc);
+                                    else issue_chunk<CELL, X3, 0, TC_KS>(tbase, sb, tbase + TC_AX_HI + ch * TC_KS, tbase + TC_AX_LO + ch * TC_KS, acc);
+                                } else {                     // recurrent part: weight_hh_l{l} . h_{f-1} (always accumulates)
+                                    uint32_t acc_h = 1;
+                                    const int k0 = (ch - nkx) * TC_KS;
+                                    issue_chunk<CELL, X3, 1, TC_KS>(tbase, sb, tbase + TC_AH_HI + k0, tbase + TC_AH_LO + k0, acc_h);
                                 }
+                                if (release) { umma::mma_commit(&empty[us]); --c.outstanding; }
+                                ++use_count;
+                                if (++us == nslots) { us = 0; up ^= 1u; }
                             }
                             umma::mma_commit(acc_ready);
                         }
-                        if (m.resident) layer_base += nkx + ((T > 1 || stateful) ? nkh : 0);
                     }
         }
         __syncwarp();

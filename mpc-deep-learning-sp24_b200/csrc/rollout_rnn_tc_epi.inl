@@ -1,5 +1,9 @@
 // Epilogue warps of rollout_rnn_tc_kernel (included inside the kernel body; warps 0..7).
 // Thread <-> data: TMEM lane / trajectory row = 32*(warp%4) + lane; hidden units [32*uh, 32*uh+32), uh = warp/4.
+// The layer's sequence lives in registers as seq[T][32] and is ROTATED by one frame after every cell, so the
+// frame loop is a real loop (4x less code than unrolling it): at cell (l, f)
+//   seq[0] = layer l-1 output of frame f (consumed as x, then overwritten by this cell's output)
+//   seq[T-1] = layer l output of frame f-1 (the recurrent input, f > 0)
 {
     const int q = warp & 3, uh = warp >> 2;
     const int row = q * 32 + lane;
@@ -17,6 +21,16 @@
     const float4* const biasS = reinterpret_cast<const float4*>(sm + L.bias);
     const float* const fcS = sm + L.fc;
     uint32_t cellpar = 0;
+    constexpr float C_SIG = FAST ? 0.5f : -1.4426950408889634f;       // pre-activation scale of sigmoid gates
+    constexpr float C_TANH = FAST ? 1.0f : 2.8853900817779268f;       // ... of tanh gates (biases pre-scaled alike)
+
+    if (CELL == CELL_GRU) {                            // nh accumulates onto zero (see issue_chunk)
+        uint32_t zr[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) zr[i] = 0u;
+        umma::tmem_st16(tlane + TC_D + 192 + u0, zr);
+        umma::tmem_st16(tlane + TC_D + 192 + u0 + 16, zr);
+    }
 
     for (int tile = blockIdx.x; tile < p.io.ntiles; tile += gridDim.x) {
         long long n = (long long)tile * TN + row;
@@ -34,7 +48,11 @@
             }
         }
         int base = 0;                                  // physical slot of logical frame 0
-        float seq[T][32];                              // current layer's output sequence, this thread's 32 units
+        float seq[T][32];
+#pragma unroll
+        for (int f = 0; f < T; ++f)
+#pragma unroll
+            for (int j = 0; j < 32; ++j) seq[f][j] = 0.f;
         for (int t = 0; t < H; ++t) {
             float u[2] = {0.f, 0.f};
             if (owner) {
@@ -53,8 +71,8 @@
                 float cst[32];                         // LSTM cell state (register resident across the frames)
 #pragma unroll
                 for (int j = 0; j < 32; ++j) cst[j] = 0.f;
-                const float* carry_h = nullptr;
-                float* carry_c = nullptr;
+                const float* carry_h = p.io.carry;
+                float* carry_c = p.io.carry;
                 if (stateful) {
                     carry_h = p.io.carry + ((long long)l * N + n) * HID + u0;
                     if (CELL == CELL_LSTM) {
@@ -66,7 +84,7 @@
                         }
                     }
                 }
-#pragma unroll
+#pragma unroll 1
                 for (int f = 0; f < T; ++f) {
                     const bool has_h = f > 0 || stateful;
                     // ---- publish the A operands of cell (l, f)
@@ -80,24 +98,22 @@
                             stage8<X3>(tlane + TC_AX_HI, tlane + TC_AX_LO, xn);
                         }
                     } else {
-                        stage16<X3>(tlane + TC_AX_HI + u0, tlane + TC_AX_LO + u0, &seq[f][0]);
-                        stage16<X3>(tlane + TC_AX_HI + u0 + 16, tlane + TC_AX_LO + u0 + 16, &seq[f][16]);
+                        stage16<X3>(tlane + TC_AX_HI + u0, tlane + TC_AX_LO + u0, &seq[0][0]);
+                        stage16<X3>(tlane + TC_AX_HI + u0 + 16, tlane + TC_AX_LO + u0 + 16, &seq[0][16]);
                     }
-                    if (has_h) {
-                        if (f > 0) {
-                            stage16<X3>(tlane + TC_AH_HI + u0, tlane + TC_AH_LO + u0, &seq[f > 0 ? f - 1 : 0][0]);
-                            stage16<X3>(tlane + TC_AH_HI + u0 + 16, tlane + TC_AH_LO + u0 + 16, &seq[f > 0 ? f - 1 : 0][16]);
-                        } else {
-                            float hv[16];
+                    if (f > 0) {
+                        stage16<X3>(tlane + TC_AH_HI + u0, tlane + TC_AH_LO + u0, &seq[T - 1][0]);
+                        stage16<X3>(tlane + TC_AH_HI + u0 + 16, tlane + TC_AH_LO + u0 + 16, &seq[T - 1][16]);
+                    } else if (stateful) {
+                        float hv[16];
 #pragma unroll
-                            for (int hb = 0; hb < 2; ++hb) {
+                        for (int hb = 0; hb < 2; ++hb) {
 #pragma unroll
-                                for (int j = 0; j < 16; j += 4) {
-                                    float4 v = *reinterpret_cast<const float4*>(carry_h + hb * 16 + j);
-                                    hv[j] = v.x; hv[j + 1] = v.y; hv[j + 2] = v.z; hv[j + 3] = v.w;
-                                }
-                                stage16<X3>(tlane + TC_AH_HI + u0 + hb * 16, tlane + TC_AH_LO + u0 + hb * 16, hv);
+                            for (int j = 0; j < 16; j += 4) {
+                                float4 v = *reinterpret_cast<const float4*>(carry_h + hb * 16 + j);
+                                hv[j] = v.x; hv[j + 1] = v.y; hv[j + 2] = v.z; hv[j + 3] = v.w;
                             }
+                            stage16<X3>(tlane + TC_AH_HI + u0 + hb * 16, tlane + TC_AH_LO + u0 + hb * 16, hv);
                         }
                     }
                     umma::wait_st();
@@ -114,11 +130,15 @@
                         umma::tmem_ld8(c0, g0);
                         umma::tmem_ld8(c0 + 64, g1);
                         umma::tmem_ld8(c0 + 128, g2);
-                        if (CELL == CELL_LSTM || has_h) umma::tmem_ld8(c0 + 192, g3);
+                        umma::tmem_ld8(c0 + 192, g3);
                         umma::wait_ld();
+                        if (CELL == CELL_GRU) {        // nh: re-zero for the next cell's accumulate-only recurrent part
+                            const uint32_t zr[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+                            umma::tmem_st8(c0 + 192, zr);
+                        }
                         if (f > 0) {
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) hold[i] = seq[f > 0 ? f - 1 : 0][ub * 8 + i];
+                            for (int i = 0; i < 8; ++i) hold[i] = seq[T - 1][ub * 8 + i];
                         } else if (stateful) {
                             float4 v0 = *reinterpret_cast<const float4*>(carry_h + ub * 8), v1 = *reinterpret_cast<const float4*>(carry_h + ub * 8 + 4);
                             hold[0] = v0.x; hold[1] = v0.y; hold[2] = v0.z; hold[3] = v0.w;
@@ -130,23 +150,23 @@
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             const int j = ub * 8 + i;
-                            const float4 b = biasS[l * HID + u0 + j];
+                            const float4 b = biasS[l * HID + u0 + j];          // pre-scaled (kernel prologue)
                             if (CELL == CELL_GRU) {
-                                // torch GRU cell: n = tanh(i_n + b_in + r*(h_n + b_hn)); h' = (h - n)*z + n
-                                const float rg = act_sigmoid<FAST>(g0[i] + b.x);
-                                const float zg = act_sigmoid<FAST>(g1[i] + b.y);
-                                const float hn = has_h ? g3[i] + b.w : b.w;
-                                const float ng = act_tanh<FAST>(fmaf(rg, hn, g2[i] + b.z));
-                                seq[f][j] = fmaf(hold[i] - ng, zg, ng);
+                                // D columns [nx | r | z | nh]; torch GRU cell: n = tanh(i_n + b_in + r*(h_n + b_hn)); h' = (h - n)*z + n
+                                const float rg = act_sig_scaled<FAST>(fmaf(g1[i], C_SIG, b.x));
+                                const float zg = act_sig_scaled<FAST>(fmaf(g2[i], C_SIG, b.y));
+                                const float a = fmaf(g0[i], C_TANH, b.z), d = fmaf(g3[i], C_TANH, b.w);
+                                const float ng = act_tanh_scaled<FAST>(fmaf(rg, d, a));
+                                seq[0][j] = fmaf(hold[i] - ng, zg, ng);
                             } else {
-                                // torch LSTM cell: c' = f*c + i*g; h' = o*tanh(c')
-                                const float ig = act_sigmoid<FAST>(g0[i] + b.x);
-                                const float fg = act_sigmoid<FAST>(g1[i] + b.y);
-                                const float gg = act_tanh<FAST>(g2[i] + b.z);
-                                const float og = act_sigmoid<FAST>(g3[i] + b.w);
+                                // D columns [i | f | g | o]; torch LSTM cell: c' = f*c + i*g; h' = o*tanh(c')
+                                const float ig = act_sig_scaled<FAST>(fmaf(g0[i], C_SIG, b.x));
+                                const float fg = act_sig_scaled<FAST>(fmaf(g1[i], C_SIG, b.y));
+                                const float gg = act_tanh_scaled<FAST>(fmaf(g2[i], C_TANH, b.z));
+                                const float og = act_sig_scaled<FAST>(fmaf(g3[i], C_SIG, b.w));
                                 const float cn = fmaf(fg, cst[j], ig * gg);
                                 cst[j] = cn;
-                                seq[f][j] = og * act_tanh<FAST>(cn);
+                                seq[0][j] = og * act_tanh_scaled<FAST>(cn * C_TANH);
                             }
                         }
                     }
@@ -155,14 +175,22 @@
                         float* ch = p.io.carry + ((long long)l * N + n) * HID + u0;
 #pragma unroll
                         for (int j = 0; j < 32; j += 4) {
-                            *reinterpret_cast<float4*>(ch + j) = make_float4(seq[f][j], seq[f][j + 1], seq[f][j + 2], seq[f][j + 3]);
+                            *reinterpret_cast<float4*>(ch + j) = make_float4(seq[0][j], seq[0][j + 1], seq[0][j + 2], seq[0][j + 3]);
                             if (CELL == CELL_LSTM)
                                 *reinterpret_cast<float4*>(carry_c + j) = make_float4(cst[j], cst[j + 1], cst[j + 2], cst[j + 3]);
                         }
                     }
+                    // ---- rotate: this cell's output becomes seq[T-1], the next frame's input becomes seq[0]
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float o = seq[0][j];
+#pragma unroll
+                        for (int k = 0; k + 1 < T; ++k) seq[k][j] = seq[k + 1][j];
+                        seq[T - 1][j] = o;
+                    }
                 }
             }
-            // ---- head: full_c(out[:, -1, :]) partial sums over this thread's 32 units
+            // ---- head: full_c(out[:, -1, :]) partial sums over this thread's 32 units (last frame = seq[T-1])
             {
                 float y[8];
 #pragma unroll
