@@ -157,26 +157,39 @@ float tf32_rna_host(float x) {          // cvt.rna.tf32.f32: round to nearest, t
     return r;
 }
 
-struct TcPlan { int nslots, slot_floats, resident, smem_bytes, ntiles, grid; };
+struct TcPlan { int nslots, slot_floats, resident, group, smem_bytes, ntiles, grid; };
 
+// Ring geometry: a slot holds `group` 16-row chunks of one weight matrix (one TMA + one MMA-issue unit).
+// Big groups keep the single control thread off the critical path; residency (a layer's two matrices stay
+// in shared memory for all T frames) divides the L2 -> SM weight traffic by T.
 int make_tc_plan(const mpcdl_rollout_args& a, TcPlan& pl, int num_sms) {
     const mpcdl_model_desc& d = a.model;
     TcPart parts[2 * MAX_LAYERS];
     uint32_t bo, fo;
     build_tc_parts(d, parts, bo, fo);
-    uint32_t chunk_max = 0;
-    for (int i = 0; i < 2 * d.layers; ++i) chunk_max = std::max(chunk_max, parts[i].chunk_floats);
-    pl.slot_floats = (int)(a.precision == MPCDL_PREC_TF32X3 ? chunk_max : chunk_max / 2);
+    const bool x3 = a.precision == MPCDL_PREC_TF32X3;
+    const uint32_t chunk = parts[1].chunk_floats / (x3 ? 1 : 2);        // floats per 16-row chunk in the ring (hi+lo | hi)
+    const int per_part = TC_HID / TC_KS;
     NoiseParams nz;
     fill_noise(nz, a);
-    const int fixed = tc_layout(0, 0, d.layers, TC_T, nz).total * 4;
-    int nslots = (SMEM_LIMIT - fixed) / (pl.slot_floats * 4);
-    nslots = std::min(nslots, TC_MAX_SLOTS);
-    if (a.tune_nslots > 0) nslots = std::min(nslots, a.tune_nslots);
-    if (nslots < 2) return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core rollout: shared memory holds only %d weight slots (noise net too large?)", nslots);
-    const int per_layer = d.layers > 1 ? 2 * (TC_HID / TC_KS) : 1 + TC_HID / TC_KS;
-    pl.resident = (nslots >= per_layer && a.tune_kc >= 0) ? 1 : 0;
-    pl.nslots = nslots;
+    const int budget = SMEM_LIMIT - tc_layout(0, 0, d.layers, TC_T, nz).total * 4;
+    const int pref_x3[3] = {2, 4, 1}, pref_1[3] = {4, 2, 1};
+    const int* pref = x3 ? pref_x3 : pref_1;
+    int G = 0, nslots = 0, resident = 0;
+    if (a.tune_kc >= 0)
+        for (int i = 0; i < 3 && !G; ++i) {                             // resident, preferred group size first
+            const int g = a.tune_ntg > 0 ? a.tune_ntg : pref[i], ns = std::min<int>(budget / (int)(g * chunk * 4), TC_MAX_SLOTS);
+            if (ns >= 2 * per_part / g) { G = g; nslots = ns; resident = 1; }
+        }
+    for (int g = 4; g >= 1 && !G; g >>= 1) {                            // streaming: largest group with >= 3 slots
+        if (a.tune_ntg > 0 && g != a.tune_ntg) continue;
+        const int ns = std::min<int>(budget / (int)(g * chunk * 4), TC_MAX_SLOTS);
+        if (ns >= 3 || (g == 1 && ns >= 2)) { G = g; nslots = ns; }
+    }
+    if (!G) return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core rollout: shared memory cannot hold the weight ring (noise net too large?)");
+    if (a.tune_nslots > 0 && a.tune_nslots < nslots) { nslots = a.tune_nslots; if (nslots < 2 * per_part / G) resident = 0; }
+    pl.group = G; pl.nslots = nslots; pl.resident = resident;
+    pl.slot_floats = (int)(G * chunk);
     pl.smem_bytes = std::max(tc_layout(nslots, pl.slot_floats, d.layers, TC_T, nz).total * 4, 120 * 1024);   // > half an SM: one CTA (one TMEM owner) per SM
     pl.ntiles = (int)((a.N + TC_TN - 1) / TC_TN);
     pl.grid = std::min(pl.ntiles, num_sms);
@@ -464,7 +477,7 @@ int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
         memset(out, 0, sizeof(*out));
         out->rt = 1; out->rj = 32; out->n_tg = TC_TN; out->tile_traj = TC_TN; out->threads = TC_THREADS; out->grid = tp.grid;
         out->smem_bytes = tp.smem_bytes; out->resident = tp.resident; out->nslots = tp.nslots; out->slot_floats = tp.slot_floats;
-        out->ntiles = tp.ntiles; out->variant = 4; out->ksplit = 1;
+        out->ntiles = tp.ntiles; out->variant = 4; out->ksplit = tp.group;
         return MPCDL_OK;
     }
     Plan pl;
@@ -493,7 +506,7 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
         q.m.blob = a->wblob_tc;
         q.m.cell = a->model.kind == MPCDL_GRU ? 0 : 1;
         q.m.prec = a->precision; q.m.layers = a->model.layers; q.m.window = a->model.window; q.m.stateful = a->stateful != 0;
-        q.m.nslots = tp.nslots; q.m.slot_floats = tp.slot_floats; q.m.resident = tp.resident;
+        q.m.nslots = tp.nslots; q.m.slot_floats = tp.slot_floats; q.m.resident = tp.resident; q.m.group = tp.group;
         fill_noise(q.nz, *a);
         fill_io(q.io, *a, tp.ntiles);
         cudaError_t e = launch_rnn_tc(q, tp.grid, tp.smem_bytes, st);

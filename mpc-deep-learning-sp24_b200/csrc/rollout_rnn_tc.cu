@@ -85,9 +85,10 @@ struct TcCtl {
         li_done = my_tiles_ == 0;
     }
     __device__ bool part_used(int f, int part) const { return part == 0 || f > 0 || m.stateful; }
+    __device__ int ngroups(const TcPart& p) const { return p.nchunks >= m.group ? p.nchunks / m.group : 1; }
     __device__ void li_advance() {
         const TcPart& p = m.parts[2 * li_l + li_part];
-        if (++li_c < p.nchunks) return;
+        if (++li_c < ngroups(p)) return;
         li_c = 0;
         if (m.resident) {                       // per layer visit: x chunks, then h chunks (if ever used)
             if (li_part == 0 && (m.window > 1 || m.stateful)) { li_part = 1; return; }
@@ -114,9 +115,17 @@ struct TcCtl {
                 else if (!mbar_try_wait(&empty[ld_slot], ld_par)) break;
             }
             const TcPart& p = m.parts[2 * li_l + li_part];
-            const uint32_t bytes = (m.prec == PREC_TF32X3 ? p.chunk_floats : p.chunk_floats / 2) * 4u;
-            mbar_expect_tx(&full[ld_slot], bytes);
-            bulk_g2s(ring + ld_slot * m.slot_floats, m.blob + p.off + li_c * p.chunk_floats, bytes, &full[ld_slot]);
+            const uint32_t g = p.nchunks >= m.group ? m.group : 1;          // 16-row chunks in this group
+            const float* src = m.blob + p.off + li_c * g * p.chunk_floats;
+            float* dst = ring + ld_slot * m.slot_floats;
+            if (m.prec == PREC_TF32X3) {                // [hi|lo] x g, contiguous in the blob
+                mbar_expect_tx(&full[ld_slot], g * p.chunk_floats * 4u);
+                bulk_g2s(dst, src, g * p.chunk_floats * 4u, &full[ld_slot]);
+            } else {                                    // hi blocks only, compacted
+                const uint32_t hb = p.chunk_floats / 2;
+                mbar_expect_tx(&full[ld_slot], g * hb * 4u);
+                for (uint32_t i = 0; i < g; ++i) bulk_g2s(dst + i * hb, src + i * p.chunk_floats, hb * 4u, &full[ld_slot]);
+            }
             ++ld_count;
             ++outstanding;
             if (++ld_slot == (uint32_t)m.nslots) { ld_slot = 0; ld_par ^= ld_wrapped; ld_wrapped = 1; }
@@ -125,27 +134,37 @@ struct TcCtl {
     }
 };
 
-// All MMAs of one weight chunk (KC rows of K, both operands' hi/lo parts): D[:, DCOL..DCOL+N) (+)= A . W^T.
+// All MMAs of one ring slot = G weight chunks of KC rows of K (both operands' hi/lo parts): D[:, DCOL..DCOL+N) (+)= A . W^T.
 //   GRU D columns: [nx | r | z | nh]; weight_ih rows are packed [n; r; z] -> DCOL 0, weight_hh rows [r; z; n]
 //   -> DCOL 64, so each part is ONE N = 192 instruction per k-step (nh is zeroed by the epilogue after it
 //   is read, which lets the recurrent part always accumulate).  LSTM: [i | f | g | o], N = 256, DCOL 0.
 // Pass order lo.hi, hi.lo, hi.hi: the small terms are summed first.
-template <int CELL, bool X3, int PART, int KC>
-__device__ __forceinline__ void issue_chunk(uint32_t tbase, uint32_t sb, uint32_t a_hi, uint32_t a_lo, uint32_t& acc) {
+template <int CELL, bool X3, int PART, int KC, int G>
+__device__ __forceinline__ void issue_group(uint32_t tbase, uint32_t sb, uint32_t a_hi, uint32_t a_lo, uint32_t& acc) {
     constexpr int N = (CELL == CELL_GRU ? 3 : 4) * 64;
-    constexpr uint32_t LBO = N / 8 * 128, BLK = KC / 4 * LBO;
+    constexpr uint32_t LBO = N / 8 * 128, BLK = KC / 4 * LBO;          // one hi (or lo) block of KC rows
+    constexpr uint32_t SUB = X3 ? 2 * BLK : BLK;                       // bytes per 16-row chunk inside the slot
     constexpr uint32_t DCOL = (CELL == CELL_GRU && PART == 1) ? 64 : 0;
     constexpr uint32_t IDESC = umma::idesc_tf32(128, N);
     const uint64_t d0 = umma::smem_desc_kmajor(sb, LBO, 128u);
 #pragma unroll
-    for (int pass = X3 ? 0 : 2; pass < 3; ++pass) {
+    for (int s = 0; s < G; ++s) {
 #pragma unroll
-        for (int kk = 0; kk < KC / 8; ++kk) {
-            const uint64_t bd = d0 + (((pass == 1 ? BLK : 0u) + kk * 2u * LBO) >> 4);
-            umma::mma_tf32_ts(tbase + TC_D + DCOL, (pass == 0 ? a_lo : a_hi) + kk * 8, bd, IDESC, acc);
-            acc = 1;
+        for (int pass = X3 ? 0 : 2; pass < 3; ++pass) {
+#pragma unroll
+            for (int kk = 0; kk < KC / 8; ++kk) {
+                const uint64_t bd = d0 + ((s * SUB + (pass == 1 ? BLK : 0u) + kk * 2u * LBO) >> 4);
+                umma::mma_tf32_ts(tbase + TC_D + DCOL, (pass == 0 ? a_lo : a_hi) + s * KC + kk * 8, bd, IDESC, acc);
+                acc = 1;
+            }
         }
     }
+}
+template <int CELL, bool X3, int PART>
+__device__ __forceinline__ void issue_groups(int G, uint32_t tbase, uint32_t sb, uint32_t a_hi, uint32_t a_lo, uint32_t& acc) {
+    if (G == 4) issue_group<CELL, X3, PART, TC_KS, 4>(tbase, sb, a_hi, a_lo, acc);
+    else if (G == 2) issue_group<CELL, X3, PART, TC_KS, 2>(tbase, sb, a_hi, a_lo, acc);
+    else issue_group<CELL, X3, PART, TC_KS, 1>(tbase, sb, a_hi, a_lo, acc);
 }
 
 template <int CELL, int PREC>
@@ -207,7 +226,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
             for (int it = 0; it < my_tiles; ++it)
                 for (int t = 0; t < H; ++t)
                     for (int l = 0; l < NL; ++l) {
-                        const int nkx = m.parts[2 * l].nchunks, nkh = m.parts[2 * l + 1].nchunks;
+                        const int G = m.group, kg = G * TC_KS;
+                        const int nkx = c.ngroups(m.parts[2 * l]), nkh = c.ngroups(m.parts[2 * l + 1]);
                         const uint32_t layer_s = us, layer_p = up, layer_count = use_count;
                         for (int f = 0; f < T; ++f) {
                             if (resident) { us = layer_s; up = layer_p; use_count = layer_count; }
@@ -224,12 +244,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
                                 umma::fence_after_sync();
                                 const uint32_t sb = ring_s + us * slot_bytes;
                                 if (ch < nkx) {              // input part: weight_ih_l{l} . x_f
-                                    if (l == 0) issue_chunk<CELL, X3, 0, 8>(tbase, sb, tbase + TC_AX_HI, tbase + TC_AX_LO, acc);
-                                    else issue_chunk<CELL, X3, 0, TC_KS>(tbase, sb, tbase + TC_AX_HI + ch * TC_KS, tbase + TC_AX_LO + ch * TC_KS, acc);
+                                    if (l == 0) issue_group<CELL, X3, 0, 8, 1>(tbase, sb, tbase + TC_AX_HI, tbase + TC_AX_LO, acc);
+                                    else issue_groups<CELL, X3, 0>(G, tbase, sb, tbase + TC_AX_HI + ch * kg, tbase + TC_AX_LO + ch * kg, acc);
                                 } else {                     // recurrent part: weight_hh_l{l} . h_{f-1} (always accumulates)
                                     uint32_t acc_h = 1;
-                                    const int k0 = (ch - nkx) * TC_KS;
-                                    issue_chunk<CELL, X3, 1, TC_KS>(tbase, sb, tbase + TC_AH_HI + k0, tbase + TC_AH_LO + k0, acc_h);
+                                    const int k0 = (ch - nkx) * kg;
+                                    issue_groups<CELL, X3, 1>(G, tbase, sb, tbase + TC_AH_HI + k0, tbase + TC_AH_LO + k0, acc_h);
                                 }
                                 if (release) { umma::mma_commit(&empty[us]); --c.outstanding; }
                                 ++use_count;

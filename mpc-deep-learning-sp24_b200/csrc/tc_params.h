@@ -33,6 +33,7 @@ struct TcModel {
     TcPart parts[2 * MAX_LAYERS];      // [2l] = weight_ih_l{l}, [2l+1] = weight_hh_l{l}
     int cell, prec, layers, window, stateful;
     int nslots, slot_floats, resident; // ring geometry; resident = a layer's chunks stay for all T frames
+    int group;                         // 16-row weight chunks per ring slot (1, 2 or 4): one TMA/issue unit
 };
 
 struct TcRolloutParams {
