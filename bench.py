@@ -240,7 +240,10 @@ def run_native(args, w):
     init_p, U_p = init_h.pin_memory(), U_h.pin_memory()
     init_d, U_d = init_p.to(dev), U_p.to(dev)
     cost_d = tuple(c.to(dev) for c in cost)
-    kw = dict(noise=noise, seed=1, traj_offset=rank * N, cost=cost_d, return_states=w["states"])
+    prec = args.precision
+    if prec != "fp32" and meta["kind"] == "Basic":
+        raise SystemExit("bench.py: --precision tf32x3|tf32 applies to the GRU/LSTM workloads (tcgen05 path)")
+    kw = dict(noise=noise, seed=1, traj_offset=rank * N, cost=cost_d, return_states=w["states"], precision=prec)
     costs_all = torch.empty(world * N, device=dev) if world > 1 else None
 
     def step(init, U):
@@ -323,7 +326,7 @@ def run_native(args, w):
         value = units / (ms_per_step * 1e-3)
         kind = {"Basic": 0, "GRU": 1, "LSTM": 2}[meta["kind"]]
         plan = ops.plan(kind, meta["hidden"], meta["layers"], meta["window"], N, H, stateful=meta["state_f"],
-                        noise_cfg=noise.cfg() if noise is not None else None)
+                        noise_cfg=noise.cfg() if noise is not None else None, precision=prec)
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -338,16 +341,25 @@ def run_native(args, w):
             traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
         except Exception:
             pass
-        roofline = {"bound": "fp32", "achieved": ach_tf, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach_tf / fp32_peak,
-                    "traffic": traffic,
-                    "peak_source": "FP32 FFMA peak measured live by mpcdl_ffma_peak (MEASURED_PEAKS.json has no FP32 figure; "
-                                   "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)",
+        if prec == "fp32":
+            bound, peak = "fp32", fp32_peak
+            peak_source = ("FP32 FFMA peak measured live by mpcdl_ffma_peak (MEASURED_PEAKS.json has no FP32 figure; "
+                           "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)")
+        else:
+            # TF32 tensor peak = half the measured dense BF16 rate (nominal 1.1 vs 2.25 PFLOP/s); tf32x3 issues 3 MMA
+            # passes per algorithmic FLOP, so its ceiling against this peak is 1/3
+            bound, peak = "tensor", peaks.get("bf16_tflops", 1590.0) / 2
+            peak_source = ("TF32 dense peak taken as MEASURED_PEAKS.json bf16_tflops / 2" if peaks else "fallback 1590 / 2") + \
+                          ("; tf32x3 executes 3 tensor passes per algorithmic FLOP" if prec == "tf32x3" else "")
+        roofline = {"bound": bound, "achieved": ach_tf, "peak": peak, "unit": "TFLOP/s", "frac": ach_tf / peak,
+                    "traffic": traffic, "peak_source": peak_source, "fp32_ffma_peak": fp32_peak,
                     "kernel_ms": k_ms, "flop_per_traj_step": w["flop"],
                     "hbm": {"achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                             "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak,
                             "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": {"fp32": "f32", "tf32x3": "tf32x3 (3-pass TF32 operands, FP32 accumulate/state)", "tf32": "tf32 (FP32 accumulate/state)"}[prec],
                 "data": "synthetic",
                 "config": {"workload": w["desc"], "N_per_gpu": N, "H": H, "l2": "flushed between steps (256 MiB memset outside the event pairs)",
                            "parallelism": f"trajectory shards x{world}, one all-gather of costs per step" if world > 1 else "single GPU",
@@ -374,6 +386,8 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--skip-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32x3", "tf32"],
+                    help="gate-GEMM arithmetic of the GRU/LSTM workloads: fp32 = FFMA kernels (parity path), tf32x3 / tf32 = tcgen05 kernels")
     args = ap.parse_args()
     w = WORKLOADS[args.workload]
     if args.impl == "reference":

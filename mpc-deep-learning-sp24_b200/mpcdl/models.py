@@ -76,7 +76,7 @@ class _RolloutMixin:
 
     @torch.no_grad()
     def rollout(self, init, U, stats=None, *, noise=None, eps=None, seed=0, traj_offset=0, cost=None,
-                return_states=True, stateful=None, carry=None, tune=(), precision="fp32"):
+                return_states=True, stateful=None, carry=None, tune=(), precision=None):
         """Closed-loop rollout of N trajectories over H steps in one kernel launch.
 
         init  s0 [N,6] (MLP) or window [N,T,8] (GRU/LSTM), raw units; U [N,H,2] controls.
@@ -99,6 +99,7 @@ class _RolloutMixin:
         cref, cw = None, []
         if cost is not None:
             cref, cw = self._cost(cost, dev)
+        precision = getattr(self, "precision", "fp32") if precision is None else precision
         if precision not in _lib.PRECISION:
             raise RuntimeError(f"mpcdl: unknown precision {precision!r} (fp32 | tf32x3 | tf32)")
         prec = _lib.PRECISION[precision]
@@ -155,6 +156,7 @@ class _RNNBase(_RolloutMixin, nn.Module):
         self.layers = layers
         self.state_f = state_f
         self.h_state = None
+        self.precision = "fp32"        # default arithmetic of forward()/rollout(): "fp32" | "tf32x3" | "tf32" (tcgen05)
         self._packed = _Packed()
         self._window = None
 

@@ -65,3 +65,24 @@ def test_plans_fit_the_machine():
                 assert p["smem_bytes"] <= 232448 and p["threads"] <= 512 and p["threads"] % 32 == 0
                 assert 1 <= p["grid"] <= 148 and p["ntiles"] * p["tile_traj"] >= n
                 assert p["tile_traj"] == p["rt"] * p["n_tg"]
+
+
+def test_tensor_core_plans_and_errors():
+    """tcgen05 path: planner geometry (one 128-trajectory tile per CTA, ring fits the SM) and the
+    'no silent fallback' rule for unsupported shapes."""
+    from mpcdl import _lib, ops
+    for prec in ("tf32x3", "tf32"):
+        for kind in (1, 2):
+            for st in (False, True):
+                for nz in (None, [3, 32, 2, 2]):
+                    p = ops.plan(kind, 64, 4, 4, 65536, 100, stateful=st, noise_cfg=nz, precision=prec)
+                    assert p["variant"] == 4 and p["tile_traj"] == 128 and p["threads"] == 384
+                    assert 120 * 1024 <= p["smem_bytes"] <= 232448 and p["nslots"] >= 2
+                    assert p["ksplit"] in (1, 2, 4) and p["grid"] == 148 and p["ntiles"] == 512
+                    if p["resident"]:
+                        assert p["nslots"] * p["ksplit"] >= 8          # a layer's two 64-row matrices stay in the ring
+    for args in [(1, 128, 2, 4), (1, 64, 4, 8), (0, 64, 4, 0)]:           # hidden 128 / window 8 / MLP: FP32 kernels only
+        with pytest.raises(RuntimeError):
+            ops.plan(args[0], args[1], args[2], args[3], 100, 5, precision="tf32x3")
+    d = _lib.ModelDesc(_lib.GRU, 32, 2, 4)
+    assert _lib.lib.mpcdl_blob_floats_tc(C.byref(d)) == 0

@@ -131,3 +131,88 @@ def test_t2_full_horizon(name, N, H, gold_stats):
     for a, b in zip(qk, qt):
         assert a <= 2 * b + 1e-6, (qk, qt)
     assert _quantiles(R.rel_err(yk, y32))[1] <= 1e-5
+
+
+# ------------------------------------------------------------------------------ T3: tensor-core precisions
+# Stated bounds of the tcgen05 path, rel err = max_d |dy_d| / max|ref_d| per trajectory-step:
+#   tf32x3  one-step <= 2e-5  (vs the reference modules' FP32 output);  H = 50 vs FP64: p50 <= 4e-5, p90 <= 1e-4, p99 <= 3e-4
+#   tf32    one-step <= 5e-3;                                           H = 50 vs FP64: p50 <= 3e-3, p90 <= 8e-3, p99 <= 3e-2
+TC_BOUNDS = {"tf32x3": (2e-5, (4e-5, 1e-4, 3e-4)), "tf32": (5e-3, (3e-3, 8e-3, 3e-2))}
+
+
+@pytest.mark.parametrize("prec", ["tf32x3", "tf32"])
+@pytest.mark.parametrize("name", RNN)
+def test_t3_tensor_core_onestep(name, prec, bags, gold_onestep):
+    """Module.forward on every validation window through the tcgen05 kernel (stateful: carried h_state)."""
+    import mpcdl
+    ds = mpcdl.RobotData(bags, 4)
+    m, meta = _model(name)
+    m.precision = prec
+    x = ds.featrs.to(_dev())
+    y = m(x)
+    assert _t1(y, gold_onestep[name]) <= TC_BOUNDS[prec][0]
+    if meta["state_f"]:
+        y2 = m(x)
+        assert _t1(y2, gold_onestep[name + "_second"]) <= 2 * TC_BOUNDS[prec][0]
+
+
+@pytest.mark.parametrize("prec", ["tf32x3", "tf32"])
+@pytest.mark.parametrize("name", ["GRU_64_4_4_16_False", "GRU_64_4_4_64_True", "LSTM_64_4_4_16_False", "LSTM_64_4_4_64_True"])
+def test_t3_tensor_core_horizon(name, prec, gold_stats):
+    """Ragged N (300 = 2 tiles + 44), H = 50: error quantiles against the FP64 oracle within the stated bound."""
+    from mpcdl import synth
+    from oracle import rollout_ref as R
+    m, meta = _model(name)
+    st = gold_stats[1]
+    init, U = synth.make_inputs(synth.load_rows(), 300, 50, window=4, seed=3)
+    ref64 = R.as_double(R.build_from_name(name, load_ckpt(name))[0])
+    y64 = R.rollout_rnn(ref64, {k: v.double() for k, v in st.items()}, init.double(), U.double(), stateful=meta["state_f"])[0]
+    out = m.rollout(init.to(_dev()), U.to(_dev()), st, precision=prec)
+    q = _quantiles(R.rel_err(out[0].cpu(), y64))
+    for a, b in zip(q, TC_BOUNDS[prec][1]):
+        assert a <= b, (q, TC_BOUNDS[prec][1])
+    if meta["state_f"]:                       # the returned carry continues the rollout exactly like one long rollout
+        a = m.rollout(init.to(_dev()), U[:, :20].contiguous().to(_dev()), st, precision=prec)
+        win = torch.cat([init.to(_dev()), torch.cat([a[0], U[:, :20].to(_dev())], 2)], 1)[:, -4:].contiguous()
+        b = m.rollout(win, U[:, 20:].contiguous().to(_dev()), st, precision=prec, carry=a[2])
+        assert torch.equal(torch.cat([a[0], b[0]], 1), out[0])
+
+
+@pytest.mark.parametrize("prec", ["tf32x3", "tf32"])
+def test_t3_tensor_core_noise_cost(prec, gold_rollouts, gold_stats):
+    """Residual-noise injection with supplied eps + tracking cost on the tcgen05 path vs the golden rollout
+    made by the reference modules; Philox draws are invariant to sharding (traj_offset)."""
+    import mpcdl
+    from oracle import rollout_ref as R
+    noise = mpcdl.FeedforwardNoiseModel(6, 2, 3, n_layers=2, size=32, activation="tanh", output_activation="identity")
+    noise.model.load_state_dict(load_ckpt("noise_seed0_h3_s32_l2"))
+    noise.to(_dev())
+    g = gold_rollouts
+    cost = tuple(torch.from_numpy(g[k]) for k in ("cost_ref", "cost_qw", "cost_rw"))
+    eps = torch.from_numpy(g["eps"]).to(_dev())
+    name = "GRU_64_4_4_16_False"
+    m, _ = _model(name)
+    win0, Uw = torch.from_numpy(g["win0"]).to(_dev()), torch.from_numpy(g["Uw"]).to(_dev())
+    states, costs = m.rollout(win0, Uw, gold_stats[1], noise=noise, eps=eps, cost=cost, precision=prec)
+    err = R.rel_err(states.cpu(), torch.from_numpy(g[name + "_noise"]))
+    assert err[:, 0].max().item() <= TC_BOUNDS[prec][0]
+    assert _quantiles(err)[1] <= TC_BOUNDS[prec][1][1]
+    cref = torch.from_numpy(g[name + "_noise_cost"])
+    assert ((costs.cpu() - cref).abs() / cref.abs()).max().item() <= (1e-3 if prec == "tf32x3" else 0.2)
+    # cost-only mode returns the same costs; Philox noise keyed by the global trajectory index
+    _, c2 = m.rollout(win0, Uw, gold_stats[1], noise=noise, eps=eps, cost=cost, precision=prec, return_states=False)
+    assert torch.equal(c2, costs)
+    full = m.rollout(win0, Uw, gold_stats[1], noise=noise, seed=7, precision=prec)[0]
+    part = m.rollout(win0[40:].contiguous(), Uw[40:].contiguous(), gold_stats[1], noise=noise, seed=7, traj_offset=40, precision=prec)[0]
+    assert torch.equal(full[40:], part)
+
+
+def test_tensor_core_rejects_unsupported():
+    m, _ = _model("Basic_64_4_32")
+    with pytest.raises(RuntimeError):
+        m.rollout(torch.zeros(8, 6, device=_dev()), torch.zeros(8, 3, 2, device=_dev()), None, precision="tf32x3")
+    g, _ = _model("GRU_64_4_4_16_False")
+    with pytest.raises(RuntimeError):           # window 3: the tcgen05 kernel is built for FT_SIZE = 4 only
+        g.rollout(torch.zeros(8, 3, 8, device=_dev()), torch.zeros(8, 3, 2, device=_dev()), None, precision="tf32")
+    with pytest.raises(RuntimeError):
+        g.rollout(torch.zeros(8, 4, 8, device=_dev()), torch.zeros(8, 3, 2, device=_dev()), None, precision="bf16")

@@ -183,3 +183,51 @@ def test_synth_inputs_are_deterministic_and_bounded():
     assert a[0].shape == (100, 4, 8) and a[1].shape == (100, 30, 2)
     u = torch.as_tensor(rows[:, 6:8], dtype=torch.float32)
     assert (a[1] >= u.amin(0)).all() and (a[1] <= u.amax(0)).all()
+
+
+def test_pack_rnn_tensor_core_layout():
+    """mpcdl_pack_rnn_tc against a numpy restatement: tf32 hi/lo split (round to nearest, ties away),
+    canonical K-major UMMA core-matrix order, GRU weight_ih rows packed [n; r; z]."""
+    import numpy as np
+    import torch
+    from conftest import load_ckpt
+    from mpcdl import _lib, pack
+
+    def rna(x):
+        u = x.astype(np.float32).view(np.uint32)
+        return ((u + np.uint32(0x1000)) & np.uint32(0xFFFFE000)).view(np.float32)
+
+    for name, kind, G in (("GRU_64_4_4_16_False", _lib.GRU, 3), ("LSTM_64_4_4_16_False", _lib.LSTM, 4)):
+        sd = load_ckpt(name)
+        blob = pack.pack_rnn(sd, kind, 64, 4, 4, tensor_core=True).numpy()
+        pre = "gru" if kind == _lib.GRU else "lstm"
+        L, h, N = 4, 64, G * 64
+        off = L * h * 4
+        b_ih, b_hh = sd[f"{pre}.bias_ih_l1"].numpy(), sd[f"{pre}.bias_hh_l1"].numpy()
+        bias = blob[h * 4:2 * h * 4].reshape(h, 4)                        # layer 1
+        if kind == _lib.GRU:
+            want = np.stack([b_ih[:h] + b_hh[:h], b_ih[h:2 * h] + b_hh[h:2 * h], b_ih[2 * h:], b_hh[2 * h:]], 1)
+        else:
+            want = (b_ih + b_hh).reshape(4, h).T
+        assert np.array_equal(bias, want)
+        fc = blob[off:off + h * 8 + 8]
+        assert np.array_equal(fc[:h * 8].reshape(h, 8)[:, :6], sd["full_c.weight"].numpy().T)
+        assert np.array_equal(fc[h * 8:h * 8 + 6], sd["full_c.bias"].numpy())
+        pos = (off + h * 8 + 8 + 31) // 32 * 32
+        for l in range(L):
+            for part, key in enumerate(("weight_ih", "weight_hh")):
+                W = sd[f"{pre}.{key}_l{l}"].numpy()
+                K = W.shape[1]
+                if kind == _lib.GRU and part == 0:
+                    W = np.concatenate([W[2 * h:], W[:h], W[h:2 * h]])       # [n; r; z]
+                kc = min(K, 16)
+                hi = rna(W)
+                lo = rna(W - hi)
+                for c in range(K // kc):
+                    chunk = blob[pos:pos + 2 * kc * N]
+                    for half, ref in ((0, hi), (1, lo)):
+                        blk = chunk[half * kc * N:(half + 1) * kc * N].reshape(kc // 4, N // 8, 8, 4)   # [k/4][n/8][n%8][k%4]
+                        got = blk.transpose(1, 2, 0, 3).reshape(N, kc)
+                        assert np.array_equal(got, ref[:, c * kc:(c + 1) * kc]), (name, l, part, c, half)
+                    pos += 2 * kc * N
+        assert pos == blob.size

@@ -15,6 +15,11 @@ if [[ $what == *bench* ]]; then
   for wl in c5 c3 c3l c5g c4; do
     timeout 600 python bench.py --workload $wl --steps 5 --warmup 3 > gpurun_out/bench_$wl.json 2> gpurun_out/bench_$wl.err; echo "bench $wl exit $?"
   done
+  for prec in tf32x3 tf32; do
+    for wl in c3 c3s c3l c5g; do
+      timeout 600 python bench.py --workload $wl --precision $prec --steps 5 --warmup 3 --skip-cpu > gpurun_out/bench_${wl}_$prec.json 2> gpurun_out/bench_${wl}_$prec.err; echo "bench $wl $prec exit $?"
+    done
+  done
 fi
 if [[ $what == *sweep* ]]; then
   timeout 600 python tools/gpu_quick.py > gpurun_out/sweep.log 2>&1; echo "sweep exit $?"
