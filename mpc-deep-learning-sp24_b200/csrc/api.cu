@@ -79,7 +79,7 @@ const Mlp2Cand kMlp2[] = {
     {16, 4, 4, 2, 32, 64, 32}, {16, 8, 2, 1, 128, 512, 32},
 };
 double mlp2_cycles(const Mlp2Cand& c, int TN) {
-    if (c.ks == 2 && c.rt == 4) return 2009.0 * TN / 32;
+    if (c.ks == 2 && c.rt == 4) return 2009.0 * TN / 32;     // TN 28 on 147 SMs (7 warps) measured SLOWER than TN 32 on 128 (r01c)
     if (c.ks == 2) return 4029.0 * TN / 64;
     return 6596.0 + (TN - 128) * 39.3;
 }
