@@ -26,7 +26,7 @@ extern "C" {
 
 enum { MPCDL_MLP = 0, MPCDL_GRU = 1, MPCDL_LSTM = 2 };
 /* Arithmetic of the gate GEMMs.  FP32 = FFMA kernels (the parity path, <= 1e-5 one-step).  The tensor-core
- * modes run the [128 x 64].[64 x 192|256] gate contractions on tcgen05 (GRU/LSTM, hidden 64, window 4):
+ * modes run the [128 x 64].[64 x 64|192|256] layer / gate contractions on tcgen05 (hidden 64; GRU/LSTM window 4):
  * TF32X3 = three TF32 passes on hi/lo split operands (FP32-class accuracy, bound stated in DESIGN.md 5),
  * TF32 = one TF32 pass + MUFU.TANH activations.  State, accumulation, statistics and cost stay FP32. */
 enum { MPCDL_PREC_FP32 = 0, MPCDL_PREC_TF32X3 = 1, MPCDL_PREC_TF32 = 2 };
@@ -65,11 +65,16 @@ int mpcdl_pack_rnn(const mpcdl_model_desc* desc, const float* const* w_ih, const
 
 /* Tensor-core blob of a GRU_Model / LSTM_Model (same arguments as mpcdl_pack_rnn): every weight matrix is
  * split into tf32 hi/lo parts and laid out in the canonical K-major UMMA core-matrix order, in K-slices
- * the kernel streams with TMA.  Only hidden = 64, window = 4 is supported (0 / MPCDL_ERR_UNSUPPORTED else). */
+ * the kernel streams with TMA.  Only hidden = 64, window = 4 is supported (0 / MPCDL_ERR_UNSUPPORTED else).
+ * mpcdl_blob_floats_tc also sizes the MLP blob of mpcdl_pack_mlp_tc. */
 size_t mpcdl_blob_floats_tc(const mpcdl_model_desc* desc);
 int mpcdl_pack_rnn_tc(const mpcdl_model_desc* desc, const float* const* w_ih, const float* const* w_hh,
                       const float* const* b_ih, const float* const* b_hh, const float* fc_w, const float* fc_b,
                       float* blob);
+
+/* Tensor-core blob of a Basic_Model (same arguments as mpcdl_pack_mlp; hidden = 64): per layer the matrix as
+ * tf32 hi/lo blocks in UMMA operand order; the 64 -> 6 output layer stays FP32. */
+int mpcdl_pack_mlp_tc(const mpcdl_model_desc* desc, const float* const* W, const float* const* b, float* blob);
 
 /* Residual-noise net = utils/pytorch_utils.py:19-57 build_mlp((6+2)*history -> size x n_layers -> 12)
  * as used by FeedforwardNoiseModel (model_scripts/noise_model.py:19-40).  W[i] [out][in], b[i] [out],
@@ -118,7 +123,7 @@ int mpcdl_rollout(const mpcdl_rollout_args* args, void* stream);
 typedef struct {
     int32_t rt, rj, n_tg, tile_traj, threads, grid, smem_bytes, resident, nslots, slot_floats, ntiles;
     int32_t variant;           /* 0 = generic ring-fed kernel, 2 = weight-resident MLP kernel,
-                                  4 = tcgen05 GRU/LSTM kernel                                                */
+                                  4 = tcgen05 GRU/LSTM kernel, 5 = tcgen05 MLP kernel                        */
     int32_t ksplit;            /* K slices of a hidden layer (weight-resident MLP kernel)                   */
 } mpcdl_plan;
 int mpcdl_rollout_plan(const mpcdl_rollout_args* args, mpcdl_plan* plan);

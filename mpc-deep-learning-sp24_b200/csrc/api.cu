@@ -196,6 +196,38 @@ int make_tc_plan(const mpcdl_rollout_args& a, TcPlan& pl, int num_sms) {
     return MPCDL_OK;
 }
 
+// ---------------------------------------------------------------------------- tensor-core MLP (rollout_mlp_tc.cu)
+bool mc_supported(const mpcdl_model_desc& d) { return d.kind == MPCDL_MLP && d.hidden == TC_HID; }
+
+uint32_t build_mc_offsets(const mpcdl_model_desc& d, bool x3, McModel& m) {
+    uint32_t off = 0, so = 0;
+    m.bias_off = off; off += (uint32_t)(d.layers + 1) * TC_HID;
+    m.out_off = off;  off += TC_HID * 8 + 8;
+    off = (off + 31u) / 32u * 32u;
+    for (int l = 0; l <= d.layers; ++l) {
+        const uint32_t blk = (l == 0 ? 8u : (uint32_t)TC_HID) * TC_HID;
+        m.w_off[l] = off;  off += 2 * blk;             // blob always holds hi and lo
+        m.w_smem[l] = so;  so += blk * (x3 ? 2u : 1u); // shared memory holds what the precision needs
+    }
+    m.w_floats = so;
+    m.layers = d.layers;
+    return off;
+}
+
+struct McPlan { int smem_bytes, ntiles, grid, tiles_per_cta; };
+int make_mc_plan(const mpcdl_rollout_args& a, McPlan& pl, int num_sms) {
+    McModel m;
+    build_mc_offsets(a.model, a.precision == MPCDL_PREC_TF32X3, m);
+    pl.smem_bytes = std::max(mc_layout((int)m.w_floats, a.model.layers).total * 4, 120 * 1024);
+    if (pl.smem_bytes > SMEM_LIMIT)
+        return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core MLP: %d layers of tf32 hi/lo weights (%d KB) do not fit shared memory; use MPCDL_PREC_TF32 or FP32",
+                    a.model.layers, pl.smem_bytes / 1024);
+    pl.ntiles = (int)((a.N + TC_TN - 1) / TC_TN);
+    pl.tiles_per_cta = (a.tune_ntg == 1 || a.tune_ntg == 2) ? a.tune_ntg : (pl.ntiles > num_sms ? MC_TILES : 1);
+    pl.grid = std::min((pl.ntiles + pl.tiles_per_cta - 1) / pl.tiles_per_cta, num_sms);
+    return MPCDL_OK;
+}
+
 int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
     const mpcdl_model_desc& d = a.model;
     const bool rnn = d.kind != MPCDL_MLP;
@@ -274,6 +306,7 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
 }
 
 bool tc_supported(const mpcdl_model_desc& d);
+bool mc_supported(const mpcdl_model_desc& d);
 int check_args(const mpcdl_rollout_args* a) {
     if (!a) return fail(MPCDL_ERR_ARG, "args is NULL");
     int rc = check_desc(&a->model);
@@ -285,9 +318,11 @@ int check_args(const mpcdl_rollout_args* a) {
     if (a->model.kind != MPCDL_MLP && a->stateful && !a->carry) return fail(MPCDL_ERR_ARG, "stateful rollout needs a carry buffer");
     if (a->precision != MPCDL_PREC_FP32) {
         if (a->precision != MPCDL_PREC_TF32X3 && a->precision != MPCDL_PREC_TF32) return fail(MPCDL_ERR_ARG, "unknown precision %d", a->precision);
-        if (!tc_supported(a->model))
-            return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core precision needs a GRU/LSTM with hidden=%d window=%d (got kind=%d hidden=%d window=%d); use MPCDL_PREC_FP32",
+        if (!tc_supported(a->model) && !mc_supported(a->model))
+            return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core precision needs hidden=%d (GRU/LSTM: window=%d); got kind=%d hidden=%d window=%d; use MPCDL_PREC_FP32",
                         TC_HID, TC_T, a->model.kind, a->model.hidden, a->model.window);
+        if (a->model.kind == MPCDL_MLP && a->noise_wblob)
+            return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core MLP rollout has no residual-noise path; use MPCDL_PREC_FP32");
         if (!a->wblob_tc) return fail(MPCDL_ERR_ARG, "tensor-core precision needs wblob_tc (mpcdl_pack_rnn_tc)");
     }
     if (a->noise_wblob) {
@@ -384,7 +419,8 @@ int mpcdl_pack_rnn(const mpcdl_model_desc* desc, const float* const* w_ih, const
 
 size_t mpcdl_blob_floats_tc(const mpcdl_model_desc* desc) {
     if (check_desc(desc)) return 0;
-    if (!tc_supported(*desc)) { fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: GRU/LSTM with hidden=%d window=%d only", TC_HID, TC_T); return 0; }
+    if (mc_supported(*desc)) { McModel m; return build_mc_offsets(*desc, true, m); }
+    if (!tc_supported(*desc)) { fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: hidden=%d only (GRU/LSTM: window=%d)", TC_HID, TC_T); return 0; }
     TcPart parts[2 * MAX_LAYERS];
     uint32_t bo, fo;
     return build_tc_parts(*desc, parts, bo, fo);
@@ -439,6 +475,37 @@ int mpcdl_pack_rnn_tc(const mpcdl_model_desc* desc, const float* const* w_ih, co
     return MPCDL_OK;
 }
 
+int mpcdl_pack_mlp_tc(const mpcdl_model_desc* desc, const float* const* W, const float* const* b, float* blob) {
+    int rc = check_desc(desc);
+    if (rc) return rc;
+    if (!mc_supported(*desc)) return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core MLP blob: hidden=%d only", TC_HID);
+    if (!W || !b || !blob) return fail(MPCDL_ERR_ARG, "mpcdl_pack_mlp_tc: bad arguments");
+    McModel m;
+    const uint32_t total = build_mc_offsets(*desc, true, m);
+    std::fill(blob, blob + total, 0.f);
+    const int h = TC_HID, L = desc->layers;
+    for (int l = 0; l <= L; ++l) {
+        const int K = l == 0 ? 8 : h;
+        for (int j = 0; j < h; ++j) blob[m.bias_off + l * h + j] = b[l][j];
+        float* hi = blob + m.w_off[l];
+        float* lo = hi + (size_t)K * h;
+        for (int n = 0; n < h; ++n)
+            for (int k = 0; k < K; ++k) {
+                const float w = W[l][(size_t)n * K + k];
+                const float whi = tf32_rna_host(w);
+                const size_t e = (size_t)(k / 4) * (h / 8) * 32 + (size_t)(n / 8) * 32 + (n % 8) * 4 + (k % 4);
+                hi[e] = whi;
+                lo[e] = tf32_rna_host(w - whi);
+            }
+    }
+    float* out = blob + m.out_off;                                      // W^T [j][8] then bias[8], FP32 (CUDA-core head)
+    for (int d = 0; d < 6; ++d) {
+        out[h * 8 + d] = b[L + 1][d];
+        for (int j = 0; j < h; ++j) out[j * 8 + d] = W[L + 1][d * h + j];
+    }
+    return MPCDL_OK;
+}
+
 size_t mpcdl_noise_blob_floats(int history, int size, int n_layers) {
     size_t total = 0;
     int K = 8 * history;
@@ -470,6 +537,16 @@ int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
     if (rc) return rc;
     if (!out) return fail(MPCDL_ERR_ARG, "plan is NULL");
     int sms = g_num_sms ? g_num_sms : 148;                   // planning works without a device (B200 = 148 SMs)
+    if (a->precision != MPCDL_PREC_FP32 && a->model.kind == MPCDL_MLP) {
+        McPlan mp;
+        rc = make_mc_plan(*a, mp, sms);
+        if (rc) return rc;
+        memset(out, 0, sizeof(*out));
+        out->rt = 1; out->rj = 64; out->n_tg = TC_TN; out->tile_traj = TC_TN; out->threads = MC_THREADS; out->grid = mp.grid;
+        out->smem_bytes = mp.smem_bytes; out->resident = 1; out->nslots = 1; out->ntiles = mp.ntiles; out->variant = 5;
+        out->ksplit = mp.tiles_per_cta;
+        return MPCDL_OK;
+    }
     if (a->precision != MPCDL_PREC_FP32) {
         TcPlan tp;
         rc = make_tc_plan(*a, tp, sms);
@@ -496,6 +573,19 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     if (rc) return rc;
     if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (a->precision != MPCDL_PREC_FP32 && a->model.kind == MPCDL_MLP) {
+        McPlan mp;
+        rc = make_mc_plan(*a, mp, g_num_sms);
+        if (rc) return rc;
+        McRolloutParams q;
+        memset(&q, 0, sizeof(q));
+        build_mc_offsets(a->model, a->precision == MPCDL_PREC_TF32X3, q.m);
+        q.m.blob = a->wblob_tc; q.m.prec = a->precision; q.m.tiles_per_cta = mp.tiles_per_cta;
+        fill_io(q.io, *a, mp.ntiles);
+        cudaError_t e = launch_mlp_tc(q, mp.grid, mp.smem_bytes, st);
+        if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "tensor-core MLP kernel launch failed: %s (smem=%d)", cudaGetErrorString(e), mp.smem_bytes);
+        return MPCDL_OK;
+    }
     if (a->precision != MPCDL_PREC_FP32) {
         TcPlan tp;
         rc = make_tc_plan(*a, tp, g_num_sms);

@@ -33,6 +33,7 @@ cudaError_t launch_mlp2(const RolloutParams& p, int rt, int rj, int ks, int grid
 int mlp2_smem_bytes(int blob_floats, int hid, int TN, int ks, int rt, int rj);
 cudaError_t launch_rnn(const RolloutParams& p, int cell, int rt, int rj, int grid, int smem_bytes, cudaStream_t st);
 cudaError_t launch_rnn_tc(const TcRolloutParams& p, int grid, int smem_bytes, cudaStream_t st);
+cudaError_t launch_mlp_tc(const McRolloutParams& p, int grid, int smem_bytes, cudaStream_t st);
 cudaError_t launch_ffma_peak(float* out, int iters, int grid, cudaStream_t st);
 
 }  // namespace mpcdl

@@ -70,3 +70,40 @@ __host__ __device__ inline TcSmem tc_layout(int nslots, int slot_floats, int lay
 constexpr int TC_MAX_SLOTS = 12;
 
 }  // namespace mpcdl
+
+// ------------------------------------------------------------------ tensor-core MLP kernel (rollout_mlp_tc.cu)
+namespace mpcdl {
+
+constexpr int MC_TILES = 2;           // trajectory tiles per CTA: the MMA phase of one overlaps the epilogue of the other
+constexpr int MC_THREADS = 320;       // 2 x 4 epilogue warps (thread = trajectory row) + one MMA-issuing warp per tile
+constexpr int MC_TILE_COLS = 256;     // TMEM columns per tile: D [0,64), A_hi [64,128), A_lo [128,192)
+
+// blob: [bias (L+1) x 64][out: W^T [64][8], bias [8]][pad to 32] then per layer l = 0..L the matrix
+// W_l [64 rows = units][K = 8 | 64] as [hi block][lo block] in the canonical K-major UMMA order (N = 64).
+struct McModel {
+    const float* blob;
+    uint32_t bias_off, out_off;
+    uint32_t w_off[MAX_LAYERS + 1];   // float offset of layer l's hi block (lo block follows)
+    uint32_t w_smem[MAX_LAYERS + 1];  // float offset of layer l inside the shared-memory weight region
+    uint32_t w_floats;                // shared-memory weight region size
+    int layers, prec, tiles_per_cta;
+};
+struct McRolloutParams {
+    McModel m;
+    IoParams io;
+    NoiseParams nz;                   // never enabled (owner_finish reads the flag)
+};
+struct McSmem { int bars, w, bias, out, norm, total; };
+__host__ __device__ inline McSmem mc_layout(int w_floats, int layers) {
+    McSmem L;
+    int o = 0;
+    L.bars = o;  o += 64;
+    L.w = o;     o += align_up(w_floats, 32);
+    L.bias = o;  o += (layers + 1) * TC_HID;
+    L.out = o;   o += TC_HID * 8 + 8;
+    L.norm = o;  o += 32;
+    L.total = o;
+    return L;
+}
+
+}  // namespace mpcdl

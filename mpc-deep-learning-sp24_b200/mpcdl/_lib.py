@@ -61,7 +61,7 @@ class Plan(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
-EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
+EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_pack_mlp_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
            "mpcdl_rollout", "mpcdl_rollout_plan", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version")
 
 
@@ -82,6 +82,8 @@ def _load():
     lib.mpcdl_blob_floats_tc.argtypes = [C.POINTER(ModelDesc)]
     lib.mpcdl_pack_rnn_tc.restype = C.c_int
     lib.mpcdl_pack_rnn_tc.argtypes = [C.POINTER(ModelDesc), fpp, fpp, fpp, fpp, fp, fp, fp]
+    lib.mpcdl_pack_mlp_tc.restype = C.c_int
+    lib.mpcdl_pack_mlp_tc.argtypes = [C.POINTER(ModelDesc), fpp, fpp, fp]
     lib.mpcdl_noise_blob_floats.restype = C.c_size_t
     lib.mpcdl_noise_blob_floats.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.mpcdl_pack_noise.restype = C.c_int

@@ -103,8 +103,6 @@ class _RolloutMixin:
         if precision not in _lib.PRECISION:
             raise RuntimeError(f"mpcdl: unknown precision {precision!r} (fp32 | tf32x3 | tf32)")
         prec = _lib.PRECISION[precision]
-        if prec and self.KIND == _lib.MLP:
-            raise RuntimeError("mpcdl: the tensor-core precisions cover the GRU/LSTM models; Basic_Model runs the FP32 kernels")
         states, costs = ops.OPS[self.KIND](self._blob(dev), self._norm(stats, dev), init, U, hidden, layers, window,
                                            stateful, carry if stateful else None, nblob, ncfg, eps, int(seed),
                                            int(traj_offset), cref, cw, bool(return_states), cost is not None,
@@ -128,6 +126,7 @@ class Basic_Model(_RolloutMixin, nn.Module):
                 self.layers.append(nn.Dropout(0.1))       # shifts the Linear indices (basic_model.py:53-54)
         self.layers.append(nn.Linear(hidden, output))
         self._hidden, self._nlayers = hidden, layers
+        self.precision = "fp32"        # "fp32" | "tf32x3" | "tf32" (tcgen05, hidden 64)
         self._packed = _Packed()
 
     def _desc(self):
@@ -136,6 +135,12 @@ class Basic_Model(_RolloutMixin, nn.Module):
     def _blob(self, device):
         return self._packed.get(list(self.parameters()), device,
                                 lambda: pack.pack_mlp(self.state_dict(), self._hidden, self._nlayers))
+
+    def _blob_tc(self, device):
+        if not hasattr(self, "_packed_tc"):
+            self._packed_tc = _Packed()
+        return self._packed_tc.get(list(self.parameters()), device,
+                                   lambda: pack.pack_mlp(self.state_dict(), self._hidden, self._nlayers, tensor_core=True))
 
     def forward(self, x):
         """x [B,8] z-scored features -> [B,6] z-scored next state (one fused launch, H = 1).

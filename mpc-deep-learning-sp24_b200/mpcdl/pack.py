@@ -34,7 +34,7 @@ def _blob(desc):
     return np.empty(n, dtype=np.float32)
 
 
-def pack_mlp(sd, hidden: int, layers: int) -> torch.Tensor:
+def pack_mlp(sd, hidden: int, layers: int, tensor_core: bool = False) -> torch.Tensor:
     """Basic_Model state_dict -> blob.  Dropout entries (do_drop=True) hold no parameters, so the
     Linear entries are simply the sorted ``layers.{i}`` indices present (basic_model.py:53-54)."""
     idx = sorted({int(k.split(".")[1]) for k in sd if k.startswith("layers.")})
@@ -47,6 +47,13 @@ def pack_mlp(sd, hidden: int, layers: int) -> torch.Tensor:
         if w.shape != s:
             raise RuntimeError(f"mpcdl: weight shape {w.shape} != {s}")
     desc = _lib.ModelDesc(_lib.MLP, hidden, layers, 0)
+    if tensor_core:
+        n = _lib.lib.mpcdl_blob_floats_tc(C.byref(desc))
+        if n == 0:
+            _lib.check(-2)
+        blob = np.empty(n, dtype=np.float32)
+        _lib.check(_lib.lib.mpcdl_pack_mlp_tc(C.byref(desc), _ptrs(W), _ptrs(b), blob.ctypes.data_as(_FP)))
+        return torch.from_numpy(blob)
     blob = _blob(desc)
     _lib.check(_lib.lib.mpcdl_pack_mlp(C.byref(desc), _ptrs(W), _ptrs(b), blob.ctypes.data_as(_FP)))
     return torch.from_numpy(blob)
