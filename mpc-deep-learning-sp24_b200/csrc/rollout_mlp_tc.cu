@@ -6,7 +6,8 @@
 // tile, FMA-pipe bound at 0.71 of the FFMA peak in rollout_mlp2.cu; here the layers run on tcgen05:
 //   * all weights (tf32 hi/lo, canonical K-major UMMA order) are TMA-copied into shared memory ONCE per CTA;
 //   * a CTA owns TWO tiles of 128 trajectories; each tile has its own TMEM slice (D 64 + A_hi 64 + A_lo 64
-//     columns), its own 4 epilogue warps (thread = trajectory = TMEM lane) and its own MMA-issuing warp, so
+//     columns), its own 8 epilogue warps (TMEM lane = trajectory, two threads per trajectory with 32 hidden
+//     units each) and its own MMA-issuing warp, so
 //     the MMA phase of one tile overlaps the epilogue phase of the other (both fit: 2 x 192 <= 512 columns);
 //   * the epilogue reads D, adds the bias, applies ReLU and writes the activations back as the next layer's
 //     A operand (tcgen05.st, tf32 hi/lo split) -- activations never touch shared memory; the 64 -> 6 output
@@ -51,8 +52,8 @@ __device__ __forceinline__ void mc_stage16(uint32_t t_hi, uint32_t t_lo, const f
     uint32_t hi[16], lo[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-        hi[i] = umma::tf32_rna(v[i]);
-        lo[i] = X3 ? umma::tf32_rna(v[i] - __uint_as_float(hi[i])) : 0u;
+        hi[i] = umma::tf32_round_fast(v[i]);
+        lo[i] = X3 ? __float_as_uint(v[i] - __uint_as_float(hi[i])) : 0u;
     }
     umma::tmem_st16(t_hi, hi);
     if (X3) umma::tmem_st16(t_lo, lo);
@@ -76,7 +77,7 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
 
     if (tid == 0) {
         mbar_init(wfull, 1);
-        for (int t = 0; t < MC_TILES; ++t) { mbar_init(&opnd[t], TN); mbar_init(&accb[t], 1); }
+        for (int t = 0; t < MC_TILES; ++t) { mbar_init(&opnd[t], MC_EPI_WARPS * 32); mbar_init(&accb[t], 1); }
         mbar_fence_init();
         // weights -> shared memory, once (hi blocks, and lo blocks for tf32x3)
         uint32_t bytes = 0;
@@ -88,7 +89,7 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                 bulk_g2s(sm + L.w + m.w_smem[l] + o, m.blob + m.w_off[l] + o, min(4096u, n - o) * 4u, wfull);
         }
     }
-    if (warp == 8) { umma::tmem_alloc(tmem_slot, 512); umma::tmem_relinquish(); }
+    if (warp == MC_TILES * MC_EPI_WARPS) { umma::tmem_alloc(tmem_slot, 512); umma::tmem_relinquish(); }
     for (int i = tid; i < (NL + 1) * HID; i += blockDim.x) sm[L.bias + i] = m.blob[m.bias_off + i];
     for (int i = tid; i < HID * 8 + 8; i += blockDim.x) sm[L.out + i] = m.blob[m.out_off + i];
     for (int i = tid; i < 28; i += blockDim.x) sm[L.norm + i] = p.io.norm[i];       // f_mean8 f_std8 l_mean6 l_std6
@@ -99,9 +100,10 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
     const int tpc = m.tiles_per_cta;
     const int ngroups = (p.io.ntiles + tpc - 1) / tpc;                 // tile groups, one per CTA iteration
 
-    if (warp >= 8) {
-        // ============================================================== MMA issuer of tile slot (warp - 8)
-        const int ts = warp - 8;
+    constexpr int EW = MC_EPI_WARPS, NEPI = MC_TILES * MC_EPI_WARPS;
+    if (warp >= NEPI) {
+        // ============================================================== MMA issuer of tile slot (warp - NEPI)
+        const int ts = warp - NEPI;
         const uint32_t tcol = tbase + ts * MC_TILE_COLS;
         const uint32_t wbase = smem_u32(sm + L.w);
         uint32_t par = 0;
@@ -124,12 +126,16 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                     }
             }
     } else {
-        // ============================================================== epilogue warps: thread = trajectory
-        const int ts = warp >> 2, q = warp & 3;
+        // ============================================================== epilogue warps: two threads per trajectory
+        const int ts = warp / EW, we = warp % EW;
+        const int q = we & 3, uh = we >> 2;                 // TMEM lane quarter, hidden-unit half
         const int row = q * 32 + lane;
+        const int u0 = uh * 32;
+        const bool owner = uh == 0;
         const uint32_t tlane = tbase + ts * MC_TILE_COLS + (static_cast<uint32_t>(q * 32) << 16);
         const float* const normS = sm + L.norm;
         const float* const outS = sm + L.out;
+        float* const ypart = sm + L.ypart + ts * 6 * TN;
         uint32_t par = 0;
         if (ts < tpc)
             for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
@@ -140,13 +146,14 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                 if (n >= N) n = N - 1;
                 float s[6], cost = 0.f;
 #pragma unroll
-                for (int d = 0; d < 6; ++d) s[d] = __ldg(p.io.init + n * 6 + d);
+                for (int d = 0; d < 6; ++d) s[d] = owner ? __ldg(p.io.init + n * 6 + d) : 0.f;
                 const float2* up = reinterpret_cast<const float2*>(p.io.U) + n * H;
-                float2 unext = __ldg(up);
+                float2 unext = owner ? __ldg(up) : make_float2(0.f, 0.f);
                 for (int t = 0; t < H; ++t) {
                     const float u[2] = {unext.x, unext.y};
-                    if (t + 1 < H) unext = __ldg(up + t + 1);            // prefetch: hidden behind this step's layers
-                    {   // z-score ([s,u] - f_mean) / f_std  (basic_model.py:34) -> A operand columns 0..7
+                    if (owner) {
+                        if (t + 1 < H) unext = __ldg(up + t + 1);        // prefetch: hidden behind this step's layers
+                        // z-score ([s,u] - f_mean) / f_std  (basic_model.py:34) -> A operand columns 0..7
                         float xn[8];
 #pragma unroll
                         for (int k = 0; k < 6; ++k) xn[k] = __fdiv_rn(__fsub_rn(s[k], normS[k]), normS[8 + k]);
@@ -155,28 +162,28 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                         uint32_t hi[8], lo[8];
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
-                            hi[i] = umma::tf32_rna(xn[i]);
-                            lo[i] = X3 ? umma::tf32_rna(xn[i] - __uint_as_float(hi[i])) : 0u;
+                            hi[i] = umma::tf32_round_fast(xn[i]);
+                            lo[i] = X3 ? __float_as_uint(xn[i] - __uint_as_float(hi[i])) : 0u;
                         }
                         umma::tmem_st8(tlane + MC_A_HI, hi);
                         if (X3) umma::tmem_st8(tlane + MC_A_LO, lo);
+                        umma::wait_st();
                     }
-                    umma::wait_st();
                     umma::fence_before_sync();
                     mbar_arrive(&opnd[ts]);
                     float y[6];
 #pragma unroll
-                    for (int d = 0; d < 6; ++d) y[d] = outS[HID * 8 + d];
+                    for (int d = 0; d < 6; ++d) y[d] = owner ? outS[HID * 8 + d] : 0.f;
                     for (int l = 0; l <= NL; ++l) {
                         const bool last = l == NL;
-                        const float4* bl = reinterpret_cast<const float4*>(sm + L.bias + l * HID);
+                        const float4* bl = reinterpret_cast<const float4*>(sm + L.bias + l * HID + u0);
                         mbar_wait(&accb[ts], par);
                         par ^= 1u;
                         umma::fence_after_sync();
 #pragma unroll
-                        for (int b = 0; b < 4; ++b) {
+                        for (int b = 0; b < 2; ++b) {
                             float v[16];
-                            umma::tmem_ld16(tlane + MC_D + b * 16, v);
+                            umma::tmem_ld16(tlane + MC_D + u0 + b * 16, v);
                             umma::wait_ld();
 #pragma unroll
                             for (int i = 0; i < 16; i += 4) {
@@ -185,12 +192,12 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                                 v[i + 2] = fmaxf(v[i + 2] + bb.z, 0.f); v[i + 3] = fmaxf(v[i + 3] + bb.w, 0.f);
                             }
                             if (!last) {
-                                mc_stage16<X3>(tlane + MC_A_HI + b * 16, tlane + MC_A_LO + b * 16, v);
-                            } else {                                     // output layer 64 -> 6 in FP32 (k ascending)
+                                mc_stage16<X3>(tlane + MC_A_HI + u0 + b * 16, tlane + MC_A_LO + u0 + b * 16, v);
+                            } else {                                     // output layer 64 -> 6 in FP32, this thread's 32 units
 #pragma unroll
                                 for (int i = 0; i < 16; ++i) {
-                                    const float4 w0 = *reinterpret_cast<const float4*>(outS + (b * 16 + i) * 8);
-                                    const float2 w1 = *reinterpret_cast<const float2*>(outS + (b * 16 + i) * 8 + 4);
+                                    const float4 w0 = *reinterpret_cast<const float4*>(outS + (u0 + b * 16 + i) * 8);
+                                    const float2 w1 = *reinterpret_cast<const float2*>(outS + (u0 + b * 16 + i) * 8 + 4);
                                     y[0] = fmaf(v[i], w0.x, y[0]); y[1] = fmaf(v[i], w0.y, y[1]); y[2] = fmaf(v[i], w0.z, y[2]);
                                     y[3] = fmaf(v[i], w0.w, y[3]); y[4] = fmaf(v[i], w1.x, y[4]); y[5] = fmaf(v[i], w1.y, y[5]);
                                 }
@@ -204,18 +211,28 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                             umma::fence_before_sync();               // D reads are ordered before the next step's MMAs
                         }
                     }
-                    float nxt[6];
-                    owner_finish(p, normS + 16, y, nullptr, 1, 0, n, valid, t, u, nxt, cost);
+                    // the unit-half-1 thread hands its partial output sums to the trajectory's owner thread
+                    if (!owner) {
 #pragma unroll
-                    for (int d = 0; d < 6; ++d) s[d] = nxt[d];
+                        for (int d = 0; d < 6; ++d) ypart[d * TN + row] = y[d];
+                    }
+                    named_bar_sync(1 + ts, EW * 32);
+                    if (owner) {
+#pragma unroll
+                        for (int d = 0; d < 6; ++d) y[d] += ypart[d * TN + row];
+                        float nxt[6];
+                        owner_finish(p, normS + 16, y, nullptr, 1, 0, n, valid, t, u, nxt, cost);
+#pragma unroll
+                        for (int d = 0; d < 6; ++d) s[d] = nxt[d];
+                    }
                 }
-                if (valid && p.io.costs) p.io.costs[n] = cost;
+                if (owner && valid && p.io.costs) p.io.costs[n] = cost;
             }
     }
     // ------------------------------------------------------------------ teardown
     umma::fence_before_sync();
     __syncthreads();
-    if (warp == 8) umma::tmem_dealloc(tbase, 512);
+    if (warp == MC_TILES * MC_EPI_WARPS) umma::tmem_dealloc(tbase, 512);
 }
 
 cudaError_t launch_mlp_tc(const McRolloutParams& p, int grid, int smem_bytes, cudaStream_t st) {

@@ -49,8 +49,8 @@ __device__ __forceinline__ void stage16(uint32_t t_hi, uint32_t t_lo, const floa
     uint32_t hi[16], lo[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-        hi[i] = umma::tf32_rna(v[i]);
-        lo[i] = X3 ? umma::tf32_rna(v[i] - __uint_as_float(hi[i])) : 0u;
+        hi[i] = umma::tf32_round_fast(v[i]);
+        lo[i] = X3 ? __float_as_uint(v[i] - __uint_as_float(hi[i])) : 0u;
     }
     umma::tmem_st16(t_hi, hi);
     if (X3) umma::tmem_st16(t_lo, lo);
@@ -60,8 +60,8 @@ __device__ __forceinline__ void stage8(uint32_t t_hi, uint32_t t_lo, const float
     uint32_t hi[8], lo[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        hi[i] = umma::tf32_rna(v[i]);
-        lo[i] = X3 ? umma::tf32_rna(v[i] - __uint_as_float(hi[i])) : 0u;
+        hi[i] = umma::tf32_round_fast(v[i]);
+        lo[i] = X3 ? __float_as_uint(v[i] - __uint_as_float(hi[i])) : 0u;
     }
     umma::tmem_st8(t_hi, hi);
     if (X3) umma::tmem_st8(t_lo, lo);

@@ -75,7 +75,8 @@ constexpr int TC_MAX_SLOTS = 12;
 namespace mpcdl {
 
 constexpr int MC_TILES = 2;           // trajectory tiles per CTA: the MMA phase of one overlaps the epilogue of the other
-constexpr int MC_THREADS = 320;       // 2 x 4 epilogue warps (thread = trajectory row) + one MMA-issuing warp per tile
+constexpr int MC_EPI_WARPS = 8;       // epilogue warps per tile: lane quarter = warp % 4, unit half = warp / 4 (2 threads per trajectory)
+constexpr int MC_THREADS = (MC_TILES * MC_EPI_WARPS + MC_TILES) * 32;   // + one MMA-issuing warp per tile
 constexpr int MC_TILE_COLS = 256;     // TMEM columns per tile: D [0,64), A_hi [64,128), A_lo [128,192)
 
 // blob: [bias (L+1) x 64][out: W^T [64][8], bias [8]][pad to 32] then per layer l = 0..L the matrix
@@ -93,7 +94,7 @@ struct McRolloutParams {
     IoParams io;
     NoiseParams nz;                   // never enabled (owner_finish reads the flag)
 };
-struct McSmem { int bars, w, bias, out, norm, total; };
+struct McSmem { int bars, w, bias, out, norm, ypart, total; };
 __host__ __device__ inline McSmem mc_layout(int w_floats, int layers) {
     McSmem L;
     int o = 0;
@@ -102,6 +103,7 @@ __host__ __device__ inline McSmem mc_layout(int w_floats, int layers) {
     L.bias = o;  o += (layers + 1) * TC_HID;
     L.out = o;   o += TC_HID * 8 + 8;
     L.norm = o;  o += 32;
+    L.ypart = o; o += MC_TILES * 6 * TC_TN;     // output-layer partial sums of the unit-half-1 threads
     L.total = o;
     return L;
 }

@@ -87,6 +87,15 @@ __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) 
     hi = tf32_rna(x);
     lo = tf32_rna(x - __uint_as_float(hi));
 }
+// Activation-side split on the integer pipe: cvt.rna.tf32.f32 expands to ~5 SASS instructions (inf/nan handling),
+// which made the epilogues issue-bound (profiles/r01c).  hi = round-to-nearest (ties away) by add-and-mask
+// (finite inputs), lo = the exact residual left as raw FP32 bits: the tensor core reads only the top 19 bits
+// of a tf32 operand, i.e. truncates it (|lo| <= 2^-11 |x|, so the representation error stays <= 2^-21 |x|).
+__device__ __forceinline__ uint32_t tf32_round_fast(float x) { return (__float_as_uint(x) + 0x1000u) & 0xFFFFE000u; }
+__device__ __forceinline__ void split_tf32_fast(float x, uint32_t& hi, uint32_t& lo) {
+    hi = tf32_round_fast(x);
+    lo = __float_as_uint(x - __uint_as_float(hi));
+}
 
 // ------------------------------------------------------------------ descriptors
 // Canonical K-major, SWIZZLE_NONE layout (16-byte units): element (row r, 16-B k-chunk c) sits at
