@@ -241,8 +241,6 @@ def run_native(args, w):
     init_d, U_d = init_p.to(dev), U_p.to(dev)
     cost_d = tuple(c.to(dev) for c in cost)
     prec = args.precision
-    if prec != "fp32" and meta["kind"] == "Basic":
-        raise SystemExit("bench.py: --precision tf32x3|tf32 applies to the GRU/LSTM workloads (tcgen05 path)")
     kw = dict(noise=noise, seed=1, traj_offset=rank * N, cost=cost_d, return_states=w["states"], precision=prec)
     costs_all = torch.empty(world * N, device=dev) if world > 1 else None
 

@@ -81,8 +81,18 @@ def test_tensor_core_plans_and_errors():
                     assert p["ksplit"] in (1, 2, 4) and p["grid"] == 148 and p["ntiles"] == 512
                     if p["resident"]:
                         assert p["nslots"] * p["ksplit"] >= 8          # a layer's two 64-row matrices stay in the ring
-    for args in [(1, 128, 2, 4), (1, 64, 4, 8), (0, 64, 4, 0)]:           # hidden 128 / window 8 / MLP: FP32 kernels only
+    for args in [(1, 128, 2, 4), (1, 64, 4, 8), (0, 16, 4, 0)]:           # hidden 128 / window 8 / MLP hidden 16: FP32 kernels only
         with pytest.raises(RuntimeError):
             ops.plan(args[0], args[1], args[2], args[3], 100, 5, precision="tf32x3")
+    with pytest.raises(RuntimeError):                                      # tcgen05 MLP has no residual-noise path
+        ops.plan(0, 64, 4, 0, 100, 5, noise_cfg=[3, 32, 2, 2], precision="tf32")
+    # tcgen05 MLP (rollout_mlp_tc.cu): 128-trajectory tiles, two ping-pong tiles per CTA once there are more tiles than SMs
+    for prec in ("tf32x3", "tf32"):
+        for layers in (1, 2, 4):
+            p = ops.plan(0, 64, layers, 0, 4096, 50, precision=prec)
+            assert p["variant"] == 5 and p["tile_traj"] == 128 and p["ntiles"] == 32 and p["grid"] == 32 and p["ksplit"] == 1
+            p = ops.plan(0, 64, layers, 0, 1 << 20, 50, precision=prec)
+            assert p["grid"] == 148 and p["ksplit"] == 2 and p["ntiles"] == 8192
+            assert 120 * 1024 <= p["smem_bytes"] <= 232448 and p["threads"] % 32 == 0 and p["threads"] <= 1024
     d = _lib.ModelDesc(_lib.GRU, 32, 2, 4)
     assert _lib.lib.mpcdl_blob_floats_tc(C.byref(d)) == 0

@@ -207,9 +207,59 @@ def test_t3_tensor_core_noise_cost(prec, gold_rollouts, gold_stats):
     assert torch.equal(full[40:], part)
 
 
+# tcgen05 MLP (rollout_mlp_tc.cu), hidden-64 checkpoints.  Stated bounds (profiles/r01c/mc_check_v2.log):
+#   tf32x3  one-step <= 5e-6 (FP32-class: measured 4e-7..9e-7);  H = 50 vs FP64: p50 <= 1e-5, p90 <= 3e-5, p99 <= 1e-4
+#   tf32    one-step <= 3e-3;                                     H = 50 vs FP64: p50 <= 4e-3, p90 <= 1.2e-2, p99 <= 4e-2
+MC_BOUNDS = {"tf32x3": (5e-6, (1e-5, 3e-5, 1e-4)), "tf32": (3e-3, (4e-3, 1.2e-2, 4e-2))}
+FWD64 = [n for n in FWD if n.startswith("Basic_64")]
+
+
+@pytest.mark.parametrize("prec", ["tf32x3", "tf32"])
+@pytest.mark.parametrize("name", FWD64)
+def test_t3_mlp_tensor_core_onestep(name, prec, bags, gold_onestep):
+    """Basic_Model.forward on every validation row through the tcgen05 MLP kernel (4550 rows = 35 tiles + 70)."""
+    import mpcdl
+    ds = mpcdl.RobotData(bags)
+    m, _ = _model(name)
+    m.precision = prec
+    y = m(ds.featrs.to(_dev()))
+    assert y.shape == (4550, 6)
+    assert _t1(y, gold_onestep[name]) <= MC_BOUNDS[prec][0]
+
+
+@pytest.mark.parametrize("prec", ["tf32x3", "tf32"])
+@pytest.mark.parametrize("n", [300, 40000])
+@pytest.mark.parametrize("name", ["Basic_64_4_32", "Basic_64_1_32"])
+def test_t3_mlp_tensor_core_horizon(name, n, prec, gold_stats):
+    """H = 50, ragged N; 40000 > 148 tiles exercises the two-tiles-per-CTA ping-pong and the persistent loop.
+    Quantiles vs the FP64 oracle within the stated bound; cost-only mode returns identical costs."""
+    from mpcdl import synth
+    from oracle import rollout_ref as R
+    m, _ = _model(name)
+    st = gold_stats[0]
+    init, U = synth.make_inputs(synth.load_rows(), n, 50, window=0, seed=5)
+    ref64 = R.as_double(R.build_from_name(name, load_ckpt(name))[0])
+    ns = min(n, 2000)                                     # the FP64 oracle runs on a slice that spans tile boundaries
+    sl = slice(n - ns, n)
+    y64 = R.rollout_mlp(ref64, {k: v.double() for k, v in st.items()}, init[sl].double(), U[sl].double())[0]
+    cost = (torch.zeros(50, 6), torch.ones(6), torch.ones(2))
+    states, costs = m.rollout(init.to(_dev()), U.to(_dev()), st, precision=prec, cost=cost)
+    assert states.shape == (n, 50, 6) and torch.isfinite(states).all()
+    q = _quantiles(R.rel_err(states[sl].cpu(), y64))
+    for a, b in zip(q, MC_BOUNDS[prec][1]):
+        assert a <= b, (q, MC_BOUNDS[prec][1])
+    _, c2 = m.rollout(init.to(_dev()), U.to(_dev()), st, precision=prec, cost=cost, return_states=False)
+    assert torch.equal(c2, costs)
+    want = (states ** 2).sum((1, 2)) + (U.to(_dev()) ** 2).sum((1, 2))
+    assert ((costs - want).abs() / want).max().item() <= 1e-4
+    # a shard of the batch gives the same bits as the same trajectories inside the full batch
+    part = m.rollout(init[128:].contiguous().to(_dev()), U[128:].contiguous().to(_dev()), st, precision=prec)[0]
+    assert torch.equal(part, states[128:])
+
+
 def test_tensor_core_rejects_unsupported():
-    m, _ = _model("Basic_64_4_32")
-    with pytest.raises(RuntimeError):
+    m, _ = _model("Basic_16_4_32")
+    with pytest.raises(RuntimeError):           # hidden 16: FP32 kernels only, no silent fallback
         m.rollout(torch.zeros(8, 6, device=_dev()), torch.zeros(8, 3, 2, device=_dev()), None, precision="tf32x3")
     g, _ = _model("GRU_64_4_4_16_False")
     with pytest.raises(RuntimeError):           # window 3: the tcgen05 kernel is built for FT_SIZE = 4 only

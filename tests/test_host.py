@@ -231,3 +231,38 @@ def test_pack_rnn_tensor_core_layout():
                         assert np.array_equal(got, ref[:, c * kc:(c + 1) * kc]), (name, l, part, c, half)
                     pos += 2 * kc * N
         assert pos == blob.size
+
+
+def test_pack_mlp_tensor_core_layout():
+    """mpcdl_pack_mlp_tc against a numpy restatement: biases [L+1][64], FP32 output head W^T [64][8] + bias[8],
+    then per layer the tf32 hi block and lo block in canonical K-major UMMA order [k/4][n/8][n%8][k%4]."""
+    import numpy as np
+    from conftest import load_ckpt
+    from mpcdl import pack
+
+    def rna(x):
+        u = x.astype(np.float32).view(np.uint32)
+        return ((u + np.uint32(0x1000)) & np.uint32(0xFFFFE000)).view(np.float32)
+
+    for name, L in (("Basic_64_1_32", 1), ("Basic_64_2_64", 2), ("Basic_64_4_32", 4)):
+        sd = load_ckpt(name)
+        blob = pack.pack_mlp(sd, 64, L, tensor_core=True).numpy()
+        h = 64
+        for l in range(L + 1):
+            assert np.array_equal(blob[l * h:(l + 1) * h], sd[f"layers.{l}.bias"].numpy())
+        off = (L + 1) * h
+        assert np.array_equal(blob[off:off + h * 8].reshape(h, 8)[:, :6], sd[f"layers.{L + 1}.weight"].numpy().T)
+        assert np.array_equal(blob[off + h * 8:off + h * 8 + 6], sd[f"layers.{L + 1}.bias"].numpy())
+        pos = (off + h * 8 + 8 + 31) // 32 * 32
+        for l in range(L + 1):
+            W = sd[f"layers.{l}.weight"].numpy()
+            K = W.shape[1]
+            hi = rna(W)
+            lo = rna(W - hi)
+            for ref in (hi, lo):
+                blk = blob[pos:pos + K * h].reshape(K // 4, h // 8, 8, 4)
+                assert np.array_equal(blk.transpose(1, 2, 0, 3).reshape(h, K), ref), (name, l)
+                pos += K * h
+        assert pos == blob.size
+    with pytest.raises(RuntimeError):                # hidden 16: FP32 kernels only
+        pack.pack_mlp(load_ckpt("Basic_16_1_32"), 16, 1, tensor_core=True)

@@ -16,7 +16,7 @@ if [[ $what == *bench* ]]; then
     timeout 600 python bench.py --workload $wl --steps 5 --warmup 3 > gpurun_out/bench_$wl.json 2> gpurun_out/bench_$wl.err; echo "bench $wl exit $?"
   done
   for prec in tf32x3 tf32; do
-    for wl in c3 c3s c3l c5g; do
+    for wl in c2 c5 c3 c3s c3l c5g; do
       timeout 600 python bench.py --workload $wl --precision $prec --steps 5 --warmup 3 --skip-cpu > gpurun_out/bench_${wl}_$prec.json 2> gpurun_out/bench_${wl}_$prec.err; echo "bench $wl $prec exit $?"
     done
   done
@@ -33,5 +33,13 @@ if [[ $what == *ncu* ]]; then
   timeout 300 python bench.py --workload c3 --steps 2 --warmup 3 --skip-cpu > gpurun_out/plain_c3.log 2>&1 &&
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:rollout_rnn -s 1 -c 1 -f -o gpurun_out/prof_c3 \
       python bench.py --workload c3 --steps 2 --warmup 3 --skip-cpu > gpurun_out/ncu_full_c3.log 2>&1
+fi
+if [[ $what == *tcprof* ]]; then
+  timeout 300 python bench.py --workload c5 --precision tf32x3 --steps 2 --warmup 3 --skip-cpu > gpurun_out/plain_c5_tf32x3.log 2>&1 &&
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:rollout_mlp_tc -s 1 -c 1 -f -o gpurun_out/prof_c5_tf32x3 \
+      python bench.py --workload c5 --precision tf32x3 --steps 2 --warmup 3 --skip-cpu > gpurun_out/ncu_full_c5_tf32x3.log 2>&1
+  timeout 300 python bench.py --workload c3 --precision tf32x3 --steps 2 --warmup 3 --skip-cpu > gpurun_out/plain_c3_tf32x3.log 2>&1 &&
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:rollout_rnn_tc -s 1 -c 1 -f -o gpurun_out/prof_c3_tf32x3 \
+      python bench.py --workload c3 --precision tf32x3 --steps 2 --warmup 3 --skip-cpu > gpurun_out/ncu_full_c3_tf32x3.log 2>&1
 fi
 ls -la gpurun_out
