@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MPCDL_VERSION 101
+#define MPCDL_VERSION 102
 
 enum { MPCDL_MLP = 0, MPCDL_GRU = 1, MPCDL_LSTM = 2 };
 /* Arithmetic of the gate GEMMs.  FP32 = FFMA kernels (the parity path, <= 1e-5 one-step).  The tensor-core
@@ -127,6 +127,37 @@ typedef struct {
     int32_t ksplit;            /* K slices of a hidden layer (weight-resident MLP kernel)                   */
 } mpcdl_plan;
 int mpcdl_rollout_plan(const mpcdl_rollout_args* args, mpcdl_plan* plan);
+
+/* Stand-alone residual-noise net (the reference's FeedforwardNoiseModel call surface).
+ *   closed_loop = 0: FeedforwardNoiseModel.forward / get_prediction  model_scripts/noise_model.py:34-45
+ *       q [N, 6*history] (history oldest first, q order), u [N, 2*history]  ->  out [N,6] = mu + softplus(p) * eps,
+ *       optional mu / scale [N,6] (the Normal's parameters);  H must be 1, eps is [N,6].
+ *   closed_loop = 1: DynamicsNN.get_prediction (noise_model.py:113-125) fed back on itself for H steps, i.e. the
+ *       open-loop branch of run_dynamics_model (scripts/test_model.py:67-87) batched over N trajectories:
+ *       q [N,6] initial state (q order), u [N,H,2] controls  ->  out [N,H,6] (out[:,t] = q_{t+1});
+ *       the history deques start left-padded with (q0, u0) (noise_model.py:119-121); eps is [N,H,6].
+ * eps = NULL draws Philox(seed, traj_offset + n, step0 + t), the same stream as mpcdl_rollout. */
+typedef struct {
+    const float* noise_wblob;  /* device: mpcdl_pack_noise output */
+    int32_t history, size, n_layers, act;
+    int32_t closed_loop;
+    const float* q;            /* device */
+    const float* u;            /* device */
+    const float* eps;          /* device or NULL */
+    uint64_t seed;
+    int64_t traj_offset;
+    int32_t step0;
+    float* out;                /* device */
+    float* mu;                 /* device or NULL (closed_loop = 0 only) */
+    float* scale;              /* device or NULL (closed_loop = 0 only) */
+    int64_t N;
+    int32_t H;
+} mpcdl_noise_args;
+int mpcdl_noise_forward(const mpcdl_noise_args* args, void* stream);
+
+/* Per-sample error metrics of eval_models.calc_error (model_scripts/eval_models.py:91-92):
+ * mae[n] = mean_d |output[n,d] - labels[n,d]|, rmse[n] = sqrt(mean_d (output - labels)^2), d < 6; all device, FP32. */
+int mpcdl_error_metrics(const float* output, const float* labels, int64_t B, float* mae, float* rmse, void* stream);
 
 /* FP32 FFMA peak micro-kernel (register-only FMA chains on every SM); used by bench.py to measure
  * the FP32 roofline denominator on the box it runs on.  out: device buffer of >= grid*256 floats.

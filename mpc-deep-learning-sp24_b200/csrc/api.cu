@@ -621,6 +621,44 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     return MPCDL_OK;
 }
 
+int mpcdl_noise_forward(const mpcdl_noise_args* a, void* stream) {
+    if (!a) return fail(MPCDL_ERR_ARG, "args is NULL");
+    if (!a->noise_wblob || !a->q || !a->u || !a->out) return fail(MPCDL_ERR_ARG, "noise_wblob/q/u/out must be non-NULL device pointers");
+    if (a->N < 1 || a->H < 1) return fail(MPCDL_ERR_ARG, "N=%lld H=%d must be >= 1", (long long)a->N, a->H);
+    if (!a->closed_loop && a->H != 1) return fail(MPCDL_ERR_ARG, "FeedforwardNoiseModel.forward is one step: H=%d must be 1", a->H);
+    if (a->closed_loop && (a->mu || a->scale)) return fail(MPCDL_ERR_ARG, "mu/scale outputs exist for the one-step forward only");
+    if (a->history < 1 || a->history > 8) return fail(MPCDL_ERR_UNSUPPORTED, "noise history=%d outside [1,8]", a->history);
+    if (a->size < 4 || a->size > 64 || a->size % 4) return fail(MPCDL_ERR_UNSUPPORTED, "noise size=%d must be a multiple of 4 in [4,64]", a->size);
+    if (a->n_layers < 0 || a->n_layers > MAX_NOISE_LAYERS) return fail(MPCDL_ERR_UNSUPPORTED, "noise n_layers=%d outside [0,%d]", a->n_layers, MAX_NOISE_LAYERS);
+    if (a->act < MPCDL_ACT_IDENTITY || a->act > MPCDL_ACT_SIGMOID) return fail(MPCDL_ERR_UNSUPPORTED, "noise activation %d unsupported", a->act);
+    int rc = device_info();
+    if (rc) return rc;
+    if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    AuxParams p;
+    memset(&p, 0, sizeof(p));
+    p.nz.blob = a->noise_wblob; p.nz.enabled = 1; p.nz.hist = a->history; p.nz.size = a->size; p.nz.nlayers = a->n_layers;
+    p.nz.act = a->act; p.nz.in_dim = 8 * a->history;
+    p.nz.blob_floats = (int)mpcdl_noise_blob_floats(a->history, a->size, a->n_layers);
+    p.q = a->q; p.u = a->u; p.eps = a->eps; p.seed = a->seed; p.traj_offset = a->traj_offset; p.step0 = a->step0;
+    p.out = a->out; p.mu = a->mu; p.scale = a->scale; p.N = a->N; p.H = a->H;
+    p.ntiles = (int)((a->N + AUX_TN - 1) / AUX_TN);
+    const int smem = aux_smem_bytes(p.nz.blob_floats, p.nz.in_dim, p.nz.size);
+    if (smem > SMEM_LIMIT) return fail(MPCDL_ERR_UNSUPPORTED, "noise net needs %d bytes of shared memory", smem);
+    cudaError_t e = launch_aux(p, a->closed_loop != 0, std::min(p.ntiles, g_num_sms), smem, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "noise kernel launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+int mpcdl_error_metrics(const float* output, const float* labels, int64_t B, float* mae, float* rmse, void* stream) {
+    if (!output || !labels || !mae || !rmse || B < 1) return fail(MPCDL_ERR_ARG, "mpcdl_error_metrics: bad arguments");
+    int rc = device_info();
+    if (rc) return rc;
+    if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    cudaError_t e = launch_error_metrics(output, labels, B, mae, rmse, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "error_metrics launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
 int mpcdl_ffma_peak(float* out_device, int iters, int grid, void* stream) {
     if (!out_device || iters < 1 || grid < 1) return fail(MPCDL_ERR_ARG, "mpcdl_ffma_peak: bad arguments");
     cudaError_t e = launch_ffma_peak(out_device, iters, grid, static_cast<cudaStream_t>(stream));

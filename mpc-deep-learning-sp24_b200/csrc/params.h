@@ -52,6 +52,23 @@ struct RolloutParams {
     NoiseParams nz;
 };
 
+// standalone noise-net entry points (aux_kernels.cu): forward (H = 1, explicit history) and DynamicsNN closed loop
+struct AuxParams {
+    NoiseParams nz;
+    const float* q;          // forward: [N, 6*hist] history (oldest first); closed loop: q0 [N,6]
+    const float* u;          // forward: [N, 2*hist];                          closed loop: U [N,H,2]
+    const float* eps;        // [N,H,6] or null (-> Philox(seed, traj_offset + n, step0 + t))
+    unsigned long long seed;
+    long long traj_offset;
+    int step0;
+    float* out;              // [N,H,6]
+    float* mu;               // forward only, optional [N,6]
+    float* scale;            // forward only, optional [N,6]
+    long long N;
+    int H;
+    int ntiles;
+};
+
 // ------------------------------------------------------------------ shared-memory layout (float offsets)
 struct SmemLayout {
     int bars;        // 2*nslots uint64

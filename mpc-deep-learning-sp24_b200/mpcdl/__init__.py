@@ -5,9 +5,9 @@ library has not been built (no fallback).
 """
 from . import _lib, ops, pack, data, synth, parallel  # noqa: F401
 from .models import (Basic_Model, GRU_Model, LSTM_Model, FeedforwardNoiseModel, build_mlp,   # noqa: F401
-                     from_checkpoint_name)
+                     CasadiDynamicCLBicycleNoise, DynamicsNN, from_checkpoint_name)
 from .data import RobotData, zscore_stats              # noqa: F401
 
 INPUTS, OUTPUT = 8, 6                                  # basic_model.py:63-64, deep_models.py:94-95
-__all__ = ["Basic_Model", "GRU_Model", "LSTM_Model", "FeedforwardNoiseModel", "RobotData", "zscore_stats",
+__all__ = ["Basic_Model", "GRU_Model", "LSTM_Model", "FeedforwardNoiseModel", "CasadiDynamicCLBicycleNoise", "DynamicsNN", "RobotData", "zscore_stats",
            "from_checkpoint_name", "ops", "pack", "data", "synth", "parallel"]

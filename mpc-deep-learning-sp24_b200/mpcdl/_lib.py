@@ -53,6 +53,21 @@ class RolloutArgs(C.Structure):
     ]
 
 
+class NoiseArgs(C.Structure):
+    _fields_ = [
+        ("noise_wblob", C.c_void_p),
+        ("history", C.c_int32), ("size", C.c_int32), ("n_layers", C.c_int32), ("act", C.c_int32),
+        ("closed_loop", C.c_int32),
+        ("q", C.c_void_p), ("u", C.c_void_p), ("eps", C.c_void_p),
+        ("seed", C.c_uint64),
+        ("traj_offset", C.c_int64),
+        ("step0", C.c_int32),
+        ("out", C.c_void_p), ("mu", C.c_void_p), ("scale", C.c_void_p),
+        ("N", C.c_int64),
+        ("H", C.c_int32),
+    ]
+
+
 class Plan(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("rt", "rj", "n_tg", "tile_traj", "threads", "grid", "smem_bytes",
                                          "resident", "nslots", "slot_floats", "ntiles", "variant", "ksplit")]
@@ -62,7 +77,7 @@ class Plan(C.Structure):
 
 
 EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_pack_mlp_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
-           "mpcdl_rollout", "mpcdl_rollout_plan", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version")
+           "mpcdl_rollout", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version")
 
 
 def _load():
@@ -92,6 +107,10 @@ def _load():
     lib.mpcdl_rollout.argtypes = [C.POINTER(RolloutArgs), C.c_void_p]
     lib.mpcdl_rollout_plan.restype = C.c_int
     lib.mpcdl_rollout_plan.argtypes = [C.POINTER(RolloutArgs), C.POINTER(Plan)]
+    lib.mpcdl_noise_forward.restype = C.c_int
+    lib.mpcdl_noise_forward.argtypes = [C.POINTER(NoiseArgs), C.c_void_p]
+    lib.mpcdl_error_metrics.restype = C.c_int
+    lib.mpcdl_error_metrics.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.mpcdl_ffma_peak.restype = C.c_int
     lib.mpcdl_ffma_peak.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.mpcdl_last_error.restype = C.c_char_p

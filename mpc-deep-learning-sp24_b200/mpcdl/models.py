@@ -278,6 +278,26 @@ class FeedforwardNoiseModel(nn.Module):
         return self._packed.get(list(self.model.parameters()), device,
                                 lambda: pack.pack_noise(self.model.state_dict(), self.history, self.size, self.n_layers))
 
+    def forward(self, q, u, eps=None, return_params=False):
+        """q [B,6*history] (q order, oldest first), u [B,2*history] -> Normal(mu, softplus(p)).rsample() [B,6]
+        (noise_model.py:34-40) in one kernel launch.  The reference draws eps from torch's global RNG;
+        here eps is either supplied ([B,6], the parity path) or drawn in-kernel by Philox keyed with
+        ``torch.initial_seed()`` and a per-module call counter (reproducible under torch.manual_seed)."""
+        q, u = q.contiguous(), u.contiguous()
+        self._calls = getattr(self, "_calls", 0) + (eps is None)
+        out, mu, scale = torch.ops.mpcdl.noise_forward(self.packed(q.device), self.cfg(), q, u, eps,
+                                                       int(torch.initial_seed()) & 0x7FFFFFFFFFFFFFFF, 0, self._calls, bool(return_params))
+        return (out, mu, scale) if return_params else out
+
+    def get_prediction(self, q, u, eps=None):
+        """numpy in, numpy out (noise_model.py:42-45); the arrays go to the device the parameters live on."""
+        import numpy as np
+        dev = next(self.model.parameters()).device
+        qt = torch.from_numpy(np.ascontiguousarray(q, dtype=np.float32)).to(dev)
+        ut = torch.from_numpy(np.ascontiguousarray(u, dtype=np.float32)).to(dev)
+        et = None if eps is None else torch.from_numpy(np.ascontiguousarray(eps, dtype=np.float32)).to(dev)
+        return self(qt, ut, et).cpu().numpy()
+
     def export(self, path="../model_data", name="noise_model.pkl"):
         import os
         torch.save(self.model.state_dict(), os.path.join(path, name))
@@ -285,6 +305,99 @@ class FeedforwardNoiseModel(nn.Module):
     def load(self, path="../model_data", name="noise_model.pkl"):
         import os
         self.model.load_state_dict(torch.load(os.path.join(path, name), map_location="cpu"))
+
+
+Q_PERM = [4, 5, 3, 0, 1, 2]    # q = frame-order state[Q_PERM]   (noise_model.py:108, utils/data_utils.py:47-49)
+Q_INV = [3, 4, 5, 2, 0, 1]     # state = q[Q_INV]
+
+
+class CasadiDynamicCLBicycleNoise:
+    """nominal step + learned residual noise (noise_model.py:54-111), same constructor and methods.
+
+    The reference's nominal model is the CasADi bicycle of ``mpclab_common`` -- a private submodule that is not
+    in the tree.  Here ``nominal_model`` is either one of the learned dynamics modules of this
+    package (``Basic_Model`` / ``GRU_Model`` / ``LSTM_Model``: the substitution BASELINE.json's north_star makes)
+    together with its z-score ``stats``, or any object with the reference's ``qu2state / step / state2q``
+    protocol (then ``vehicle_state`` must be passed in, there is no VehicleState type here).
+    ``get_prediction`` keeps the reference's batch-1, stateful-deque semantics; ``rollout`` is the fused,
+    batched form of calling it in the open-loop feedback of run_dynamics_model (scripts/test_model.py:67-87)."""
+
+    def __init__(self, nominal_model, noise_model, dynamics_uses_frenet, track=None, history=1, stats=None):
+        from collections import deque
+        if dynamics_uses_frenet:
+            raise RuntimeError("mpcdl: Frenet-frame dynamics need mpclab_common's track (absent); use global coordinates")
+        self.nominal_model, self.noise_model = nominal_model, noise_model
+        self.dynamics_uses_frenet, self.track, self.history, self.stats = dynamics_uses_frenet, track, history, stats
+        self.q_buffer, self.u_buffer = deque(maxlen=history), deque(maxlen=history)
+
+    def _device(self):
+        return next(self.noise_model.model.parameters()).device
+
+    def get_nominal_prediction(self, q, u, vehicle_state=None):
+        import numpy as np
+        assert q.shape == (6,) and u.shape == (2,), f"Got unexpected shape: q={q.shape}, u={u.shape}"
+        m = self.nominal_model
+        if isinstance(m, Basic_Model):
+            dev = self._device()
+            s0 = torch.from_numpy(np.asarray(q, dtype=np.float32)[Q_INV][None].copy()).to(dev)
+            U = torch.from_numpy(np.asarray(u, dtype=np.float32)[None, None].copy()).to(dev)
+            return m.rollout(s0, U, self.stats)[0][0, 0].cpu().numpy()[Q_PERM]
+        if hasattr(m, "qu2state"):
+            if vehicle_state is None:
+                raise RuntimeError("mpcdl: pass vehicle_state (mpclab_common's VehicleState is not available here)")
+            m.qu2state(vehicle_state, q, u)
+            m.step(vehicle_state)
+            return m.state2q(vehicle_state)
+        raise RuntimeError("mpcdl: nominal_model must be a Basic_Model or follow the qu2state/step/state2q protocol "
+                           "(window models are rolled out with .rollout)")
+
+    def _push(self, q, u):
+        self.q_buffer.append(q)
+        self.u_buffer.append(u)
+        while len(self.q_buffer) < self.history:       # noise_model.py:97-99
+            self.q_buffer.append(q)
+            self.u_buffer.append(u)
+
+    def get_prediction(self, q, u, vehicle_state=None, eps=None):
+        import numpy as np
+        assert len(q.shape) == 1 and len(u.shape) == 1
+        self._push(q, u)
+        nominal_next_q = self.get_nominal_prediction(q, u, vehicle_state)
+        noise = self.noise_model.get_prediction(np.asarray(self.q_buffer).reshape(1, -1),
+                                                np.asarray(self.u_buffer).reshape(1, -1), eps)
+        return nominal_next_q + noise
+
+    def rollout(self, q0, U, eps=None, seed=0, traj_offset=0, **kw):
+        """q0 [N,6] (q order; or a frame-order window [N,T,8] for GRU/LSTM nominal models), U [N,H,2] ->
+        predicted q [N,H,6]: nominal learned step + residual noise, the whole horizon in one launch."""
+        m = self.nominal_model
+        if not isinstance(m, _RolloutMixin):
+            raise RuntimeError("mpcdl: the fused rollout needs a learned nominal model of this package")
+        init = q0[:, Q_INV].contiguous() if q0.dim() == 2 else q0
+        states = m.rollout(init, U, self.stats, noise=self.noise_model, eps=eps, seed=seed, traj_offset=traj_offset, **kw)[0]
+        return states[:, :, Q_PERM]
+
+    def step(self, state):
+        raise NotImplementedError("mpcdl: VehicleState stepping belongs to mpclab_common (absent)")
+
+
+class DynamicsNN(CasadiDynamicCLBicycleNoise):
+    """The noise net as the whole dynamics (noise_model.py:113-128): next q = sample of the net."""
+
+    def get_prediction(self, q, u, vehicle_state=None, eps=None):
+        import numpy as np
+        assert len(q.shape) == 1 and len(u.shape) == 1
+        self._push(q, u)
+        return self.noise_model.get_prediction(np.asarray(self.q_buffer).reshape(1, -1),
+                                               np.asarray(self.u_buffer).reshape(1, -1), eps)
+
+    def rollout(self, q0, U, eps=None, seed=0, traj_offset=0):
+        """q0 [N,6], U [N,H,2] -> [N,H,6]; out[:,t] = get_prediction(out[:,t-1], U[:,t]) with fresh deques."""
+        nm = self.noise_model
+        if nm.history != self.history:
+            raise RuntimeError(f"mpcdl: wrapper history {self.history} != noise model history {nm.history}")
+        return torch.ops.mpcdl.dynamics_nn_rollout(nm.packed(U.device), nm.cfg(), q0.contiguous(), U.contiguous(), eps,
+                                                   int(seed), int(traj_offset))
 
 
 def from_checkpoint_name(name, sd=None, device=None):

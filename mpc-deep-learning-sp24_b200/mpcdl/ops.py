@@ -127,6 +127,97 @@ _libimpl.impl("rollout_mlp", _make(_lib.MLP))
 _libimpl.impl("rollout_gru", _make(_lib.GRU))
 _libimpl.impl("rollout_lstm", _make(_lib.LSTM))
 
+
+
+# ---------------------------------------------------------------------------- noise net / error metrics
+_libdef.define("noise_forward(Tensor noise_wblob, int[] noise_cfg, Tensor q, Tensor u, Tensor? eps, int seed, "
+               "int traj_offset, int step0, bool return_params) -> (Tensor, Tensor, Tensor)")
+_libdef.define("dynamics_nn_rollout(Tensor noise_wblob, int[] noise_cfg, Tensor q0, Tensor U, Tensor? eps, int seed, "
+               "int traj_offset) -> Tensor")
+_libdef.define("error_metrics(Tensor output, Tensor labels) -> (Tensor, Tensor)")
+
+
+def _noise_args(noise_wblob, noise_cfg, dev):
+    hist, size, nl, act = noise_cfg
+    if noise_wblob.numel() != _lib.lib.mpcdl_noise_blob_floats(hist, size, nl):
+        raise RuntimeError("mpcdl: noise_wblob size does not match noise_cfg")
+    a = _lib.NoiseArgs()
+    a.noise_wblob = _f32c(noise_wblob, "noise_wblob", dev)
+    a.history, a.size, a.n_layers, a.act = hist, size, nl, act
+    return a
+
+
+def _launch_noise(a, dev):
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(_lib.lib.mpcdl_noise_forward(C.byref(a), C.c_void_p(stream)))
+
+
+def _noise_forward_impl(noise_wblob, noise_cfg, q, u, eps, seed, traj_offset, step0, return_params):
+    """FeedforwardNoiseModel.forward (model_scripts/noise_model.py:34-40): q [B,6*hist], u [B,2*hist] -> [B,6]."""
+    dev = q.device
+    a = _noise_args(noise_wblob, noise_cfg, dev)
+    hist = a.history
+    if q.dim() != 2 or q.shape[1] != 6 * hist or tuple(u.shape) != (q.shape[0], 2 * hist):
+        raise RuntimeError(f"mpcdl: noise forward needs q [B,{6 * hist}] and u [B,{2 * hist}], got {tuple(q.shape)} {tuple(u.shape)}")
+    B = int(q.shape[0])
+    a.q, a.u = _f32c(q, "q", dev), _f32c(u, "u", dev)
+    if eps is not None:
+        if tuple(eps.shape) != (B, 6):
+            raise RuntimeError(f"mpcdl: eps must be [B,6], got {tuple(eps.shape)}")
+        a.eps = _f32c(eps, "eps", dev)
+    a.seed, a.traj_offset, a.step0 = seed & 0xFFFFFFFFFFFFFFFF, traj_offset, step0
+    out = torch.empty((B, 6), device=dev, dtype=torch.float32)
+    mu = torch.empty((B, 6) if return_params else (0,), device=dev, dtype=torch.float32)
+    scale = torch.empty((B, 6) if return_params else (0,), device=dev, dtype=torch.float32)
+    a.out = out.data_ptr()
+    if return_params:
+        a.mu, a.scale = mu.data_ptr(), scale.data_ptr()
+    a.N, a.H = B, 1
+    _launch_noise(a, dev)
+    return out, mu, scale
+
+
+def _dynnn_rollout_impl(noise_wblob, noise_cfg, q0, U, eps, seed, traj_offset):
+    """DynamicsNN.get_prediction fed back on itself (noise_model.py:113-125, test_model.py:67-87), fused over H."""
+    dev = U.device
+    a = _noise_args(noise_wblob, noise_cfg, dev)
+    if U.dim() != 3 or U.shape[2] != 2 or tuple(q0.shape) != (U.shape[0], 6):
+        raise RuntimeError(f"mpcdl: DynamicsNN rollout needs q0 [N,6] and U [N,H,2], got {tuple(q0.shape)} {tuple(U.shape)}")
+    N, H = int(U.shape[0]), int(U.shape[1])
+    a.closed_loop = 1
+    a.q, a.u = _f32c(q0, "q0", dev), _f32c(U, "U", dev)
+    if eps is not None:
+        if tuple(eps.shape) != (N, H, 6):
+            raise RuntimeError(f"mpcdl: eps must be [N,H,6], got {tuple(eps.shape)}")
+        a.eps = _f32c(eps, "eps", dev)
+    a.seed, a.traj_offset = seed & 0xFFFFFFFFFFFFFFFF, traj_offset
+    out = torch.empty((N, H, 6), device=dev, dtype=torch.float32)
+    a.out = out.data_ptr()
+    a.N, a.H = N, H
+    _launch_noise(a, dev)
+    return out
+
+
+def _error_metrics_impl(output, labels):
+    """Per-sample MAE / RMSE of eval_models.calc_error (model_scripts/eval_models.py:91-92)."""
+    dev = output.device
+    if output.dim() != 2 or output.shape[1] != 6 or output.shape != labels.shape:
+        raise RuntimeError(f"mpcdl: error_metrics needs output and labels [B,6], got {tuple(output.shape)} {tuple(labels.shape)}")
+    B = int(output.shape[0])
+    mae = torch.empty(B, device=dev, dtype=torch.float32)
+    rmse = torch.empty(B, device=dev, dtype=torch.float32)
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(_lib.lib.mpcdl_error_metrics(C.c_void_p(_f32c(output, "output", dev)), C.c_void_p(_f32c(labels, "labels", dev)),
+                                               B, C.c_void_p(mae.data_ptr()), C.c_void_p(rmse.data_ptr()), C.c_void_p(stream)))
+    return mae, rmse
+
+
+_libimpl.impl("noise_forward", _noise_forward_impl)
+_libimpl.impl("dynamics_nn_rollout", _dynnn_rollout_impl)
+_libimpl.impl("error_metrics", _error_metrics_impl)
+
 OPS = {_lib.MLP: torch.ops.mpcdl.rollout_mlp, _lib.GRU: torch.ops.mpcdl.rollout_gru, _lib.LSTM: torch.ops.mpcdl.rollout_lstm}
 
 

@@ -75,3 +75,62 @@ def sharded_rollout(rollout_fn, init, U, *, eps=None, group=None, **kw):
 def mppi_weights(costs: torch.Tensor, lam: float = 1.0) -> torch.Tensor:
     """softmin weights of an MPPI update, computed redundantly on every rank from the gathered costs."""
     return torch.softmax(-(costs - costs.min()) / lam, dim=0)
+
+
+class HostPipeline:
+    """Host-buffer driver of the rollout: copy-in, kernel and copy-out of consecutive batches overlap.
+
+    A planner that keeps its control samples in host memory pays H2D(init, U) + kernel + D2H(result) per call;
+    issued on one stream they serialise (C2: 0.42 ms per call against a 0.28 ms kernel).  The pipeline gives every
+    in-flight batch its own device input buffers and runs the three stages on three streams (copy-in, the caller's
+    current stream for the kernel, copy-out), so batch i+1 is uploaded and batch i-1 downloaded while batch i
+    computes.  Every batch still moves all of its bytes; only the waiting is overlapped.
+
+        pipe = HostPipeline(lambda init, U: model.rollout(init, U, stats)[0], depth=2)
+        pipe.submit((init_pinned, U_pinned), out_pinned)      # returns at once
+        pipe.drain()                                          # current stream (and host, if sync=True) waits
+
+    ``fn(*device_inputs) -> Tensor`` runs on the current stream; host tensors must be pinned for real overlap."""
+
+    def __init__(self, fn, depth: int = 2, device=None):
+        self.fn, self.depth = fn, max(1, int(depth))
+        self.dev = torch.device(device if device is not None else ("cuda", torch.cuda.current_device()))
+        self.s_in, self.s_out = torch.cuda.Stream(self.dev), torch.cuda.Stream(self.dev)
+        self.slots = [dict(bufs=None, used=None, done=None) for _ in range(self.depth)]
+        self.k = 0
+
+    def submit(self, host_inputs, host_out):
+        slot = self.slots[self.k % self.depth]
+        self.k += 1
+        cur = torch.cuda.current_stream(self.dev)
+        if slot["bufs"] is None or any(b.shape != h.shape for b, h in zip(slot["bufs"], host_inputs)):
+            slot["bufs"] = [torch.empty(h.shape, dtype=h.dtype, device=self.dev) for h in host_inputs]
+        if slot["used"] is not None:
+            self.s_in.wait_event(slot["used"])          # the kernel that last read these buffers has finished
+        else:
+            self.s_in.wait_stream(cur)
+        with torch.cuda.stream(self.s_in):
+            for b, h in zip(slot["bufs"], host_inputs):
+                b.copy_(h, non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record(self.s_in)
+        cur.wait_event(ready)
+        res = self.fn(*slot["bufs"])
+        slot["used"] = torch.cuda.Event()
+        slot["used"].record(cur)
+        if slot["done"] is not None:
+            self.s_out.wait_event(slot["done"])
+        self.s_out.wait_event(slot["used"])
+        res.record_stream(self.s_out)
+        with torch.cuda.stream(self.s_out):
+            host_out.copy_(res, non_blocking=True)
+            slot["done"] = torch.cuda.Event()
+            slot["done"].record(self.s_out)
+        return res
+
+    def drain(self, sync: bool = False):
+        cur = torch.cuda.current_stream(self.dev)
+        cur.wait_stream(self.s_out)
+        cur.wait_stream(self.s_in)
+        if sync:
+            cur.synchronize()

@@ -216,6 +216,74 @@ with torch.no_grad():
         ok = ok and np.array_equal(pr, my_noise(qq, uu, e).numpy())
 check("a7 DynamicsNN.get_prediction history/left-pad semantics bit-identical (6 calls)", ok)
 
+# ---------------------------------------------------------------------------- 3d. run_dynamics_model (a8)
+sys.modules["mpclab_common.models.dynamics_models"].DynamicBicycleConfig = object
+import scripts.test_model as tm  # noqa: E402   (the reference's own loop, scripts/test_model.py:67-87)
+import model_scripts.noise_model as nm2  # noqa: E402  (test_model imports the package path: a second module object)
+
+
+class _IdentityNominal:
+    """stand-in for the missing CasADi bicycle (mpclab_common): next q = q.  Only q_nominal uses it."""
+    def qu2state(self, state, q, u): state.q = q
+    def step(self, state): pass
+    def state2q(self, state): return state.q
+
+
+aux = {}
+Tn = 24
+q_data = rows32[:Tn, R.Q_PERM]
+u_data = rows32[:Tn, 6:8]
+dataset_h1 = [(q_data[k][None].numpy(), u_data[k][None].numpy(), None) for k in range(Tn)]
+for open_loop in (True, False):
+    dyn2 = nm2.DynamicsNN(_IdentityNominal(), ref_noise, False, history=3)
+    with torch.no_grad():
+        torch.manual_seed(11)
+        (qd, qn, qz), _ = tm.run_dynamics_model(dyn2, dataset_h1, open_loop)
+        torch.manual_seed(11)
+        eps_dyn = torch.stack([torch.randn(1, 6) for _ in range(Tn - 1)])[:, 0]
+    mine_tr = R.run_dynamics_model(my_noise, q_data, u_data, eps_dyn, open_loop)
+    ref_tr = torch.from_numpy(np.stack([np.asarray(x, dtype=np.float32) for x in qz]))
+    check(f"a8 run_dynamics_model(open_loop={open_loop}) 'with noise' trajectory: oracle == reference (bit)", bit_equal(ref_tr, mine_tr))
+    aux["rdm_open" if open_loop else "rdm_closed"] = ref_tr.numpy()
+aux["rdm_q"], aux["rdm_u"], aux["rdm_eps"] = q_data.numpy(), u_data.numpy(), eps_dyn.numpy()
+# the batched closed loop restates the same recursion (q0 = q_data[0], U[t] = u_data[t+1])
+tr_b = R.rollout_dynnn(my_noise, q_data[:1], u_data[None, 1:], eps_dyn[None])
+check("a7/a8 rollout_dynnn (batched) == run_dynamics_model(open_loop=True)", bit_equal(tr_b[0], torch.from_numpy(aux["rdm_open"][1:])))
+aux["noise_q"], aux["noise_u"], aux["noise_eps"], aux["noise_out"] = qh.numpy(), uh.numpy(), eps.numpy(), nr.numpy()
+mu_, sc_ = my_noise.mu_scale(qh, uh)
+aux["noise_mu"], aux["noise_scale"] = mu_.detach().numpy(), sc_.detach().numpy()
+Nd, Hd = 300, 40
+qd0 = rows32[torch.arange(Nd) * 7 % 4000][:, R.Q_PERM].contiguous()
+_, Ud = synth.make_inputs(synth.load_rows(), Nd, Hd, window=0, seed=4)
+epsd = synth.make_eps(Nd, Hd, seed=5)
+aux["dyn_q0"], aux["dyn_U"], aux["dyn_eps"] = qd0.numpy(), Ud.numpy(), epsd.numpy()
+aux["dyn_out"] = R.rollout_dynnn(my_noise, qd0, Ud, epsd).numpy()
+
+# a9 SAMPLE=True branch under a seeded python RNG (eval_models.py:70-75)
+import random  # noqa: E402
+ev.SAMPLE, ev.EPOCHS = True, 2000
+for name, ds_ref, feats, labs in (("Basic_64_4_32", ref_ds, mfn, mln), ("GRU_64_4_4_16_True", ref_rds, rfn, rln)):
+    p = name.split("_")
+    if p[0] == "Basic":
+        ref_m = fwd.Basic_Model(8, int(p[1]), 6, int(p[2]), False).cpu().eval()
+        ref_m.load_state_dict(torch.load(f"{REF}/model_data/fwd_models/{name}.pt", map_location="cpu"))
+        state_f = False
+    else:
+        ref_m = rnn.GRU_Model(8, int(p[1]), 6, int(p[2]), True).cpu().eval()
+        ref_m.load_state_dict(torch.load(f"{REF}/model_data/rnn_models/{name}.pt", map_location="cpu"))
+        state_f = True
+    random.seed(5)
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        ev.calc_error(ds_ref, ref_m, name, state_f)
+    printed = [float(l.split(":")[1]) for l in buf.getvalue().splitlines() if ":" in l]
+    random.seed(5)
+    mae_s, rmse_s = R.calc_error_sampled(torch.from_numpy(onestep[name]), labs, 2000, random)
+    check(f"a9 {name} calc_error SAMPLE=True seed 5 {printed} vs oracle ({mae_s:.4f},{rmse_s:.4f})",
+          abs(printed[0] - mae_s) < 1e-4 and abs(printed[1] - rmse_s) < 1e-4)
+    aux[name + "_err_sampled"] = np.asarray([mae_s, rmse_s])
+np.savez_compressed(f"{GOLD}/aux.npz", **aux)
+
 # ---------------------------------------------------------------------------- 4. golden rollouts
 rows = synth.load_rows()
 gold = {}

@@ -282,6 +282,50 @@ def calc_error(outputs, labels):
     return d.abs().mean(dim=1).mean().item(), d.pow(2).mean(dim=1).sqrt().mean().item()
 
 
+def calc_error_sampled(outputs, labels, epochs, rng):
+    """SAMPLE=True branch (eval_models.py:70-75): `epochs` draws of random.randint(0, len-1) from `rng`
+    (a random.Random or the random module), sums accumulated in Python floats in draw order (:91-96).
+    outputs / labels: the model output and label of EVERY dataset sample [B,6]."""
+    d = outputs - labels
+    mae, rmse = d.abs().mean(dim=1), d.pow(2).mean(dim=1).sqrt()
+    diff = rm = 0.0
+    for _ in range(epochs):
+        i = rng.randint(0, len(outputs) - 1)
+        diff += mae[i].item()
+        rm += rmse[i].item()
+    return diff / epochs, rm / epochs
+
+
+# --------------------------------------------------------------------------------------
+# a7 / a8  DynamicsNN closed loop            noise_model.py:113-125, scripts/test_model.py:67-87
+# --------------------------------------------------------------------------------------
+@torch.no_grad()
+def rollout_dynnn(noise, q0, U, eps):
+    """q_{t+1} = noise(history of q, history of u): DynamicsNN.get_prediction fed back on itself (the
+    open_loop=True branch of run_dynamics_model with the noise net as the whole dynamics), batched.
+    q0 [N,6] in q order, U [N,H,2] (U[:,t] = the control passed with q_t), eps [N,H,6] -> [N,H,6]."""
+    hist, q, out = _NoiseHistory(noise.history), q0, []
+    for t in range(U.shape[1]):
+        qh, uh = hist.push(q, U[:, t])
+        q = noise(qh, uh, eps[:, t])
+        out.append(q)
+    return torch.stack(out, 1)
+
+
+@torch.no_grad()
+def run_dynamics_model(noise, q_data, u_data, eps, open_loop):
+    """The `with noise` trajectory of run_dynamics_model (test_model.py:67-87) for a DynamicsNN model and a
+    dataset of history 1: q_noised[0] = q_data[0]; q_noised[k] = get_prediction(q_noised[k-1] if open_loop else
+    q_data[k], u_data[k]) for k >= 1 (note the control index: the CURRENT sample's u, :83).
+    q_data [T,6] (q order), u_data [T,2], eps [T-1,6] -> [T,6]."""
+    hist, out = _NoiseHistory(noise.history), [q_data[0]]
+    for k in range(1, len(q_data)):
+        q = out[-1] if open_loop else q_data[k]
+        qh, uh = hist.push(q[None], u_data[k][None])
+        out.append(noise(qh, uh, eps[k - 1][None])[0])
+    return torch.stack(out)
+
+
 # --------------------------------------------------------------------------------------
 # error metric used by every tolerance in tests/ and DESIGN.md (SURVEY.md 8c)
 # --------------------------------------------------------------------------------------

@@ -51,6 +51,11 @@ def gold_rollouts():
 
 
 @pytest.fixture(scope="session")
+def gold_aux():
+    return np.load(os.path.join(GOLD, "aux.npz"))
+
+
+@pytest.fixture(scope="session")
 def bags():
     from mpcdl import synth
     return synth.load_bags("mpc_data_clean")

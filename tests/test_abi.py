@@ -54,6 +54,28 @@ def test_status_codes_without_device():
     assert lib.mpcdl_rollout(None, None) == -1
 
 
+def test_noise_entry_points_without_device():
+    """mpcdl_noise_forward / mpcdl_error_metrics: argument checks come before any device work."""
+    from mpcdl import _lib
+    lib = _lib.lib
+    assert C.sizeof(_lib.NoiseArgs) == 120 and _lib.NoiseArgs.q.offset == 32 and _lib.NoiseArgs.N.offset == 104
+    assert lib.mpcdl_noise_forward(None, None) == -1
+    a = _lib.NoiseArgs()
+    assert lib.mpcdl_noise_forward(C.byref(a), None) == -1               # null pointers
+    for f in ("noise_wblob", "q", "u", "out"):
+        setattr(a, f, 16)
+    a.history, a.size, a.n_layers, a.act, a.N, a.H = 3, 32, 2, 2, 8, 2
+    assert lib.mpcdl_noise_forward(C.byref(a), None) == -1               # one-step forward with H = 2
+    assert b"H=2" in lib.mpcdl_last_error()
+    a.H, a.size = 1, 30
+    assert lib.mpcdl_noise_forward(C.byref(a), None) == -2               # size not a multiple of 4
+    a.size, a.history = 32, 9
+    assert lib.mpcdl_noise_forward(C.byref(a), None) == -2
+    a.history, a.closed_loop, a.mu = 3, 1, 16
+    assert lib.mpcdl_noise_forward(C.byref(a), None) == -1               # mu/scale exist for the forward only
+    assert lib.mpcdl_error_metrics(None, None, 4, None, None, None) == -1
+
+
 def test_plans_fit_the_machine():
     from mpcdl import _lib, ops
     for kind, hid, layers, win, n, h in [(0, 64, 4, 0, 4096, 50), (0, 16, 1, 0, 1000, 50), (0, 256, 4, 0, 65536, 10),

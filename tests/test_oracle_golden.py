@@ -91,3 +91,52 @@ def test_fp32_vs_fp64_one_step_is_tight(gold_stats):
     st64 = {k: v.double() for k, v in gold_stats[0].items()}
     y64 = R.rollout_mlp(R.as_double(m), st64, s0.double(), U.double())[0]
     assert R.rel_err(y32, y64).max().item() < 2e-6
+
+
+# ------------------------------------------------------------------ a6 / a7 / a8 / a9 goldens (tests/golden/aux.npz)
+def _noise_oracle():
+    m = R.RefNoise(6, 2, 3, 2, 32, "tanh", "identity")
+    m.model.load_state_dict(load_ckpt("noise_seed0_h3_s32_l2"))
+    return m.eval()
+
+
+def test_noise_forward_matches_reference_golden(gold_aux):
+    """a6: the golden output came from the reference FeedforwardNoiseModel.forward under a shared seed."""
+    g = gold_aux
+    m = _noise_oracle()
+    with torch.no_grad():
+        out = m(torch.from_numpy(g["noise_q"]), torch.from_numpy(g["noise_u"]), torch.from_numpy(g["noise_eps"]))
+    assert torch.equal(out, torch.from_numpy(g["noise_out"]))
+
+
+@pytest.mark.parametrize("open_loop", [True, False])
+def test_run_dynamics_model_matches_reference_golden(open_loop, gold_aux):
+    """a8: the golden trajectory came from the reference's own run_dynamics_model loop around its DynamicsNN."""
+    g = gold_aux
+    tr = R.run_dynamics_model(_noise_oracle(), torch.from_numpy(g["rdm_q"]), torch.from_numpy(g["rdm_u"]),
+                              torch.from_numpy(g["rdm_eps"]), open_loop)
+    assert torch.equal(tr, torch.from_numpy(g["rdm_open" if open_loop else "rdm_closed"]))
+
+
+def test_rollout_dynnn_batched_is_the_same_recursion(gold_aux):
+    g = gold_aux
+    m = _noise_oracle()
+    q, u, e = (torch.from_numpy(g[k]) for k in ("rdm_q", "rdm_u", "rdm_eps"))
+    tr = R.rollout_dynnn(m, q[:1], u[None, 1:], e[None])
+    assert torch.equal(tr[0], torch.from_numpy(g["rdm_open"][1:]))
+    out = R.rollout_dynnn(m, torch.from_numpy(g["dyn_q0"]), torch.from_numpy(g["dyn_U"]), torch.from_numpy(g["dyn_eps"]))
+    assert torch.equal(out, torch.from_numpy(g["dyn_out"]))
+    # a row of the batch is independent of the rest of the batch
+    one = R.rollout_dynnn(m, torch.from_numpy(g["dyn_q0"][7:8]), torch.from_numpy(g["dyn_U"][7:8]), torch.from_numpy(g["dyn_eps"][7:8]))
+    assert torch.allclose(one[0], out[7], rtol=0, atol=1e-6)
+
+
+def test_calc_error_sampled_matches_reference_golden(gold_aux, gold_onestep, bags):
+    """a9 SAMPLE=True: same random.randint stream as the reference -> the values its calc_error printed."""
+    import random
+    from mpcdl import RobotData
+    for name, size in (("Basic_64_4_32", None), ("GRU_64_4_4_16_True", 4)):
+        ds = RobotData(bags, size)
+        random.seed(5)
+        mae, rmse = R.calc_error_sampled(torch.from_numpy(gold_onestep[name]), ds.labels, 2000, random)
+        assert (mae, rmse) == tuple(gold_aux[name + "_err_sampled"])
