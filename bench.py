@@ -58,6 +58,12 @@ WORKLOADS = {
                N=1048576, H=50, noise=False, states=False, flop=34560, cpu_n=65536),
     "c5g": dict(desc="C5 GRU_64_4_4_16_False, 1048576 x horizon 100, cost-only", ckpt="GRU_64_4_4_16_False",
                 N=1048576, H=100, noise=False, states=False, flop=701184, cpu_n=2048),
+    # MPPI planner iteration: controls sampled in-kernel around a nominal sequence, cost-only rollout,
+    # softmin update; host traffic per iteration = one state + the nominal sequence in, the new sequence out
+    "c5m": dict(desc="MPPI iteration, MLP Basic_64_4_32, 1048576 samples x horizon 50 (in-kernel control sampling + softmin update)",
+                ckpt="Basic_64_4_32", N=1048576, H=50, noise=False, states=False, flop=34560, cpu_n=65536, mppi=True),
+    "c5gm": dict(desc="MPPI iteration, GRU_64_4_4_16_False, 1048576 samples x horizon 100 (in-kernel control sampling + softmin update)",
+                 ckpt="GRU_64_4_4_16_False", N=1048576, H=100, noise=False, states=False, flop=701184, cpu_n=2048, mppi=True),
 }
 
 
@@ -229,7 +235,7 @@ def run_native(args, w):
         dist.init_process_group("nccl", device_id=dev)
     N, H = w["N"], w["H"]
 
-    meta, init_h, U_h, cost = make_problem(w, seed=rank)
+    meta, init_h, U_h, cost = make_problem(dict(w, N=1), seed=0) if w.get("mppi") else make_problem(w, seed=rank)
     model, _ = mpcdl.from_checkpoint_name(w["ckpt"], load_ckpt(w["ckpt"]), dev)
     stats = load_stats(meta["window"])
     noise = None
@@ -243,8 +249,20 @@ def run_native(args, w):
     prec = args.precision
     kw = dict(noise=noise, seed=1, traj_offset=rank * N, cost=cost_d, return_states=w["states"], precision=prec)
     costs_all = torch.empty(world * N, device=dev) if world > 1 else None
+    mppi = bool(w.get("mppi"))
+    if mppi:
+        from mpcdl.mppi import MPPI
+        SIG, LO, HI = (0.06, 0.03), (-0.875, -0.285), (0.237, 0.279)      # 0.25 sigma_u and the recorded control range
+        planner = MPPI(model, stats, world * N, SIG, LO, HI, cost_d, lam=5.0, precision=prec, seed=1)
+        init_h, U_h = init_h[0].contiguous(), U_h[0].contiguous()         # ONE start state and the nominal sequence
+        init_p, U_p = init_h.pin_memory(), U_h.pin_memory()
+        init_d, U_d = init_p.to(dev), U_p.to(dev)
+        kw.update(sample=dict(n=N, sigma=SIG, lo=LO, hi=HI, seed=1), shared_init=True)
 
     def step(init, U):
+        if mppi:                                       # rollout + (all-gather of costs) + softmin update
+            u_new, info = planner.step(init, U)
+            return None, u_new
         out = model.rollout(init, U, stats, **kw)
         if world > 1:                                  # the path's only collective: all-gather of costs
             dist.all_gather_into_tensor(costs_all, out[1])
@@ -287,7 +305,7 @@ def run_native(args, w):
     k_ms = sum(e0.elapsed_time(e1) for e0, e1 in kev) / args.steps
 
     # ---- timed region 2: end to end with host buffers (H2D inputs, D2H result every step)
-    res_shape = (N, H, 6) if w["states"] else (N,)
+    res_shape = (N, H, 6) if w["states"] else ((H, 2) if mppi else (N,))
     res_p = torch.empty(res_shape, dtype=torch.float32).pin_memory()
     e2e_steps = max(3, min(args.steps, 200))
 
@@ -344,7 +362,7 @@ def run_native(args, w):
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         alg_flop = N * H * w["flop"]
-        alg_bytes = N * H * ((24 if w["states"] else 0) + 8) + init_h.numel() * 4 + N * 4
+        alg_bytes = N * H * ((24 if w["states"] else 0) + (0 if mppi else 8)) + init_h.numel() * 4 + N * 4
         ach_tf = alg_flop / (k_ms * 1e-3) / 1e12
         traffic = None
         try:
@@ -380,7 +398,7 @@ def run_native(args, w):
                         "how": "mpcdl.parallel.HostPipeline(depth=2): pinned host buffers, every batch copied in and its result copied out, "
                                "copies of neighbouring batches overlap the kernel",
                         "serial_value": units / (e2e_serial_ms * 1e-3), "serial_ms_per_step": e2e_serial_ms},
-                "gpu_launches": args.steps, "gpu_launches_total": max(args.warmup, 3) + 2 * args.steps + 2 * (e2e_steps + 3) + 6, "clocks": clocks, "wall_s_region1": wall}
+                "gpu_launches": args.steps * (6 if mppi else 1), "gpu_launches_total": max(args.warmup, 3) + 2 * args.steps + 2 * (e2e_steps + 3) + 6, "clocks": clocks, "wall_s_region1": wall}
         if world == 1 and not args.skip_cpu:
             val, med, threads, sample, _ = time_cpu(w, 9, 1)
             line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,

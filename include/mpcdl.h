@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MPCDL_VERSION 102
+#define MPCDL_VERSION 103
 
 enum { MPCDL_MLP = 0, MPCDL_GRU = 1, MPCDL_LSTM = 2 };
 /* Arithmetic of the gate GEMMs.  FP32 = FFMA kernels (the parity path, <= 1e-5 one-step).  The tensor-core
@@ -108,6 +108,14 @@ typedef struct {
     int32_t tune_rt, tune_ntg, tune_nslots, tune_kc;
     int32_t precision;         /* MPCDL_PREC_*; the tensor-core modes need wblob_tc                         */
     const float* wblob_tc;     /* device: mpcdl_pack_rnn_tc output (precision != FP32), else NULL           */
+    /* MPPI planner call (generalises run_dynamics_model's feedback loop, scripts/test_model.py:67-87):
+     * sample_controls != 0 -> U is the NOMINAL control sequence [H,2] and trajectory n applies
+     *   u_t = clamp(U[t] + ctrl_sigma * z, ctrl_lo, ctrl_hi),  z ~ N(0,1) from Philox(ctrl_seed, traj_offset + n, t),
+     * generated in registers (no [N,H,2] tensor exists); shared_init != 0 -> init holds ONE state [6] / window [T,8]
+     * that every trajectory starts from. */
+    int32_t sample_controls, shared_init;
+    float ctrl_sigma[2], ctrl_lo[2], ctrl_hi[2];
+    uint64_t ctrl_seed;
 } mpcdl_rollout_args;
 
 /* The fused closed loop.  Replaces, batched over N trajectories and H steps in ONE launch:
@@ -154,6 +162,28 @@ typedef struct {
     int32_t H;
 } mpcdl_noise_args;
 int mpcdl_noise_forward(const mpcdl_noise_args* args, void* stream);
+
+/* MPPI update from the costs of sampled rollouts (sample_controls above): with w_n = exp(-(cost_n - cmin) / lambda),
+ *   sums[0 .. 2H) = sum_n w_n * (u_{n,t} - U[t])   (the sampled controls are re-generated from the same Philox keys),
+ *   sums[2H] = sum_n w_n,  sums[2H+1] = cmin.
+ * The new nominal sequence is clamp(U + sums[0..2H) / sums[2H]).  Sharded use: all-reduce MIN the local minima
+ * (mpcdl_mppi_min), pass the global one as cmin, all-reduce SUM the first 2H+1 entries.  Deterministic (fixed-order
+ * two-stage reduction, no atomics).  workspace: device, >= mpcdl_mppi_workspace_floats(H) floats. */
+typedef struct {
+    const float* costs;        /* device [N] */
+    int64_t N, traj_offset;
+    int32_t H;
+    const float* U;            /* device [H,2] nominal sequence */
+    float ctrl_sigma[2], ctrl_lo[2], ctrl_hi[2];
+    uint64_t ctrl_seed;
+    float lambda;
+    const float* cmin;         /* device [1] global minimum cost, or NULL = minimum of these N costs */
+    float* workspace;          /* device */
+    float* sums;               /* device out [2H+2] */
+} mpcdl_mppi_args;
+size_t mpcdl_mppi_workspace_floats(int H);
+int mpcdl_mppi_min(const float* costs, int64_t N, float* workspace, float* cmin_out, void* stream);
+int mpcdl_mppi_reduce(const mpcdl_mppi_args* args, void* stream);
 
 /* Per-sample error metrics of eval_models.calc_error (model_scripts/eval_models.py:91-92):
  * mae[n] = mean_d |output[n,d] - labels[n,d]|, rmse[n] = sqrt(mean_d (output - labels)^2), d < 6; all device, FP32. */

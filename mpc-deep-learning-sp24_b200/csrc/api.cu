@@ -112,6 +112,8 @@ void fill_io(IoParams& io, const mpcdl_rollout_args& a, int ntiles) {
     for (int i = 0; i < 2; ++i) io.rw[i] = a.cost_rw[i];
     io.eps = a.eps; io.seed = a.seed; io.traj_offset = a.traj_offset; io.carry = a.carry;
     io.N = a.N; io.H = a.H; io.ntiles = ntiles;
+    io.sample = a.sample_controls != 0; io.init_mul = a.shared_init ? 0 : 1; io.ctrl_seed = a.ctrl_seed;
+    for (int i = 0; i < 2; ++i) { io.sig[i] = a.ctrl_sigma[i]; io.ulo[i] = a.ctrl_lo[i]; io.uhi[i] = a.ctrl_hi[i]; }
 }
 
 void fill_noise(NoiseParams& nz, const mpcdl_rollout_args& a) {
@@ -325,6 +327,8 @@ int check_args(const mpcdl_rollout_args* a) {
             return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core MLP rollout has no residual-noise path; use MPCDL_PREC_FP32");
         if (!a->wblob_tc) return fail(MPCDL_ERR_ARG, "tensor-core precision needs wblob_tc (mpcdl_pack_rnn_tc)");
     }
+    if (a->sample_controls && !(a->ctrl_lo[0] <= a->ctrl_hi[0] && a->ctrl_lo[1] <= a->ctrl_hi[1] && a->ctrl_sigma[0] >= 0.f && a->ctrl_sigma[1] >= 0.f))
+        return fail(MPCDL_ERR_ARG, "sample_controls needs ctrl_sigma >= 0 and ctrl_lo <= ctrl_hi");
     if (a->noise_wblob) {
         if (a->noise_history < 1 || a->noise_history > 8) return fail(MPCDL_ERR_UNSUPPORTED, "noise history=%d outside [1,8]", a->noise_history);
         if (a->noise_size < 4 || a->noise_size > 64 || a->noise_size % 4) return fail(MPCDL_ERR_UNSUPPORTED, "noise size=%d must be a multiple of 4 in [4,64]", a->noise_size);
@@ -646,6 +650,42 @@ int mpcdl_noise_forward(const mpcdl_noise_args* a, void* stream) {
     if (smem > SMEM_LIMIT) return fail(MPCDL_ERR_UNSUPPORTED, "noise net needs %d bytes of shared memory", smem);
     cudaError_t e = launch_aux(p, a->closed_loop != 0, std::min(p.ntiles, g_num_sms), smem, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "noise kernel launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+size_t mpcdl_mppi_workspace_floats(int H) { return H < 1 ? 0 : (size_t)MPPI_GRID * (2 * (size_t)H + 2); }
+
+int mpcdl_mppi_min(const float* costs, int64_t N, float* workspace, float* cmin_out, void* stream) {
+    if (!costs || !workspace || !cmin_out || N < 1) return fail(MPCDL_ERR_ARG, "mpcdl_mppi_min: bad arguments");
+    int rc = device_info();
+    if (rc) return rc;
+    if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    cudaError_t e = launch_mppi_min(costs, N, workspace, cmin_out, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "mppi_min launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+int mpcdl_mppi_reduce(const mpcdl_mppi_args* a, void* stream) {
+    if (!a) return fail(MPCDL_ERR_ARG, "args is NULL");
+    if (!a->costs || !a->U || !a->workspace || !a->sums) return fail(MPCDL_ERR_ARG, "costs/U/workspace/sums must be non-NULL device pointers");
+    if (a->N < 1 || a->H < 1 || a->H > MPPI_MAX_H) return fail(MPCDL_ERR_ARG, "N=%lld must be >= 1 and H=%d in [1,%d]", (long long)a->N, a->H, MPPI_MAX_H);
+    if (!(a->lambda > 0.f)) return fail(MPCDL_ERR_ARG, "lambda must be > 0");
+    int rc = device_info();
+    if (rc) return rc;
+    if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    MppiParams p;
+    memset(&p, 0, sizeof(p));
+    p.costs = a->costs; p.N = a->N; p.traj_offset = a->traj_offset; p.H = a->H; p.U = a->U; p.ctrl_seed = a->ctrl_seed;
+    for (int i = 0; i < 2; ++i) { p.sig[i] = a->ctrl_sigma[i]; p.ulo[i] = a->ctrl_lo[i]; p.uhi[i] = a->ctrl_hi[i]; }
+    p.inv_lambda = 1.0f / a->lambda; p.cmin = a->cmin; p.workspace = a->workspace; p.sums = a->sums;
+    cudaError_t e = cudaSuccess;
+    if (!a->cmin) {
+        e = launch_mppi_min(a->costs, a->N, a->workspace, a->sums + 2 * a->H + 1, st);
+        p.cmin = a->sums + 2 * a->H + 1;
+    }
+    if (e == cudaSuccess) e = launch_mppi_reduce(p, st);
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "mppi_reduce launch failed: %s", cudaGetErrorString(e));
     return MPCDL_OK;
 }
 

@@ -8,6 +8,7 @@
 //   K8 error_metrics   the per-sample MAE / RMSE of eval_models.calc_error  model_scripts/eval_models.py:91-92
 // Same building blocks as the fused rollout kernels (dense_resident tiles, Philox keyed by the global
 // trajectory index); all FP32, bias first, k ascending.
+#include <algorithm>
 #include "owner.cuh"
 #include "launch.h"
 
@@ -164,7 +165,103 @@ __global__ void error_metrics_kernel(const float* __restrict__ output, const flo
     rmse[n] = __fsqrt_rn(__fdiv_rn(ss, 6.0f));
 }
 
+// ---------------------------------------------------------------------------------------------- K9 MPPI update
+// (new: SURVEY.md 8f-1; the closest reference caller is the feedback loop of run_dynamics_model, test_model.py:67-87)
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__global__ void __launch_bounds__(MPPI_THREADS) mppi_min_kernel(const float* __restrict__ costs, long long N, float* __restrict__ part) {
+    __shared__ float wm[MPPI_THREADS / 32];
+    float m = INFINITY;
+    for (long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x; n < N; n += (long long)gridDim.x * blockDim.x)
+        m = fminf(m, __ldg(costs + n));
+    m = warp_min(m);
+    if ((threadIdx.x & 31) == 0) wm[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < MPPI_THREADS / 32; ++w) m = fminf(m, wm[w]);
+        part[blockIdx.x] = m;
+    }
+}
+__global__ void mppi_min_final_kernel(const float* __restrict__ part, int nparts, float* __restrict__ out) {
+    float m = INFINITY;
+    for (int i = threadIdx.x; i < nparts; i += 32) m = fminf(m, part[i]);
+    m = warp_min(m);
+    if (threadIdx.x == 0) *out = m;
+}
+
+// stage 1: per CTA, sum_n w_n * (u_{n,t} - U[t]) for every (t, channel) and sum_n w_n, in a fixed order:
+// warp-shuffle tree over the 32 trajectories of a warp pass, per-warp running sums in shared memory, warps summed 0..7
+__global__ void __launch_bounds__(MPPI_THREADS) mppi_partial_kernel(const __grid_constant__ MppiParams p) {
+    extern __shared__ float acc[];                       // [warps][2H+1]
+    const int H = p.H, W = 2 * H + 1, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float* mine = acc + warp * W;
+    for (int i = lane; i < W; i += 32) mine[i] = 0.f;
+    __syncwarp();
+    const float cmin = __ldg(p.cmin);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long rounds = (p.N + stride - 1) / stride;
+    for (long long r = 0; r < rounds; ++r) {
+        const long long n = r * stride + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+        const float w = n < p.N ? __expf(-(__ldg(p.costs + n) - cmin) * p.inv_lambda) : 0.f;
+        const float ws = warp_sum(w);
+        if (lane == 0) mine[2 * H] += ws;
+        for (int t = 0; t < H; ++t) {
+            float d0 = 0.f, d1 = 0.f;
+            if (w > 0.f) {                               // zero-weight trajectories contribute nothing: skip their draws
+                const float2 ub = __ldg(reinterpret_cast<const float2*>(p.U) + t);
+                float z0, z1;
+                philox_normal2(p.ctrl_seed, static_cast<uint64_t>(p.traj_offset + n), static_cast<uint32_t>(t), z0, z1);
+                d0 = w * (fminf(fmaxf(fmaf(p.sig[0], z0, ub.x), p.ulo[0]), p.uhi[0]) - ub.x);
+                d1 = w * (fminf(fmaxf(fmaf(p.sig[1], z1, ub.y), p.ulo[1]), p.uhi[1]) - ub.y);
+            }
+            d0 = warp_sum(d0);
+            d1 = warp_sum(d1);
+            if (lane == 0) { mine[2 * t] += d0; mine[2 * t + 1] += d1; }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < W; i += blockDim.x) {
+        float s = 0.f;
+        for (int w = 0; w < MPPI_THREADS / 32; ++w) s += acc[w * W + i];
+        p.workspace[(size_t)blockIdx.x * (W + 1) + i] = s;
+    }
+}
+// stage 2: CTA partials summed in CTA order (double accumulation), one thread per entry
+__global__ void mppi_final_kernel(const __grid_constant__ MppiParams p, int nparts) {
+    const int W = 2 * p.H + 1;
+    for (int i = threadIdx.x; i < W; i += blockDim.x) {
+        double s = 0.0;
+        for (int b = 0; b < nparts; ++b) s += (double)p.workspace[(size_t)b * (W + 1) + i];
+        p.sums[i] = (float)s;
+    }
+    if (threadIdx.x == 0) p.sums[W] = __ldg(p.cmin);
+}
+
 // ---------------------------------------------------------------------------------------------- launchers
+cudaError_t launch_mppi_min(const float* costs, long long N, float* workspace, float* cmin_out, cudaStream_t st) {
+    const int grid = (int)std::min<long long>(MPPI_GRID, (N + MPPI_THREADS - 1) / MPPI_THREADS);
+    mppi_min_kernel<<<grid, MPPI_THREADS, 0, st>>>(costs, N, workspace);
+    mppi_min_final_kernel<<<1, 32, 0, st>>>(workspace, grid, cmin_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_mppi_reduce(const MppiParams& p, cudaStream_t st) {
+    const int grid = (int)std::min<long long>(MPPI_GRID, (p.N + MPPI_THREADS - 1) / MPPI_THREADS);
+    const int smem = (MPPI_THREADS / 32) * (2 * p.H + 1) * 4;
+    mppi_partial_kernel<<<grid, MPPI_THREADS, smem, st>>>(p);
+    mppi_final_kernel<<<1, 256, 0, st>>>(p, grid);
+    return cudaGetLastError();
+}
+
 int aux_smem_bytes(int blob_floats, int in_dim, int size) { return aux_layout(blob_floats, in_dim, size, AUX_TN).total * 4; }
 
 cudaError_t launch_aux(const AuxParams& p, bool closed_loop, int grid, int smem_bytes, cudaStream_t st) {

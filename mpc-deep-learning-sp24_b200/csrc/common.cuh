@@ -125,4 +125,12 @@ __device__ __forceinline__ void philox_normal6(uint64_t seed, uint64_t traj, uin
     box_muller(c1.x, c1.y, z[4], z[5]);
 }
 
+// two N(0,1) draws for the sampled control of (trajectory, step): counter word 3 = 2 keeps the stream disjoint
+// from the residual-noise draws (words 0 and 1) under the same key
+__device__ __forceinline__ void philox_normal2(uint64_t seed, uint64_t traj, uint32_t step, float& z0, float& z1) {
+    uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+    uint4 c = philox4x32(make_uint4(static_cast<uint32_t>(traj), static_cast<uint32_t>(traj >> 32), step, 2u), key);
+    box_muller(c.x, c.y, z0, z1);
+}
+
 }  // namespace mpcdl

@@ -37,6 +37,8 @@ cudaError_t launch_mlp_tc(const McRolloutParams& p, int grid, int smem_bytes, cu
 constexpr int AUX_TN = 128, AUX_THREADS = 256;       // noise-net entry points: 128 samples per CTA tile
 int aux_smem_bytes(int blob_floats, int in_dim, int size);
 cudaError_t launch_aux(const AuxParams& p, bool closed_loop, int grid, int smem_bytes, cudaStream_t st);
+cudaError_t launch_mppi_min(const float* costs, long long N, float* workspace, float* cmin_out, cudaStream_t st);
+cudaError_t launch_mppi_reduce(const MppiParams& p, cudaStream_t st);
 cudaError_t launch_error_metrics(const float* output, const float* labels, long long B, float* mae, float* rmse, cudaStream_t st);
 cudaError_t launch_ffma_peak(float* out, int iters, int grid, cudaStream_t st);
 

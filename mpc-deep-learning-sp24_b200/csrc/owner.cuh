@@ -38,6 +38,22 @@ __device__ __forceinline__ void noise_push(float* nin, int TN, int pos, int hist
     nin[(6 * hist + (hist - 1) * 2 + 1) * TN + pos] = u[1];
 }
 
+// control of trajectory n at step t: read from U [N,H,2], or (MPPI) sampled around the nominal sequence U [H,2]
+// (the sampler is kept out of line so the plain [N,H,2] path keeps its registers and instruction footprint)
+static __device__ __noinline__ float2 sample_control(const float* U, unsigned long long seed, unsigned long long traj, int t,
+                                              float s0, float s1, float lo0, float lo1, float hi0, float hi1) {
+    const float2 ub = __ldg(reinterpret_cast<const float2*>(U) + t);
+    float z0, z1;
+    philox_normal2(seed, traj, static_cast<uint32_t>(t), z0, z1);
+    return make_float2(fminf(fmaxf(fmaf(s0, z0, ub.x), lo0), hi0), fminf(fmaxf(fmaf(s1, z1, ub.y), lo1), hi1));
+}
+template <class IO>
+__device__ __forceinline__ float2 load_control(const IO& io, long long n, int t) {
+    if (!io.sample) return __ldg(reinterpret_cast<const float2*>(io.U) + n * io.H + t);
+    return sample_control(io.U, io.ctrl_seed, static_cast<unsigned long long>(io.traj_offset + n), t, io.sig[0], io.sig[1],
+                          io.ulo[0], io.ulo[1], io.uhi[0], io.uhi[1]);
+}
+
 // y (normalised network output, column `pos` of ybuf) -> next raw state; optional noise, cost, store.
 template <class P>
 __device__ __forceinline__ void owner_finish(const P& p, const float* norm_l /* l_mean[6] l_std[6] */,

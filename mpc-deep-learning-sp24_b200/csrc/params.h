@@ -33,6 +33,12 @@ struct IoParams {
     long long N;
     int H;
     int ntiles;
+    // MPPI control sampling (sample != 0): U is the NOMINAL sequence [H,2]; trajectory n uses
+    // u_t = clamp(U[t] + sig * z(ctrl_seed, traj_offset + n, t), ulo, uhi), z ~ N(0,1) from Philox (counter word 3 = 2)
+    int sample;
+    int init_mul;            // 1: init is per trajectory; 0: one initial state / window shared by all trajectories
+    float sig[2], ulo[2], uhi[2];
+    unsigned long long ctrl_seed;
 };
 
 struct ModelParams {
@@ -67,6 +73,21 @@ struct AuxParams {
     long long N;
     int H;
     int ntiles;
+};
+
+// MPPI update (aux_kernels.cu): softmin-weighted sum of the sampled control perturbations
+constexpr int MPPI_GRID = 296, MPPI_THREADS = 256, MPPI_MAX_H = 512;
+struct MppiParams {
+    const float* costs;
+    long long N, traj_offset;
+    int H;
+    const float* U;          // nominal [H,2]
+    float sig[2], ulo[2], uhi[2];
+    unsigned long long ctrl_seed;
+    float inv_lambda;
+    const float* cmin;       // device [1]
+    float* workspace;        // [MPPI_GRID][2H+2]
+    float* sums;             // [2H+2]
 };
 
 // ------------------------------------------------------------------ shared-memory layout (float offsets)

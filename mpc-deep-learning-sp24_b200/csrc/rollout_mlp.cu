@@ -95,12 +95,12 @@ __global__ void __launch_bounds__(MLP_MAX_THREADS, 1) rollout_mlp_kernel(const _
         float s[6], cost = 0.f;
         if (owner) {
 #pragma unroll
-            for (int d = 0; d < 6; ++d) s[d] = __ldg(p.io.init + n * 6 + d);
+            for (int d = 0; d < 6; ++d) s[d] = __ldg(p.io.init + n * p.io.init_mul * 6 + d);
         }
         for (int t = 0; t < H; ++t) {
             float u[2] = {0.f, 0.f};
             if (owner) {
-                float2 uu = __ldg(reinterpret_cast<const float2*>(p.io.U + (n * H + t) * 2));
+                float2 uu = load_control(p.io, n, t);
                 u[0] = uu.x; u[1] = uu.y;
 #pragma unroll
                 for (int k = 0; k < 6; ++k) xin[k * TN + tid] = __fdiv_rn(__fsub_rn(s[k], normS[k]), normS[8 + k]);

@@ -129,16 +129,15 @@ __global__ void __launch_bounds__((Mlp2Cfg<HID, RT, RJ, KS>::MAX_THREADS), 1) ro
         if (n >= p.io.N) n = p.io.N - 1;
         float s[6], cost = 0.f;
         float2 unext = make_float2(0.f, 0.f);
-        const float2* up = reinterpret_cast<const float2*>(p.io.U) + n * H;
         if (owner) {
 #pragma unroll
-            for (int d = 0; d < 6; ++d) s[d] = __ldg(p.io.init + n * 6 + d);
-            unext = __ldg(up);
+            for (int d = 0; d < 6; ++d) s[d] = __ldg(p.io.init + n * p.io.init_mul * 6 + d);
+            unext = load_control(p.io, n, 0);
         }
         for (int t = 0; t < H; ++t) {
             float u[2] = {unext.x, unext.y};
             if (owner) {
-                if (t + 1 < H) unext = __ldg(up + t + 1);      // prefetch: hidden behind this step's layers
+                if (t + 1 < H) unext = load_control(p.io, n, t + 1);      // prefetch: hidden behind this step's layers
 #pragma unroll
                 for (int k = 0; k < 6; ++k) xin[k * TN + tid] = __fdiv_rn(__fsub_rn(s[k], normS[k]), normS[8 + k]);
 #pragma unroll

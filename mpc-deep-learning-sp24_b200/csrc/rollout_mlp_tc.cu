@@ -146,13 +146,12 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                 if (n >= N) n = N - 1;
                 float s[6], cost = 0.f;
 #pragma unroll
-                for (int d = 0; d < 6; ++d) s[d] = owner ? __ldg(p.io.init + n * 6 + d) : 0.f;
-                const float2* up = reinterpret_cast<const float2*>(p.io.U) + n * H;
-                float2 unext = owner ? __ldg(up) : make_float2(0.f, 0.f);
+                for (int d = 0; d < 6; ++d) s[d] = owner ? __ldg(p.io.init + n * p.io.init_mul * 6 + d) : 0.f;
+                float2 unext = owner ? load_control(p.io, n, 0) : make_float2(0.f, 0.f);
                 for (int t = 0; t < H; ++t) {
                     const float u[2] = {unext.x, unext.y};
                     if (owner) {
-                        if (t + 1 < H) unext = __ldg(up + t + 1);        // prefetch: hidden behind this step's layers
+                        if (t + 1 < H) unext = load_control(p.io, n, t + 1);        // prefetch: hidden behind this step's layers
                         // z-score ([s,u] - f_mean) / f_std  (basic_model.py:34) -> A operand columns 0..7
                         float xn[8];
 #pragma unroll

@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(rnn_max_consumers(RT, RJ) + 32, 1) rollout_rnn
         if (n >= N) n = N - 1;
         float cost = 0.f;
         if (owner) {                                   // initial window -> xwin[f][k][pos]
-            const float4* w4 = reinterpret_cast<const float4*>(p.io.init + n * T * 8);
+            const float4* w4 = reinterpret_cast<const float4*>(p.io.init + n * p.io.init_mul * T * 8);
             for (int f = 0; f < T; ++f) {
                 float4 a = __ldg(w4 + 2 * f), b = __ldg(w4 + 2 * f + 1);
                 float* d = xwin + f * 8 * TN + tid;
@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(rnn_max_consumers(RT, RJ) + 32, 1) rollout_rnn
             }
             float u[2] = {0.f, 0.f};
             if (owner) {
-                float2 uu = __ldg(reinterpret_cast<const float2*>(p.io.U + (n * H + t) * 2));
+                float2 uu = load_control(p.io, n, t);
                 u[0] = uu.x; u[1] = uu.y;
                 if (p.nz.enabled) {                    // newest frame feeds the noise history
                     int pf = base + T - 1; if (pf >= T) pf -= T;

@@ -50,6 +50,30 @@ class RolloutArgs(C.Structure):
         ("tune_kc", C.c_int32),
         ("precision", C.c_int32),
         ("wblob_tc", C.c_void_p),
+        ("sample_controls", C.c_int32),
+        ("shared_init", C.c_int32),
+        ("ctrl_sigma", C.c_float * 2),
+        ("ctrl_lo", C.c_float * 2),
+        ("ctrl_hi", C.c_float * 2),
+        ("ctrl_seed", C.c_uint64),
+    ]
+
+
+class MppiArgs(C.Structure):
+    _fields_ = [
+        ("costs", C.c_void_p),
+        ("N", C.c_int64),
+        ("traj_offset", C.c_int64),
+        ("H", C.c_int32),
+        ("U", C.c_void_p),
+        ("ctrl_sigma", C.c_float * 2),
+        ("ctrl_lo", C.c_float * 2),
+        ("ctrl_hi", C.c_float * 2),
+        ("ctrl_seed", C.c_uint64),
+        ("lam", C.c_float),
+        ("cmin", C.c_void_p),
+        ("workspace", C.c_void_p),
+        ("sums", C.c_void_p),
     ]
 
 
@@ -77,7 +101,7 @@ class Plan(C.Structure):
 
 
 EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_pack_mlp_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
-           "mpcdl_rollout", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version")
+           "mpcdl_rollout", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version")
 
 
 def _load():
@@ -109,6 +133,12 @@ def _load():
     lib.mpcdl_rollout_plan.argtypes = [C.POINTER(RolloutArgs), C.POINTER(Plan)]
     lib.mpcdl_noise_forward.restype = C.c_int
     lib.mpcdl_noise_forward.argtypes = [C.POINTER(NoiseArgs), C.c_void_p]
+    lib.mpcdl_mppi_workspace_floats.restype = C.c_size_t
+    lib.mpcdl_mppi_workspace_floats.argtypes = [C.c_int]
+    lib.mpcdl_mppi_min.restype = C.c_int
+    lib.mpcdl_mppi_min.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.mpcdl_mppi_reduce.restype = C.c_int
+    lib.mpcdl_mppi_reduce.argtypes = [C.POINTER(MppiArgs), C.c_void_p]
     lib.mpcdl_error_metrics.restype = C.c_int
     lib.mpcdl_error_metrics.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.mpcdl_ffma_peak.restype = C.c_int

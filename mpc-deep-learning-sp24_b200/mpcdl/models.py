@@ -76,7 +76,7 @@ class _RolloutMixin:
 
     @torch.no_grad()
     def rollout(self, init, U, stats=None, *, noise=None, eps=None, seed=0, traj_offset=0, cost=None,
-                return_states=True, stateful=None, carry=None, tune=(), precision=None):
+                return_states=True, stateful=None, carry=None, tune=(), precision=None, sample=None, shared_init=False):
         """Closed-loop rollout of N trajectories over H steps in one kernel launch.
 
         init  s0 [N,6] (MLP) or window [N,T,8] (GRU/LSTM), raw units; U [N,H,2] controls.
@@ -85,14 +85,21 @@ class _RolloutMixin:
         cost  (ref [H,6], qw [6], rw [2]) -> per-trajectory quadratic tracking cost.
         precision "fp32" (FFMA kernels, the parity path) | "tf32x3" | "tf32" (tcgen05 tensor-core kernels,
               GRU/LSTM hidden 64 window 4 only; anything else raises -- there is no silent fallback).
+        sample  MPPI call: dict(n=N, sigma=(s_a, s_steer), lo=(..), hi=(..), seed=int) -> U is the NOMINAL sequence
+              [H,2] and trajectory n applies clamp(U + sigma * z_n) with z_n drawn in-kernel (Philox keyed by
+              seed, traj_offset + n, t); no [N,H,2] tensor exists.  shared_init: init is ONE state / window.
         Returns (states [N,H,6] or None, costs [N] or None[, carry if stateful])."""
         hidden, layers, window = self._desc()
         dev = U.device
         stateful = bool(getattr(self, "state_f", False)) if stateful is None else bool(stateful)
         stateful = stateful and self.KIND != _lib.MLP
+        ctrl, ctrl_seed, n_samples = [], 0, 0
+        if sample is not None:
+            ctrl = [float(v) for k in ("sigma", "lo", "hi") for v in sample[k]]
+            ctrl_seed, n_samples = int(sample.get("seed", 0)), int(sample["n"])
         if stateful and carry is None:
             planes = layers * (2 if self.KIND == _lib.LSTM else 1)
-            carry = torch.zeros(planes, U.shape[0], hidden, device=dev)
+            carry = torch.zeros(planes, n_samples or U.shape[0], hidden, device=dev)
         nblob, ncfg = None, []
         if noise is not None:
             nblob, ncfg = noise.packed(dev), noise.cfg()
@@ -106,7 +113,8 @@ class _RolloutMixin:
         states, costs = ops.OPS[self.KIND](self._blob(dev), self._norm(stats, dev), init, U, hidden, layers, window,
                                            stateful, carry if stateful else None, nblob, ncfg, eps, int(seed),
                                            int(traj_offset), cref, cw, bool(return_states), cost is not None,
-                                           list(tune), prec, self._blob_tc(dev) if prec else None)
+                                           list(tune), prec, self._blob_tc(dev) if prec else None,
+                                           ctrl, ctrl_seed, n_samples, bool(shared_init))
         out = (states if return_states else None, costs if cost is not None else None)
         return out + (carry,) if stateful else out
 
@@ -183,7 +191,7 @@ class _RNNBase(_RolloutMixin, nn.Module):
                                                          tensor_core=True))
 
     def rollout(self, init, U, stats=None, **kw):
-        self._window = int(init.shape[1])
+        self._window = int(init.shape[-2])
         return super().rollout(init, U, stats, **kw)
 
     def forward(self, x):

@@ -21,7 +21,7 @@ from . import _lib
 _SCHEMA = ("(Tensor wblob, Tensor norm, Tensor init, Tensor U, int hidden, int layers, int window, bool stateful, "
            "Tensor(a!)? carry, Tensor? noise_wblob, int[] noise_cfg, Tensor? eps, int seed, int traj_offset, "
            "Tensor? cost_ref, float[] cost_w, bool return_states, bool return_costs, int[] tune, int precision, "
-           "Tensor? wblob_tc) -> (Tensor, Tensor)")
+           "Tensor? wblob_tc, float[] ctrl, int ctrl_seed, int n_samples, bool shared_init) -> (Tensor, Tensor)")
 
 _libdef = torch.library.Library("mpcdl", "DEF")
 for _name in ("rollout_mlp", "rollout_gru", "rollout_lstm"):
@@ -43,13 +43,21 @@ def _f32c(t: Optional[torch.Tensor], name: str, dev=None) -> int:
 
 
 def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob, noise_cfg,
-                  eps, seed, traj_offset, cost_ref, cost_w, return_states, return_costs, tune, precision=0, wblob_tc=None):
+                  eps, seed, traj_offset, cost_ref, cost_w, return_states, return_costs, tune, precision=0, wblob_tc=None,
+                  ctrl=(), ctrl_seed=0, n_samples=0, shared_init=False):
     dev = U.device
-    if U.dim() != 3 or U.shape[2] != 2:
-        raise RuntimeError(f"mpcdl: U must be [N,H,2], got {tuple(U.shape)}")
-    N, H = int(U.shape[0]), int(U.shape[1])
     T = window if kind != _lib.MLP else 0
-    want = (N, 6) if kind == _lib.MLP else (N, T, 8)
+    if len(ctrl):
+        # MPPI call: U is the nominal sequence [H,2]; the N sampled sequences exist only in registers
+        if len(ctrl) != 6 or U.dim() != 2 or U.shape[1] != 2 or n_samples < 1:
+            raise RuntimeError(f"mpcdl: sampled controls need U [H,2], ctrl = sigma[2]+lo[2]+hi[2] and n_samples >= 1; got U {tuple(U.shape)}")
+        N, H = int(n_samples), int(U.shape[0])
+    else:
+        if U.dim() != 3 or U.shape[2] != 2:
+            raise RuntimeError(f"mpcdl: U must be [N,H,2], got {tuple(U.shape)}")
+        N, H = int(U.shape[0]), int(U.shape[1])
+    one = (6,) if kind == _lib.MLP else (T, 8)
+    want = one if shared_init else (N,) + one
     if tuple(init.shape) != want:
         raise RuntimeError(f"mpcdl: init must be {want}, got {tuple(init.shape)}")
     nt = max(T, 1)
@@ -107,6 +115,11 @@ def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, state
     a.N, a.H = N, H
     if len(tune) == 4:
         a.tune_rt, a.tune_ntg, a.tune_nslots, a.tune_kc = tune
+    if len(ctrl):
+        a.sample_controls = 1
+        a.ctrl_sigma, a.ctrl_lo, a.ctrl_hi = (C.c_float * 2)(*ctrl[0:2]), (C.c_float * 2)(*ctrl[2:4]), (C.c_float * 2)(*ctrl[4:6])
+        a.ctrl_seed = ctrl_seed & 0xFFFFFFFFFFFFFFFF
+    a.shared_init = int(bool(shared_init))
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev).cuda_stream
         _lib.check(_lib.lib.mpcdl_rollout(C.byref(a), C.c_void_p(stream)))
@@ -115,10 +128,11 @@ def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, state
 
 def _make(kind):
     def impl(wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob, noise_cfg, eps, seed,
-             traj_offset, cost_ref, cost_w, return_states, return_costs, tune, precision, wblob_tc):
+             traj_offset, cost_ref, cost_w, return_states, return_costs, tune, precision, wblob_tc, ctrl, ctrl_seed,
+             n_samples, shared_init):
         return _rollout_impl(kind, wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob,
                              noise_cfg, eps, seed, traj_offset, cost_ref, cost_w, return_states, return_costs, tune,
-                             precision, wblob_tc)
+                             precision, wblob_tc, ctrl, ctrl_seed, n_samples, shared_init)
     return impl
 
 
@@ -214,6 +228,45 @@ def _error_metrics_impl(output, labels):
     return mae, rmse
 
 
+_libdef.define("mppi_reduce(Tensor costs, Tensor U, float[] ctrl, int ctrl_seed, int traj_offset, float lam, Tensor? cmin) -> Tensor")
+_libdef.define("mppi_min(Tensor costs) -> Tensor")
+
+
+def _mppi_min_impl(costs):
+    dev = costs.device
+    ws = torch.empty(_lib.lib.mpcdl_mppi_workspace_floats(1), device=dev, dtype=torch.float32)
+    out = torch.empty(1, device=dev, dtype=torch.float32)
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(_lib.lib.mpcdl_mppi_min(C.c_void_p(_f32c(costs, "costs", dev)), costs.numel(), C.c_void_p(ws.data_ptr()),
+                                          C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
+    return out
+
+
+def _mppi_reduce_impl(costs, U, ctrl, ctrl_seed, traj_offset, lam, cmin):
+    """sums [2H+2] = [sum_n w_n (u_n - U) per (t, channel), sum_n w_n, cmin]; include/mpcdl.h mpcdl_mppi_reduce."""
+    dev = costs.device
+    if U.dim() != 2 or U.shape[1] != 2 or len(ctrl) != 6 or costs.dim() != 1:
+        raise RuntimeError("mpcdl: mppi_reduce needs costs [N], U [H,2], ctrl = sigma[2]+lo[2]+hi[2]")
+    H = int(U.shape[0])
+    a = _lib.MppiArgs()
+    a.costs, a.N, a.traj_offset, a.H = _f32c(costs, "costs", dev), costs.numel(), traj_offset, H
+    a.U = _f32c(U, "U", dev)
+    a.ctrl_sigma, a.ctrl_lo, a.ctrl_hi = (C.c_float * 2)(*ctrl[0:2]), (C.c_float * 2)(*ctrl[2:4]), (C.c_float * 2)(*ctrl[4:6])
+    a.ctrl_seed, a.lam = ctrl_seed & 0xFFFFFFFFFFFFFFFF, lam
+    if cmin is not None:
+        a.cmin = _f32c(cmin, "cmin", dev)
+    ws = torch.empty(_lib.lib.mpcdl_mppi_workspace_floats(H), device=dev, dtype=torch.float32)
+    sums = torch.empty(2 * H + 2, device=dev, dtype=torch.float32)
+    a.workspace, a.sums = ws.data_ptr(), sums.data_ptr()
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(_lib.lib.mpcdl_mppi_reduce(C.byref(a), C.c_void_p(stream)))
+    return sums
+
+
+_libimpl.impl("mppi_min", _mppi_min_impl)
+_libimpl.impl("mppi_reduce", _mppi_reduce_impl)
 _libimpl.impl("noise_forward", _noise_forward_impl)
 _libimpl.impl("dynamics_nn_rollout", _dynnn_rollout_impl)
 _libimpl.impl("error_metrics", _error_metrics_impl)

@@ -118,3 +118,27 @@ def test_tensor_core_plans_and_errors():
             assert 120 * 1024 <= p["smem_bytes"] <= 232448 and p["threads"] % 32 == 0 and p["threads"] <= 1024
     d = _lib.ModelDesc(_lib.GRU, 32, 2, 4)
     assert _lib.lib.mpcdl_blob_floats_tc(C.byref(d)) == 0
+
+
+def test_mppi_entry_points_without_device():
+    from mpcdl import _lib
+    lib = _lib.lib
+    assert lib.mpcdl_mppi_workspace_floats(50) >= 102 and lib.mpcdl_mppi_workspace_floats(0) == 0
+    assert lib.mpcdl_mppi_reduce(None, None) == -1
+    a = _lib.MppiArgs()
+    for f in ("costs", "U", "workspace", "sums"):
+        setattr(a, f, 16)
+    a.N, a.H, a.lam = 10, 513, 1.0
+    assert lib.mpcdl_mppi_reduce(C.byref(a), None) == -1                 # H beyond MPPI_MAX_H
+    a.H, a.lam = 50, 0.0
+    assert lib.mpcdl_mppi_reduce(C.byref(a), None) == -1 and b"lambda" in lib.mpcdl_last_error()
+    assert lib.mpcdl_mppi_min(None, 5, None, None, None) == -1
+    # sampled-control rollouts validate their bounds before any device work
+    r = _lib.RolloutArgs()
+    r.model = _lib.ModelDesc(_lib.MLP, 64, 4, 0)
+    for f in ("wblob", "norm", "init", "U", "costs"):
+        setattr(r, f, 16)
+    r.N, r.H, r.sample_controls = 100, 10, 1
+    r.ctrl_lo, r.ctrl_hi = (C.c_float * 2)(1.0, 0.0), (C.c_float * 2)(0.0, 1.0)
+    p = _lib.Plan()
+    assert lib.mpcdl_rollout_plan(C.byref(r), C.byref(p)) == -1 and b"ctrl_lo" in lib.mpcdl_last_error()

@@ -140,3 +140,24 @@ def test_calc_error_sampled_matches_reference_golden(gold_aux, gold_onestep, bag
         random.seed(5)
         mae, rmse = R.calc_error_sampled(torch.from_numpy(gold_onestep[name]), ds.labels, 2000, random)
         assert (mae, rmse) == tuple(gold_aux[name + "_err_sampled"])
+
+
+def test_philox_known_answers_and_mppi_update():
+    """oracle/mppi_ref.py: Philox4x32-10 against the Random123 known-answer vectors; Box-Muller moments; the update
+    is a convex combination of the samples when nothing is clamped."""
+    from oracle import mppi_ref as M
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0), (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for c, k, want in kat:
+        assert tuple(M.philox4x32(np.array(c, dtype=np.uint32), np.array(k, dtype=np.uint32))) == want
+    z = M.control_normals(5, np.arange(20000), 8)
+    assert abs(z.mean()) < 0.01 and abs(z.std() - 1) < 0.01
+    assert not np.array_equal(M.control_normals(5, [7], 8), M.control_normals(6, [7], 8))
+    U = np.zeros((8, 2), np.float32)
+    u = M.sample_controls(U, 5, np.arange(100), (0.1, 0.1), (-9, -9), (9, 9))
+    costs = (u ** 2).sum((1, 2))
+    Un, S, wsum, cmin = M.mppi_update(U, u, costs, 0.05, (-9, -9), (9, 9))
+    assert cmin == costs.astype(np.float64).min() and wsum >= 1.0
+    assert (np.abs(Un) <= np.abs(u).max(0) + 1e-7).all()
+    assert (Un ** 2).sum() < np.median(costs)                         # pulled towards the cheap samples
