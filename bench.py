@@ -373,6 +373,9 @@ def run_native(args, w):
             bound, peak = "fp32", fp32_peak
             peak_source = ("FP32 FFMA peak measured live by mpcdl_ffma_peak (MEASURED_PEAKS.json has no FP32 figure; "
                            "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)")
+        elif prec == "bf16":
+            bound, peak = "tensor", peaks.get("bf16_tflops", 1590.0)
+            peak_source = "dense BF16 peak: MEASURED_PEAKS.json bf16_tflops (burst)" if peaks else "fallback 1590"
         else:
             # TF32 tensor peak = half the measured dense BF16 rate (nominal 1.1 vs 2.25 PFLOP/s); tf32x3 issues 3 MMA
             # passes per algorithmic FLOP, so its ceiling against this peak is 1/3
@@ -387,7 +390,8 @@ def run_native(args, w):
                             "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": {"fp32": "f32", "tf32x3": "tf32x3 (3-pass TF32 operands, FP32 accumulate/state)", "tf32": "tf32 (FP32 accumulate/state)"}[prec],
+                "dtype": {"fp32": "f32", "tf32x3": "tf32x3 (3-pass TF32 operands, FP32 accumulate/state)", "tf32": "tf32 (FP32 accumulate/state)",
+                          "bf16": "bf16 (BF16 gate-GEMM operands, FP32 accumulate / cell state / head / feedback)"}[prec],
                 "data": "synthetic",
                 "config": {"workload": w["desc"], "N_per_gpu": N, "H": H, "l2": "flushed between steps (256 MiB memset outside the event pairs)",
                            "parallelism": f"trajectory shards x{world}, one all-gather of costs per step" if world > 1 else "single GPU",
@@ -417,8 +421,9 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--skip-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32x3", "tf32"],
-                    help="gate-GEMM arithmetic of the GRU/LSTM workloads: fp32 = FFMA kernels (parity path), tf32x3 / tf32 = tcgen05 kernels")
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32x3", "tf32", "bf16"],
+                    help="gate-GEMM arithmetic: fp32 = FFMA kernels (parity path), tf32x3 / tf32 = tcgen05 kernels (hidden 64), "
+                         "bf16 = tcgen05 kernel of the hidden-256 LSTM (workload c4)")
     args = ap.parse_args()
     w = WORKLOADS[args.workload]
     if args.impl == "reference":

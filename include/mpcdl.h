@@ -22,14 +22,16 @@
 extern "C" {
 #endif
 
-#define MPCDL_VERSION 103
+#define MPCDL_VERSION 104
 
 enum { MPCDL_MLP = 0, MPCDL_GRU = 1, MPCDL_LSTM = 2 };
 /* Arithmetic of the gate GEMMs.  FP32 = FFMA kernels (the parity path, <= 1e-5 one-step).  The tensor-core
  * modes run the [128 x 64].[64 x 64|192|256] layer / gate contractions on tcgen05 (hidden 64; GRU/LSTM window 4):
  * TF32X3 = three TF32 passes on hi/lo split operands (FP32-class accuracy, bound stated in DESIGN.md 5),
- * TF32 = one TF32 pass + MUFU.TANH activations.  State, accumulation, statistics and cost stay FP32. */
-enum { MPCDL_PREC_FP32 = 0, MPCDL_PREC_TF32X3 = 1, MPCDL_PREC_TF32 = 2 };
+ * TF32 = one TF32 pass + MUFU.TANH activations.  State, accumulation, statistics and cost stay FP32.
+ * BF16 = the wide LSTM (hidden 256, window <= 4, stateless, no noise net): gate GEMMs [128 x 256].[256 x 1024] on
+ * tcgen05 with BF16 operands, FP32 accumulation, FP32 cell state; needs a device scratch (mpcdl_rollout_scratch_bytes). */
+enum { MPCDL_PREC_FP32 = 0, MPCDL_PREC_TF32X3 = 1, MPCDL_PREC_TF32 = 2, MPCDL_PREC_BF16 = 3 };
 enum { MPCDL_ACT_IDENTITY = 0, MPCDL_ACT_RELU = 1, MPCDL_ACT_TANH = 2, MPCDL_ACT_SIGMOID = 3 };
 enum {
     MPCDL_OK = 0,
@@ -116,6 +118,10 @@ typedef struct {
     int32_t sample_controls, shared_init;
     float ctrl_sigma[2], ctrl_lo[2], ctrl_hi[2];
     uint64_t ctrl_seed;
+    /* MPCDL_PREC_BF16 only: device workspace of >= mpcdl_rollout_scratch_bytes(args) bytes (the per-CTA layer output
+     * sequences in BF16 operand layout); borrowed for the duration of the launch, contents undefined afterwards. */
+    void* scratch;
+    uint64_t scratch_bytes;
 } mpcdl_rollout_args;
 
 /* The fused closed loop.  Replaces, batched over N trajectories and H steps in ONE launch:
@@ -127,11 +133,14 @@ typedef struct {
  * (model_scripts/eval_models.py:86). `stream` is a cudaStream_t (NULL = default stream). */
 int mpcdl_rollout(const mpcdl_rollout_args* args, void* stream);
 
+/* Bytes of args->scratch that mpcdl_rollout needs for these args (0 unless precision = MPCDL_PREC_BF16). */
+size_t mpcdl_rollout_scratch_bytes(const mpcdl_rollout_args* args);
+
 /* What mpcdl_rollout would launch for these args (no launch): tile size, grid, smem, config. */
 typedef struct {
     int32_t rt, rj, n_tg, tile_traj, threads, grid, smem_bytes, resident, nslots, slot_floats, ntiles;
     int32_t variant;           /* 0 = generic ring-fed kernel, 2 = weight-resident MLP kernel,
-                                  4 = tcgen05 GRU/LSTM kernel, 5 = tcgen05 MLP kernel                        */
+                                  4 = tcgen05 GRU/LSTM kernel, 5 = tcgen05 MLP kernel, 6 = BF16 tcgen05 LSTM-256                     */
     int32_t ksplit;            /* K slices of a hidden layer (weight-resident MLP kernel)                   */
 } mpcdl_plan;
 int mpcdl_rollout_plan(const mpcdl_rollout_args* args, mpcdl_plan* plan);

@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -307,6 +308,35 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
     return MPCDL_OK;
 }
 
+// ---------------------------------------------------------------------------- BF16 tensor-core LSTM, hidden 256 (rollout_lstm_tc.cu)
+bool lt_supported(const mpcdl_model_desc& d) {
+    return d.kind == MPCDL_LSTM && d.hidden == LT_HID && d.window >= 1 && lt_layout(d.window).total <= SMEM_LIMIT;
+}
+// blob: [bias L x 1024][fc 256 x 8 + 8][pad to 32 floats][bf16 weight slots, lstm_tc_params.h]; returns total floats
+uint32_t build_lt_offsets(const mpcdl_model_desc& d, LtModel& m) {
+    uint32_t off = 0;
+    m.bias_off = off; off += (uint32_t)d.layers * 4 * LT_HID;
+    m.fc_off = off;   off += LT_HID * 8 + 8;
+    off = (off + 31u) / 32u * 32u;
+    m.w_off = off;
+    off += (lt_layer_off_bytes(d.layers - 1) + lt_layer_bytes(d.layers - 1)) / 4;
+    m.layers = d.layers; m.window = d.window;
+    return off;
+}
+uint16_t bf16_rne_host(float x) {         // cvt.rn.bf16.f32 (finite inputs)
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    u += 0x7FFFu + ((u >> 16) & 1u);
+    return (uint16_t)(u >> 16);
+}
+struct LtPlan { int smem_bytes, ntiles, grid; };
+void make_lt_plan(const mpcdl_rollout_args& a, LtPlan& pl, int num_sms) {
+    pl.smem_bytes = lt_layout(a.model.window).total;
+    pl.ntiles = (int)((a.N + LT_TN - 1) / LT_TN);
+    pl.grid = std::min(pl.ntiles, num_sms);
+}
+bool is_lt(const mpcdl_rollout_args& a) { return a.precision == MPCDL_PREC_BF16; }
+
 bool tc_supported(const mpcdl_model_desc& d);
 bool mc_supported(const mpcdl_model_desc& d);
 int check_args(const mpcdl_rollout_args* a) {
@@ -318,7 +348,16 @@ int check_args(const mpcdl_rollout_args* a) {
         return fail(MPCDL_ERR_ARG, "wblob/norm/init/U must be non-NULL device pointers");
     if (!a->states && !a->costs) return fail(MPCDL_ERR_ARG, "both outputs (states, costs) are NULL");
     if (a->model.kind != MPCDL_MLP && a->stateful && !a->carry) return fail(MPCDL_ERR_ARG, "stateful rollout needs a carry buffer");
-    if (a->precision != MPCDL_PREC_FP32) {
+    if (a->precision == MPCDL_PREC_BF16) {
+        if (!lt_supported(a->model))
+            return fail(MPCDL_ERR_UNSUPPORTED, "MPCDL_PREC_BF16 is the LSTM hidden=%d kernel (window <= 4); got kind=%d hidden=%d window=%d",
+                        LT_HID, a->model.kind, a->model.hidden, a->model.window);
+        if (a->stateful || a->noise_wblob) return fail(MPCDL_ERR_UNSUPPORTED, "MPCDL_PREC_BF16: stateless models without the residual-noise net only; use MPCDL_PREC_FP32");
+        if (!a->wblob_tc) return fail(MPCDL_ERR_ARG, "MPCDL_PREC_BF16 needs wblob_tc (mpcdl_pack_rnn_tc)");
+        const size_t need = mpcdl_rollout_scratch_bytes(a);
+        if (!a->scratch || a->scratch_bytes < need)
+            return fail(MPCDL_ERR_ARG, "MPCDL_PREC_BF16 needs a device scratch of %zu bytes (mpcdl_rollout_scratch_bytes), got %llu", need, (unsigned long long)a->scratch_bytes);
+    } else if (a->precision != MPCDL_PREC_FP32) {
         if (a->precision != MPCDL_PREC_TF32X3 && a->precision != MPCDL_PREC_TF32) return fail(MPCDL_ERR_ARG, "unknown precision %d", a->precision);
         if (!tc_supported(a->model) && !mc_supported(a->model))
             return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core precision needs hidden=%d (GRU/LSTM: window=%d); got kind=%d hidden=%d window=%d; use MPCDL_PREC_FP32",
@@ -421,9 +460,52 @@ int mpcdl_pack_rnn(const mpcdl_model_desc* desc, const float* const* w_ih, const
 }
 
 
+namespace {
+// BF16 blob of the hidden-256 LSTM kernel (layout: lstm_tc_params.h)
+int pack_lt(const mpcdl_model_desc& d, const float* const* w_ih, const float* const* w_hh, const float* const* b_ih,
+            const float* const* b_hh, const float* fc_w, const float* fc_b, float* blob) {
+    LtModel m;
+    const uint32_t total = build_lt_offsets(d, m);
+    std::fill(blob, blob + total, 0.f);
+    const int h = LT_HID;
+    for (int l = 0; l < d.layers; ++l)
+        for (int c = 0; c < LT_NCH; ++c)
+            for (int g = 0; g < 4; ++g)
+                for (int j = 0; j < LT_CH; ++j) {
+                    const int r = g * h + c * LT_CH + j;
+                    blob[m.bias_off + (size_t)l * 4 * h + c * 256 + g * LT_CH + j] = b_ih[l][r] + b_hh[l][r];
+                }
+    float* fc = blob + m.fc_off;                                       // [j][8] then bias[8]
+    for (int dd = 0; dd < 6; ++dd) {
+        fc[h * 8 + dd] = fc_b[dd];
+        for (int j = 0; j < h; ++j) fc[j * 8 + dd] = fc_w[dd * h + j];
+    }
+    unsigned char* wb = reinterpret_cast<unsigned char*>(blob + m.w_off);
+    // one slot: [k/8][n/8][8 rows][8 k] bf16, n = 0..255 (row n -> torch row (n/64)*256 + 64c + n%64), k = k0 .. k0+nk
+    auto fill_slot = [&](unsigned char* slot, const float* W, int K, int c, int k0, int nk, int kmod) {
+        uint16_t* o = reinterpret_cast<uint16_t*>(slot);
+        for (int kk = 0; kk < nk; ++kk)
+            for (int n = 0; n < 256; ++n) {
+                const int row = (n / LT_CH) * h + c * LT_CH + n % LT_CH;
+                const int k = (k0 + kk) % kmod;
+                o[((size_t)(kk / 8) * 32 + n / 8) * 64 + (n % 8) * 8 + kk % 8] = bf16_rne_host(W[(size_t)row * K + k]);
+            }
+    };
+    for (int l = 0; l < d.layers; ++l)
+        for (int c = 0; c < LT_NCH; ++c) {
+            unsigned char* p = wb + lt_layer_off_bytes(l) + (size_t)c * lt_chunk_bytes(l);
+            if (l == 0) { fill_slot(p, w_ih[0], 8, c, 0, 16, 8); p += lt_x0_slot_bytes(); }      // [W | W] against [x_hi | x_lo]
+            else for (int sl = 0; sl < 8; ++sl, p += LT_SLOT_BYTES) fill_slot(p, w_ih[l], h, c, sl * LT_KS, LT_KS, h);
+            for (int sl = 0; sl < 8; ++sl, p += LT_SLOT_BYTES) fill_slot(p, w_hh[l], h, c, sl * LT_KS, LT_KS, h);
+        }
+    return MPCDL_OK;
+}
+}  // namespace
+
 size_t mpcdl_blob_floats_tc(const mpcdl_model_desc* desc) {
     if (check_desc(desc)) return 0;
     if (mc_supported(*desc)) { McModel m; return build_mc_offsets(*desc, true, m); }
+    if (lt_supported(*desc)) { LtModel m; return build_lt_offsets(*desc, m); }
     if (!tc_supported(*desc)) { fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: hidden=%d only (GRU/LSTM: window=%d)", TC_HID, TC_T); return 0; }
     TcPart parts[2 * MAX_LAYERS];
     uint32_t bo, fo;
@@ -434,8 +516,9 @@ int mpcdl_pack_rnn_tc(const mpcdl_model_desc* desc, const float* const* w_ih, co
                       const float* const* b_ih, const float* const* b_hh, const float* fc_w, const float* fc_b, float* blob) {
     int rc = check_desc(desc);
     if (rc) return rc;
-    if (!tc_supported(*desc)) return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: GRU/LSTM with hidden=%d window=%d only", TC_HID, TC_T);
     if (!w_ih || !w_hh || !b_ih || !b_hh || !fc_w || !fc_b || !blob) return fail(MPCDL_ERR_ARG, "mpcdl_pack_rnn_tc: bad arguments");
+    if (lt_supported(*desc)) return pack_lt(*desc, w_ih, w_hh, b_ih, b_hh, fc_w, fc_b, blob);
+    if (!tc_supported(*desc)) return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: GRU/LSTM with hidden=%d window=%d, or LSTM hidden=%d, only", TC_HID, TC_T, LT_HID);
     TcPart parts[2 * MAX_LAYERS];
     uint32_t bias_off, fc_off;
     const uint32_t total = build_tc_parts(*desc, parts, bias_off, fc_off);
@@ -536,11 +619,27 @@ int mpcdl_pack_noise(int history, int size, int n_layers, const float* const* W,
     return MPCDL_OK;
 }
 
+size_t mpcdl_rollout_scratch_bytes(const mpcdl_rollout_args* a) {
+    if (!a || a->precision != MPCDL_PREC_BF16 || !lt_supported(a->model) || a->N < 1) return 0;
+    LtPlan lp;
+    make_lt_plan(*a, lp, g_num_sms ? g_num_sms : 148);
+    return (size_t)lp.grid * lt_scratch_bytes_per_cta(a->model.window);
+}
+
 int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
     int rc = check_args(a);
     if (rc) return rc;
     if (!out) return fail(MPCDL_ERR_ARG, "plan is NULL");
     int sms = g_num_sms ? g_num_sms : 148;                   // planning works without a device (B200 = 148 SMs)
+    if (is_lt(*a)) {
+        LtPlan lp;
+        make_lt_plan(*a, lp, sms);
+        memset(out, 0, sizeof(*out));
+        out->rt = 1; out->rj = 16; out->n_tg = LT_TN; out->tile_traj = LT_TN; out->threads = LT_THREADS; out->grid = lp.grid;
+        out->smem_bytes = lp.smem_bytes; out->resident = 0; out->nslots = LT_NSLOTS; out->slot_floats = LT_SLOT_BYTES / 4;
+        out->ntiles = lp.ntiles; out->variant = 6; out->ksplit = 1;
+        return MPCDL_OK;
+    }
     if (a->precision != MPCDL_PREC_FP32 && a->model.kind == MPCDL_MLP) {
         McPlan mp;
         rc = make_mc_plan(*a, mp, sms);
@@ -577,6 +676,20 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     if (rc) return rc;
     if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (is_lt(*a)) {
+        LtPlan lp;
+        make_lt_plan(*a, lp, g_num_sms);
+        LtRolloutParams q;
+        memset(&q, 0, sizeof(q));
+        build_lt_offsets(a->model, q.m);
+        q.m.blob = a->wblob_tc;
+        q.scratch = static_cast<unsigned char*>(a->scratch);
+        if (const char* e = getenv("MPCDL_LT_DBG")) q.dbg = reinterpret_cast<unsigned int*>(strtoull(e, nullptr, 0));
+        fill_io(q.io, *a, lp.ntiles);
+        cudaError_t e = launch_lstm_tc(q, lp.grid, lp.smem_bytes, st);
+        if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "BF16 LSTM kernel launch failed: %s (smem=%d)", cudaGetErrorString(e), lp.smem_bytes);
+        return MPCDL_OK;
+    }
     if (a->precision != MPCDL_PREC_FP32 && a->model.kind == MPCDL_MLP) {
         McPlan mp;
         rc = make_mc_plan(*a, mp, g_num_sms);

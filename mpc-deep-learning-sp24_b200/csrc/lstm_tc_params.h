@@ -1,0 +1,71 @@
+// Parameter block, blob layout and shared-memory carve-up of the BF16 tcgen05 LSTM rollout kernel for wide
+// hidden states (rollout_lstm_tc.cu; BASELINE.json config 4: LSTM hidden 256).  Host + device.
+#pragma once
+#include <cstdint>
+#include "params.h"
+
+namespace mpcdl {
+
+constexpr int LT_TN = 128;             // trajectories per CTA tile = MMA M (one TMEM lane per trajectory)
+constexpr int LT_HID = 256;            // hidden units
+constexpr int LT_CH = 64;              // hidden units per gate chunk: D chunk = [i|f|g|o] x 64 = 256 TMEM columns
+constexpr int LT_NCH = LT_HID / LT_CH; // 4 chunks per cell
+constexpr int LT_KS = 32;              // K rows per weight slot: [256 gate rows][32 k] bf16 = 16 KB = two K=16 MMAs
+constexpr int LT_SLOT_BYTES = 256 * LT_KS * 2;
+constexpr int LT_NSLOTS = 4;
+constexpr int LT_EPI_WARPS = 16;       // lane quarter = warp % 4, unit group (16 of a chunk's 64) = warp / 4
+constexpr int LT_THREADS = (LT_EPI_WARPS + 4) * 32;   // + one control warpgroup: weight producer warp, MMA issuer warp, two idle
+                                                      // (setmaxnreg moves registers between whole warpgroups)
+constexpr int LT_A_BYTES = LT_TN * LT_HID * 2;        // one A operand tile [128 x 256] bf16 = 64 KB
+constexpr int LT_A_LBO = (LT_TN / 8) * 128;           // bytes between 16-B k-chunks of an A tile (2048)
+constexpr int LT_B_LBO = (256 / 8) * 128;             // same for a weight slot (4096)
+
+// blob (float units; the weight region holds bf16 pairs):
+//   [bias  L x 1024 : [l][chunk][gate][64]  (b_ih + b_hh)]
+//   [fc    256 x 8 (W^T, cols 6..7 zero) + 8 (bias)]        [pad to 32 floats]
+//   [layer 0: per chunk {x slot K = 16 ([x_hi | x_lo] against [W | W]) 8 KB, 8 h slots of 16 KB}]
+//   [layer l > 0: per chunk {8 x slots, 8 h slots}]
+// a slot is the canonical K-major no-swizzle UMMA block [k/8][n/8][8 rows][8 k] bf16; row n of chunk c is
+// gate n / 64, unit 64 c + n % 64  (torch row gate * 256 + unit, gate order i, f, g, o).
+struct LtModel {
+    const float* blob;
+    uint32_t bias_off, fc_off, w_off;      // float offsets
+    int layers, window;
+};
+__host__ __device__ inline uint32_t lt_x0_slot_bytes() { return 256 * 16 * 2; }
+__host__ __device__ inline uint32_t lt_layer_bytes(int l) {
+    return l == 0 ? LT_NCH * (lt_x0_slot_bytes() + 8 * LT_SLOT_BYTES) : LT_NCH * 16 * LT_SLOT_BYTES;
+}
+__host__ __device__ inline uint32_t lt_layer_off_bytes(int l) {       // from w_off
+    return l == 0 ? 0u : lt_layer_bytes(0) + (uint32_t)(l - 1) * lt_layer_bytes(1);
+}
+__host__ __device__ inline uint32_t lt_chunk_bytes(int l) { return lt_layer_bytes(l) / LT_NCH; }
+
+struct LtRolloutParams {
+    LtModel m;
+    NoiseParams nz;             // always disabled (owner_finish reads nz.enabled)
+    IoParams io;
+    unsigned int* dbg;          // development aid (MPCDL_LT_DEBUG builds): host-mapped words, else unused
+    unsigned char* scratch;     // per CTA: [2 layer parities][T frames] A tiles of 64 KB (the layer output sequences)
+};
+__host__ __device__ inline size_t lt_scratch_bytes_per_cta(int window) { return (size_t)2 * window * LT_A_BYTES; }
+
+struct LtSmem {        // byte offsets
+    int ax, ah, ring, xwin, bias, fc, norm, bars, total;
+};
+__host__ __device__ inline LtSmem lt_layout(int window) {
+    LtSmem L;
+    int o = 0;
+    L.ax = o;    o += LT_A_BYTES;                       // also: layer-0 tile [0, 4 KB), head partials [8 KB, 17 KB)
+    L.ah = o;    o += LT_A_BYTES;
+    L.ring = o;  o += LT_NSLOTS * LT_SLOT_BYTES;
+    L.xwin = o;  o += window * 8 * LT_TN * 4;           // raw frames [T][8][128] FP32
+    L.bias = o;  o += 1024 * 4;                         // current layer
+    L.fc = o;    o += (LT_HID * 8 + 8) * 4;
+    L.norm = o;  o += ((2 * window * 8 + 12 + 3) / 4 * 4) * 4;
+    L.bars = o;  o += 256;
+    L.total = o;
+    return L;
+}
+
+}  // namespace mpcdl

@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmpcdl.so")
 
 MLP, GRU, LSTM = 0, 1, 2
-PRECISION = {"fp32": 0, "tf32x3": 1, "tf32": 2}
+PRECISION = {"fp32": 0, "tf32x3": 1, "tf32": 2, "bf16": 3}
 ACT = {"identity": 0, "relu": 1, "tanh": 2, "sigmoid": 3}
 
 
@@ -56,6 +56,8 @@ class RolloutArgs(C.Structure):
         ("ctrl_lo", C.c_float * 2),
         ("ctrl_hi", C.c_float * 2),
         ("ctrl_seed", C.c_uint64),
+        ("scratch", C.c_void_p),
+        ("scratch_bytes", C.c_uint64),
     ]
 
 
@@ -101,7 +103,7 @@ class Plan(C.Structure):
 
 
 EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_pack_mlp_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
-           "mpcdl_rollout", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version")
+           "mpcdl_rollout", "mpcdl_rollout_scratch_bytes", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version")
 
 
 def _load():
@@ -129,6 +131,8 @@ def _load():
     lib.mpcdl_pack_noise.argtypes = [C.c_int, C.c_int, C.c_int, fpp, fpp, fp]
     lib.mpcdl_rollout.restype = C.c_int
     lib.mpcdl_rollout.argtypes = [C.POINTER(RolloutArgs), C.c_void_p]
+    lib.mpcdl_rollout_scratch_bytes.restype = C.c_size_t
+    lib.mpcdl_rollout_scratch_bytes.argtypes = [C.POINTER(RolloutArgs)]
     lib.mpcdl_rollout_plan.restype = C.c_int
     lib.mpcdl_rollout_plan.argtypes = [C.POINTER(RolloutArgs), C.POINTER(Plan)]
     lib.mpcdl_noise_forward.restype = C.c_int

@@ -84,7 +84,8 @@ class _RolloutMixin:
         noise FeedforwardNoiseModel (residual injection); eps [N,H,6] draws or None -> Philox(seed).
         cost  (ref [H,6], qw [6], rw [2]) -> per-trajectory quadratic tracking cost.
         precision "fp32" (FFMA kernels, the parity path) | "tf32x3" | "tf32" (tcgen05 tensor-core kernels,
-              GRU/LSTM hidden 64 window 4 only; anything else raises -- there is no silent fallback).
+              GRU/LSTM hidden 64 window 4 only) | "bf16" (tcgen05 kernel of the LSTM with hidden 256: BF16
+              operands, FP32 accumulation and cell state); anything else raises -- there is no silent fallback.
         sample  MPPI call: dict(n=N, sigma=(s_a, s_steer), lo=(..), hi=(..), seed=int) -> U is the NOMINAL sequence
               [H,2] and trajectory n applies clamp(U + sigma * z_n) with z_n drawn in-kernel (Philox keyed by
               seed, traj_offset + n, t); no [N,H,2] tensor exists.  shared_init: init is ONE state / window.
@@ -108,7 +109,7 @@ class _RolloutMixin:
             cref, cw = self._cost(cost, dev)
         precision = getattr(self, "precision", "fp32") if precision is None else precision
         if precision not in _lib.PRECISION:
-            raise RuntimeError(f"mpcdl: unknown precision {precision!r} (fp32 | tf32x3 | tf32)")
+            raise RuntimeError(f"mpcdl: unknown precision {precision!r} (fp32 | tf32x3 | tf32 | bf16)")
         prec = _lib.PRECISION[precision]
         states, costs = ops.OPS[self.KIND](self._blob(dev), self._norm(stats, dev), init, U, hidden, layers, window,
                                            stateful, carry if stateful else None, nblob, ncfg, eps, int(seed),

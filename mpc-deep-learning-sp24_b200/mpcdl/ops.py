@@ -120,6 +120,12 @@ def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, state
         a.ctrl_sigma, a.ctrl_lo, a.ctrl_hi = (C.c_float * 2)(*ctrl[0:2]), (C.c_float * 2)(*ctrl[2:4]), (C.c_float * 2)(*ctrl[4:6])
         a.ctrl_seed = ctrl_seed & 0xFFFFFFFFFFFFFFFF
     a.shared_init = int(bool(shared_init))
+    nscratch = _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a))
+    if nscratch:
+        # per-CTA layer output sequences of the BF16 LSTM-256 kernel; from the caching allocator, so the buffer is
+        # tied to the current stream like every other tensor of the call
+        scratch = torch.empty(nscratch, device=dev, dtype=torch.uint8)
+        a.scratch, a.scratch_bytes = scratch.data_ptr(), nscratch
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev).cuda_stream
         _lib.check(_lib.lib.mpcdl_rollout(C.byref(a), C.c_void_p(stream)))
@@ -290,6 +296,7 @@ def plan(kind, hidden, layers, window, N, H, stateful=False, noise_cfg=None, tun
     a.N, a.H = N, H
     if len(tune) == 4:
         a.tune_rt, a.tune_ntg, a.tune_nslots, a.tune_kc = tune
+    a.scratch, a.scratch_bytes = 16, _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a))
     p = _lib.Plan()
     _lib.check(_lib.lib.mpcdl_rollout_plan(C.byref(a), C.byref(p)))
     return p.as_dict()

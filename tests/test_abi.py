@@ -118,6 +118,20 @@ def test_tensor_core_plans_and_errors():
             assert 120 * 1024 <= p["smem_bytes"] <= 232448 and p["threads"] % 32 == 0 and p["threads"] <= 1024
     d = _lib.ModelDesc(_lib.GRU, 32, 2, 4)
     assert _lib.lib.mpcdl_blob_floats_tc(C.byref(d)) == 0
+    # BF16 tcgen05 kernel of the hidden-256 LSTM (rollout_lstm_tc.cu): 128-trajectory tiles, 16 epilogue warps + one
+    # control warpgroup, a per-CTA scratch of 2 x window operand tiles; everything else refuses the precision
+    p = ops.plan(2, 256, 4, 4, 65536, 100, precision="bf16")
+    assert p["variant"] == 6 and p["tile_traj"] == 128 and p["threads"] == 640 and p["grid"] == 148 and p["ntiles"] == 512
+    assert p["smem_bytes"] <= 232448
+    a = _lib.RolloutArgs()
+    a.model, a.precision, a.N, a.H = _lib.ModelDesc(2, 256, 4, 4), 3, 1000, 5
+    assert _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a)) == 8 * 2 * 4 * 128 * 256 * 2
+    a.precision = 0
+    assert _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a)) == 0
+    for args, kw in [((2, 64, 4, 4), {}), ((1, 256, 4, 4), {}), ((2, 256, 4, 8), {}), ((2, 256, 4, 4), dict(stateful=True)),
+                     ((2, 256, 4, 4), dict(noise_cfg=[3, 32, 2, 2]))]:
+        with pytest.raises(RuntimeError):
+            ops.plan(*args, 100, 5, precision="bf16", **kw)
 
 
 def test_mppi_entry_points_without_device():

@@ -266,3 +266,57 @@ def test_pack_mlp_tensor_core_layout():
         assert pos == blob.size
     with pytest.raises(RuntimeError):                # hidden 16: FP32 kernels only
         pack.pack_mlp(load_ckpt("Basic_16_1_32"), 16, 1, tensor_core=True)
+
+
+def test_pack_lstm256_bf16_layout():
+    """mpcdl_pack_rnn_tc for the hidden-256 LSTM (rollout_lstm_tc.cu, BASELINE config 4) against a numpy restatement:
+    BF16 round-to-nearest-even, per layer / 64-unit chunk the x slots then the h slots, every slot the canonical
+    K-major UMMA block [k/8][n/8][8 rows][8 k] with row n = gate n/64, unit 64*chunk + n%64; layer 0 holds [W | W]
+    (K = 16) against the [x_hi | x_lo] operand."""
+    import numpy as np
+    import torch
+    from mpcdl import _lib, pack
+
+    def bf16(x):
+        u = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32)
+        return ((u + np.uint32(0x7FFF) + ((u >> np.uint32(16)) & np.uint32(1))) >> np.uint32(16)).astype(np.uint16)
+
+    torch.manual_seed(0)
+    L, h = 2, 256
+    ref = torch.nn.ModuleDict(dict(lstm=torch.nn.LSTM(8, h, L, batch_first=True), full_c=torch.nn.Linear(h, 6)))
+    sd = {k: v.detach() for k, v in ref.state_dict().items()}
+    blob = pack.pack_rnn(sd, _lib.LSTM, h, L, 4, tensor_core=True).numpy()
+    assert torch.equal(torch.from_numpy(bf16(np.float32([1.0, 1.00390625, 1.01171875, -3.1415927]))).to(torch.int32),
+                       torch.tensor([1.0, 1.00390625, 1.01171875, -3.1415927]).to(torch.bfloat16).view(torch.int16).to(torch.int32) & 0xFFFF)
+    for l in range(L):
+        b = (sd[f"lstm.bias_ih_l{l}"] + sd[f"lstm.bias_hh_l{l}"]).numpy().reshape(4, 4, 64)        # [gate][chunk][j]
+        assert np.array_equal(blob[l * 1024:(l + 1) * 1024].reshape(4, 4, 64), b.transpose(1, 0, 2))
+    off = L * 1024
+    assert np.array_equal(blob[off:off + h * 8].reshape(h, 8)[:, :6], sd["full_c.weight"].numpy().T)
+    assert np.array_equal(blob[off + h * 8:off + h * 8 + 6], sd["full_c.bias"].numpy())
+    pos = (off + h * 8 + 8 + 31) // 32 * 32
+    w16 = blob[pos:].view(np.uint16)
+    p = 0
+
+    def slot(W, c, ks):                      # -> the [256 rows][len(ks)] block of chunk c in slot order
+        rows = np.array([(n // 64) * h + c * 64 + n % 64 for n in range(256)])
+        blk = bf16(W[rows][:, ks])                                                                  # [n][kk]
+        return blk.reshape(32, 8, len(ks) // 8, 8).transpose(2, 0, 1, 3).reshape(-1)               # [kk/8][n/8][n%8][kk%8]
+
+    for l in range(L):
+        wi, wh = sd[f"lstm.weight_ih_l{l}"].numpy(), sd[f"lstm.weight_hh_l{l}"].numpy()
+        for c in range(4):
+            if l == 0:
+                want = slot(wi, c, np.arange(16) % 8)
+                assert np.array_equal(w16[p:p + want.size], want), (l, c, "x0")
+                p += want.size
+            else:
+                for s in range(8):
+                    want = slot(wi, c, np.arange(32 * s, 32 * s + 32))
+                    assert np.array_equal(w16[p:p + want.size], want), (l, c, "x", s)
+                    p += want.size
+            for s in range(8):
+                want = slot(wh, c, np.arange(32 * s, 32 * s + 32))
+                assert np.array_equal(w16[p:p + want.size], want), (l, c, "h", s)
+                p += want.size
+    assert p == w16.size

@@ -1,0 +1,28 @@
+"""Development aid: one tiny BF16 LSTM-256 rollout (for compute-sanitizer)."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "mpc-deep-learning-sp24_b200"))
+import torch, mpcdl, bench
+from mpcdl import synth
+dev = torch.device("cuda:0")
+N, H, L = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
+name = f"LSTM_256_{L}_4_0_False"
+m, meta = mpcdl.from_checkpoint_name(name, bench.load_ckpt(name), dev)
+dbg = torch.zeros(64, dtype=torch.int32).pin_memory()      # MPCDL_LT_DEBUG builds: progress words + timed-out waits
+os.environ["MPCDL_LT_DBG"] = hex(dbg.data_ptr())
+NAMES = ["producer:empty", "mma:full", "mma:d_empty", "mma:ax_full", "mma:ah_full", "epi:d_full"]
+def report():
+    d = dbg.numpy().view("uint32")
+    print(f"progress: epilogue chunks {d[0]}  mma chunks {d[1]}  slots produced {d[2]}")
+    for i, n in enumerate(NAMES):
+        if d[16 + 2 * i]:
+            print(f"  TIMEOUT {n}: cta {d[16 + 2 * i] & 0xFFFF} count {d[17 + 2 * i]}")
+init, U = synth.make_inputs(synth.load_rows(), N, H, window=4, seed=3)
+try:
+    y = m.rollout(init.to(dev), U.to(dev), bench.load_stats(4), precision="bf16")[0]
+    torch.cuda.synchronize()
+except Exception as ex:
+    print("FAILED:", str(ex).splitlines()[0]); report(); sys.exit(1)
+report()
+y32 = m.rollout(init.to(dev), U.to(dev), bench.load_stats(4), precision="fp32")[0]
+print("ok", N, H, L, "max abs diff vs fp32 kernel", (y - y32).abs().max().item(), "nan", int(torch.isnan(y).sum()), flush=True)
