@@ -1,0 +1,138 @@
+"""GPU parity tests of the BF16 tcgen05 kernel for the wide LSTM (rollout_lstm_tc.cu; BASELINE.json config 4:
+"LSTM rnn_model rollout, hidden 256, BF16 tensor-core path vs FP32 tolerance study").
+
+The reference ships no hidden-256 checkpoint: the weights are LSTM_Model(8, 256, 6, L, False) under
+torch.manual_seed(0), the oracle is the reference module definition in the closed loop
+(oracle/rollout_ref.py), run in FP32 and FP64 on the same inputs.
+
+T3 bounds stated for this path (rel err = max_d |dy_d| / max|ref_d| per trajectory-step; measured on B200:
+one-step max 5.7e-4, H = 20 p50 2.1e-4 / p90 3.8e-4 / p99 5.3e-4 / max 6.7e-4, profiles/r01f/lt_check.log):
+  one-step (vs torch FP32)      <= 2e-3
+  H = 20 vs the FP64 oracle     p50 <= 6e-4, p90 <= 1.2e-3, p99 <= 2e-3
+Other depths / windows of the same family (random init, some output dimensions nearly zero, so the metric's
+denominator max|ref_d| is small; measured: 3 layers one-step max 4.0e-3, absolute difference 4e-5):
+  one-step <= 1e-2;  p50 <= 3e-3, p90 <= 6e-3, p99 <= 1e-2
+The FP32 FFMA kernel on the same model stays inside T1 / T2 (one-step <= 1e-5).
+"""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ONE_STEP, QUANT = 2e-3, (6e-4, 1.2e-3, 2e-3)            # config 4: 4 layers, window 4
+ONE_STEP_ANY, QUANT_ANY = 1e-2, (3e-3, 6e-3, 1e-2)      # any other depth / window
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _sd(layers, hidden=256):
+    torch.manual_seed(0)
+    ref = torch.nn.ModuleDict(dict(lstm=torch.nn.LSTM(8, hidden, layers, batch_first=True), full_c=torch.nn.Linear(hidden, 6)))
+    return {k: v.detach().clone() for k, v in ref.state_dict().items()}
+
+
+def _pair(layers, window=4):
+    import mpcdl
+    from oracle import rollout_ref as R
+    name = f"LSTM_256_{layers}_{window}_0_False"
+    sd = _sd(layers)
+    m, _ = mpcdl.from_checkpoint_name(name, sd, _dev())
+    ref, _ = R.build_from_name(name, sd)
+    return m, ref
+
+
+def _quantiles(e):
+    e = e.flatten().double()
+    return [torch.quantile(e, x).item() for x in (0.5, 0.9, 0.99)]
+
+
+def _stats(gold_stats, window):
+    st = gold_stats[1]
+    if window == 4:
+        return st
+    return dict(f_mean=st["f_mean"][:window].contiguous(), f_std=st["f_std"][:window].contiguous(), l_mean=st["l_mean"], l_std=st["l_std"])
+
+
+@pytest.mark.parametrize("layers,window,N,H", [(4, 4, 300, 20), (2, 4, 129, 6), (1, 4, 128, 3), (3, 3, 77, 5), (2, 1, 40, 4)])
+def test_t3_bf16_lstm256_horizon(layers, window, N, H, gold_stats):
+    """Ragged N (partial last tile), several depths / windows: one-step against torch FP32, quantiles against FP64."""
+    from mpcdl import synth
+    from oracle import rollout_ref as R
+    m, ref = _pair(layers, window)
+    st = _stats(gold_stats, window)
+    init, U = synth.make_inputs(synth.load_rows(), N, H, window=window, seed=3)
+    y32 = R.rollout_rnn(ref, st, init, U, stateful=False)[0]
+    y64 = R.rollout_rnn(R.as_double(ref), {k: v.double() for k, v in st.items()}, init.double(), U.double(), stateful=False)[0]
+    y = m.rollout(init.to(_dev()), U.to(_dev()), st, precision="bf16")[0].cpu()
+    assert y.shape == (N, H, 6) and not torch.isnan(y).any()
+    one, quant = (ONE_STEP, QUANT) if (layers, window) == (4, 4) else (ONE_STEP_ANY, QUANT_ANY)
+    assert R.rel_err(y, y32)[:, 0].max().item() <= one
+    q = _quantiles(R.rel_err(y, y64))
+    for a, b in zip(q, quant):
+        assert a <= b, (q, quant)
+    # the FP32 FFMA kernel of the same model is the parity path: T1 one-step
+    yk = m.rollout(init.to(_dev()), U.to(_dev()), st, precision="fp32")[0].cpu()
+    assert R.rel_err(yk, y32)[:, 0].max().item() <= 1e-5
+
+
+def test_bf16_lstm256_multi_tile_cost_and_shards(gold_stats):
+    """More tiles than SMs (CTAs loop over tiles), cost-only mode, bitwise repeatability, shard invariance."""
+    from mpcdl import synth
+    m, _ = _pair(2)
+    st = gold_stats[1]
+    N, H = 148 * 128 + 77, 3
+    rows = synth.load_rows()
+    init, U = synth.make_inputs(rows, N, H, window=4, seed=5)
+    init, U = init.to(_dev()), U.to(_dev())
+    cost = tuple(c.to(_dev()) for c in synth.make_cost(rows, H))
+    s, c = m.rollout(init, U, st, precision="bf16", cost=cost)
+    s2, c2 = m.rollout(init, U, st, precision="bf16", cost=cost)
+    assert torch.equal(s, s2) and torch.equal(c, c2)
+    _, c3 = m.rollout(init, U, st, precision="bf16", cost=cost, return_states=False)
+    assert torch.equal(c3, c)
+    s32, c32 = m.rollout(init, U, st, precision="fp32", cost=cost)
+    assert ((s - s32).abs().amax((0, 1)) / s32.abs().amax((0, 1))).max().item() <= ONE_STEP_ANY
+    assert ((c - c32).abs() / c32.abs()).max().item() <= 1e-3
+    # a tile-aligned shard gives the same bits as the same trajectories inside the full batch
+    k = 100 * 128
+    part = m.rollout(init[k:].contiguous(), U[k:].contiguous(), st, precision="bf16")[0]
+    assert torch.equal(part, s[k:])
+
+
+def test_bf16_lstm256_sampled_controls_shared_init(gold_stats):
+    """MPPI call form: controls drawn in-kernel around a nominal sequence, one shared initial window; the same
+    Philox stream as the FP32 kernel, so the two precisions roll out the SAME control samples."""
+    from mpcdl import synth
+    m, _ = _pair(2)
+    st = gold_stats[1]
+    rows = synth.load_rows()
+    H = 4
+    init, U = synth.make_inputs(rows, 1, H, window=4, seed=9)
+    cost = tuple(c.to(_dev()) for c in synth.make_cost(rows, H))
+    sample = dict(n=1000, sigma=(0.2, 0.1), lo=(-0.875, -0.285), hi=(0.237, 0.279), seed=11)
+    kw = dict(cost=cost, sample=sample, shared_init=True)
+    sb, cb = m.rollout(init[0].to(_dev()), U[0].to(_dev()), st, precision="bf16", **kw)
+    sf, cf = m.rollout(init[0].to(_dev()), U[0].to(_dev()), st, precision="fp32", **kw)
+    assert sb.shape == (1000, H, 6)
+    assert ((sb - sf).abs().amax((0, 1)) / sf.abs().amax((0, 1))).max().item() <= ONE_STEP_ANY
+    assert ((cb - cf).abs() / cf.abs()).max().item() <= 1e-3
+    half = m.rollout(init[0].to(_dev()), U[0].to(_dev()), st, precision="bf16", traj_offset=512,
+                     cost=cost, sample=dict(sample, n=488), shared_init=True)[0]
+    assert torch.equal(half, sb[512:])
+
+
+def test_bf16_rejects_unsupported(gold_stats):
+    """No silent fallback: BF16 exists for the stateless hidden-256 LSTM without the noise net only."""
+    import mpcdl
+    m, _ = _pair(1)
+    win, U = torch.zeros(8, 4, 8, device=_dev()), torch.zeros(8, 2, 2, device=_dev())
+    with pytest.raises(RuntimeError):
+        m.rollout(win, U, None, precision="bf16", stateful=True)
+    noise = mpcdl.FeedforwardNoiseModel(6, 2, 3, n_layers=2, size=32, activation="tanh", output_activation="identity").to(_dev())
+    with pytest.raises(RuntimeError):
+        m.rollout(win, U, None, precision="bf16", noise=noise)
+    with pytest.raises(RuntimeError):           # hidden 256 has no TF32 kernel
+        m.rollout(win, U, None, precision="tf32")
+    with pytest.raises(RuntimeError):           # CPU tensors: no fallback
+        m.rollout(win.cpu(), U.cpu(), None, precision="bf16")

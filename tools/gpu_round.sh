@@ -43,3 +43,13 @@ if [[ $what == *tcprof* ]]; then
       python bench.py --workload c3 --precision tf32x3 --steps 2 --warmup 3 --skip-cpu > gpurun_out/ncu_full_c3_tf32x3.log 2>&1
 fi
 ls -la gpurun_out
+if [[ $what == *c4bf16* ]]; then
+  timeout 900 python -m pytest tests/test_gpu_lstm256.py -m gpu -x -q > gpurun_out/pytest_lstm256.log 2>&1; echo "pytest lstm256 exit $?" | tee -a gpurun_out/pytest_lstm256.log
+  timeout 600 python bench.py --workload c4 --precision bf16 --steps 10 --warmup 3 > gpurun_out/bench_c4_bf16.json 2> gpurun_out/bench_c4_bf16.err; echo "bench c4 bf16 exit $?"
+  timeout 300 python bench.py --workload c4 --precision bf16 --steps 2 --warmup 3 --skip-cpu > gpurun_out/plain_c4_bf16.log 2>&1 &&
+  timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 100 --csv --log-file gpurun_out/launches_c4_bf16.csv \
+      python bench.py --workload c4 --precision bf16 --steps 2 --warmup 3 --skip-cpu > gpurun_out/ncu_launches_c4_bf16.log 2>&1
+  timeout 120 python tools/tc_prof.py LSTM_256_4_4_0_False bf16 18944 10 > gpurun_out/plain_prof_c4_bf16.log 2>&1 &&
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:rollout_lstm_tc -s 1 -c 1 -f -o gpurun_out/prof_c4_bf16 \
+      python tools/tc_prof.py LSTM_256_4_4_0_False bf16 18944 10 > gpurun_out/ncu_full_c4_bf16.log 2>&1
+fi

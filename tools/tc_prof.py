@@ -11,7 +11,8 @@ dev = torch.device("cuda:0")
 GOLD = os.path.join(ROOT, "tests", "golden")
 ck = lambda n: {k: torch.from_numpy(v) for k, v in np.load(f"{GOLD}/checkpoints/{n}.npz").items()}
 z = np.load(f"{GOLD}/stats.npz")
-m, meta = mpcdl.from_checkpoint_name(name, ck(name), dev)
+import bench
+m, meta = mpcdl.from_checkpoint_name(name, bench.load_ckpt(name), dev)    # hidden-256 LSTM: seeded random init
 pre = "mlp_" if meta["window"] == 0 else "rnn4_"
 st = {k[len(pre):]: torch.from_numpy(z[k]) for k in z.files if k.startswith(pre)}
 init, U = synth.make_inputs(synth.load_rows(), N, H, window=meta["window"], seed=0)
