@@ -333,7 +333,7 @@ struct LtPlan { int smem_bytes, ntiles, grid; };
 void make_lt_plan(const mpcdl_rollout_args& a, LtPlan& pl, int num_sms) {
     pl.smem_bytes = lt_layout(a.model.window).total;
     pl.ntiles = (int)((a.N + LT_TN - 1) / LT_TN);
-    pl.grid = std::min(pl.ntiles, num_sms);
+    pl.grid = 2 * std::min((pl.ntiles + 1) / 2, num_sms / 2);          // CTA pairs (cluster of 2): two tiles per pair
 }
 bool is_lt(const mpcdl_rollout_args& a) { return a.precision == MPCDL_PREC_BF16; }
 
@@ -481,22 +481,24 @@ int pack_lt(const mpcdl_model_desc& d, const float* const* w_ih, const float* co
         for (int j = 0; j < h; ++j) fc[j * 8 + dd] = fc_w[dd * h + j];
     }
     unsigned char* wb = reinterpret_cast<unsigned char*>(blob + m.w_off);
-    // one slot: [k/8][n/8][8 rows][8 k] bf16, n = 0..255 (row n -> torch row (n/64)*256 + 64c + n%64), k = k0 .. k0+nk
+    // one slot: [CTA rank 2][k/8][n/8][8 rows][8 k] bf16; rank r holds rows n = 128 r .. 128 r + 127 of the chunk's 256
+    // (row n -> torch row (n/64)*256 + 64c + n%64), k = k0 .. k0 + nk
     auto fill_slot = [&](unsigned char* slot, const float* W, int K, int c, int k0, int nk, int kmod) {
         uint16_t* o = reinterpret_cast<uint16_t*>(slot);
         for (int kk = 0; kk < nk; ++kk)
             for (int n = 0; n < 256; ++n) {
                 const int row = (n / LT_CH) * h + c * LT_CH + n % LT_CH;
                 const int k = (k0 + kk) % kmod;
-                o[((size_t)(kk / 8) * 32 + n / 8) * 64 + (n % 8) * 8 + kk % 8] = bf16_rne_host(W[(size_t)row * K + k]);
+                const int r = n / 128, nn = n % 128;
+                o[(size_t)r * 128 * nk + ((size_t)(kk / 8) * 16 + nn / 8) * 64 + (nn % 8) * 8 + kk % 8] = bf16_rne_host(W[(size_t)row * K + k]);
             }
     };
     for (int l = 0; l < d.layers; ++l)
         for (int c = 0; c < LT_NCH; ++c) {
             unsigned char* p = wb + lt_layer_off_bytes(l) + (size_t)c * lt_chunk_bytes(l);
-            if (l == 0) { fill_slot(p, w_ih[0], 8, c, 0, 16, 8); p += lt_x0_slot_bytes(); }      // [W | W] against [x_hi | x_lo]
-            else for (int sl = 0; sl < 8; ++sl, p += LT_SLOT_BYTES) fill_slot(p, w_ih[l], h, c, sl * LT_KS, LT_KS, h);
-            for (int sl = 0; sl < 8; ++sl, p += LT_SLOT_BYTES) fill_slot(p, w_hh[l], h, c, sl * LT_KS, LT_KS, h);
+            if (l == 0) { fill_slot(p, w_ih[0], 8, c, 0, 16, 8); p += 2 * lt_x0_slot_bytes(); }  // [W | W] against [x_hi | x_lo]
+            else for (int sl = 0; sl < LT_SPC; ++sl, p += 2 * LT_SLOT_BYTES) fill_slot(p, w_ih[l], h, c, sl * LT_KS, LT_KS, h);
+            for (int sl = 0; sl < LT_SPC; ++sl, p += 2 * LT_SLOT_BYTES) fill_slot(p, w_hh[l], h, c, sl * LT_KS, LT_KS, h);
         }
     return MPCDL_OK;
 }

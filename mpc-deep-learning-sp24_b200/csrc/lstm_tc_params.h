@@ -6,35 +6,37 @@
 
 namespace mpcdl {
 
-constexpr int LT_TN = 128;             // trajectories per CTA tile = MMA M (one TMEM lane per trajectory)
+constexpr int LT_TN = 128;             // trajectories per CTA tile (one TMEM lane per trajectory); a CTA PAIR runs M = 256 MMAs
 constexpr int LT_HID = 256;            // hidden units
 constexpr int LT_CH = 64;              // hidden units per gate chunk: D chunk = [i|f|g|o] x 64 = 256 TMEM columns
 constexpr int LT_NCH = LT_HID / LT_CH; // 4 chunks per cell
-constexpr int LT_KS = 32;              // K rows per weight slot: [256 gate rows][32 k] bf16 = 16 KB = two K=16 MMAs
-constexpr int LT_SLOT_BYTES = 256 * LT_KS * 2;
+constexpr int LT_KS = 64;              // K rows per weight slot: per CTA [128 gate rows][64 k] bf16 = 16 KB = four K=16 MMAs
+constexpr int LT_SPC = LT_HID / LT_KS; // slots per 256-deep operand (4)
+constexpr int LT_SLOT_BYTES = 128 * LT_KS * 2;        // per CTA of the pair (its half of the 256 gate rows)
 constexpr int LT_NSLOTS = 4;
 constexpr int LT_EPI_WARPS = 16;       // lane quarter = warp % 4, unit group (16 of a chunk's 64) = warp / 4
 constexpr int LT_THREADS = (LT_EPI_WARPS + 4) * 32;   // + one control warpgroup: weight producer warp, MMA issuer warp, two idle
                                                       // (setmaxnreg moves registers between whole warpgroups)
 constexpr int LT_A_BYTES = LT_TN * LT_HID * 2;        // one A operand tile [128 x 256] bf16 = 64 KB
 constexpr int LT_A_LBO = (LT_TN / 8) * 128;           // bytes between 16-B k-chunks of an A tile (2048)
-constexpr int LT_B_LBO = (256 / 8) * 128;             // same for a weight slot (4096)
+constexpr int LT_B_LBO = (128 / 8) * 128;             // same for a CTA's half of a weight slot (2048)
 
 // blob (float units; the weight region holds bf16 pairs):
 //   [bias  L x 1024 : [l][chunk][gate][64]  (b_ih + b_hh)]
 //   [fc    256 x 8 (W^T, cols 6..7 zero) + 8 (bias)]        [pad to 32 floats]
-//   [layer 0: per chunk {x slot K = 16 ([x_hi | x_lo] against [W | W]) 8 KB, 8 h slots of 16 KB}]
-//   [layer l > 0: per chunk {8 x slots, 8 h slots}]
-// a slot is the canonical K-major no-swizzle UMMA block [k/8][n/8][8 rows][8 k] bf16; row n of chunk c is
+//   [layer 0: per chunk {x slot K = 16 ([x_hi | x_lo] against [W | W]) 2 x 4 KB, 4 h slots of 2 x 16 KB}]
+//   [layer l > 0: per chunk {4 x slots, 4 h slots}]
+// a slot is [CTA rank 2][k/8][n/8][8 rows][8 k] bf16: each CTA of the pair streams ITS half (128 of the chunk's 256 gate
+// rows: rank 0 = i, f; rank 1 = g, o) as a canonical K-major no-swizzle UMMA block; row n of chunk c is
 // gate n / 64, unit 64 c + n % 64  (torch row gate * 256 + unit, gate order i, f, g, o).
 struct LtModel {
     const float* blob;
     uint32_t bias_off, fc_off, w_off;      // float offsets
     int layers, window;
 };
-__host__ __device__ inline uint32_t lt_x0_slot_bytes() { return 256 * 16 * 2; }
+__host__ __device__ inline uint32_t lt_x0_slot_bytes() { return 128 * 16 * 2; }      // per CTA
 __host__ __device__ inline uint32_t lt_layer_bytes(int l) {
-    return l == 0 ? LT_NCH * (lt_x0_slot_bytes() + 8 * LT_SLOT_BYTES) : LT_NCH * 16 * LT_SLOT_BYTES;
+    return l == 0 ? LT_NCH * 2 * (lt_x0_slot_bytes() + LT_SPC * LT_SLOT_BYTES) : LT_NCH * 2 * 2 * LT_SPC * LT_SLOT_BYTES;
 }
 __host__ __device__ inline uint32_t lt_layer_off_bytes(int l) {       // from w_off
     return l == 0 ? 0u : lt_layer_bytes(0) + (uint32_t)(l - 1) * lt_layer_bytes(1);

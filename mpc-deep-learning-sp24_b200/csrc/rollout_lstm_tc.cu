@@ -55,15 +55,18 @@ __device__ __forceinline__ void lt_mma(uint32_t d_tmem, uint64_t a_desc, uint64_
 }
 __device__ __forceinline__ void lt_fence_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 
+__device__ __forceinline__ bool lt_try_wait_cluster(uint64_t* bar, uint32_t parity);
 #ifdef MPCDL_LT_DEBUG
 // development aid: p.dbg is HOST-mapped pinned memory; a wait that times out leaves (code, count) there before the trap
-#define LT_WAIT(bar, par, code, cnt) lt_wait_dbg(bar, par, p.dbg, code, cnt)
+#define LT_WAIT(bar, par, code, cnt) lt_wait_dbg<false>(bar, par, p.dbg, code, cnt)
+#define LT_WAITC(bar, par, code, cnt) lt_wait_dbg<false>(bar, par, p.dbg, code, cnt)
 #define LT_MARK(i, v) do { if (p.dbg) { ((volatile unsigned int*)p.dbg)[i] = (v); } } while (0)
+template <bool CL>
 __device__ __forceinline__ void lt_wait_dbg(uint64_t* bar, uint32_t parity, unsigned int* dbg, unsigned int code, unsigned int cnt) {
     uint32_t spins = 0;
-    while (!mbar_try_wait(bar, parity)) {
+    while (!(CL ? lt_try_wait_cluster(bar, parity) : mbar_try_wait(bar, parity))) {
         if (++spins > (1u << 20)) {
-            if (dbg && (threadIdx.x & 31) == 0) { volatile unsigned int* d = dbg; d[16 + 2 * code] = 0xDEAD0000u | blockIdx.x; d[17 + 2 * code] = cnt; __threadfence_system(); }
+            if (dbg && (threadIdx.x & 31) == 0) { volatile unsigned int* d = dbg; code += 8 * (blockIdx.x & 1); d[16 + 2 * code] = 0xDEAD0000u | blockIdx.x; d[17 + 2 * code] = cnt; __threadfence_system(); }
             __nanosleep(1000000);
             __trap();
         }
@@ -71,6 +74,13 @@ __device__ __forceinline__ void lt_wait_dbg(uint64_t* bar, uint32_t parity, unsi
 }
 #else
 #define LT_WAIT(bar, par, code, cnt) mbar_wait(bar, par)
+#define LT_WAITC(bar, par, code, cnt) mbar_wait(bar, par)      // cta-scope acquire: the data is read by the MMA (async proxy), not by this thread
+__device__ __forceinline__ void lt_wait_cluster(uint64_t* bar, uint32_t parity) {      // bounded spin like mbar_wait
+    uint32_t spins = 0;
+    while (!lt_try_wait_cluster(bar, parity)) {
+        if (++spins > (1u << 26)) __trap();
+    }
+}
 #define LT_MARK(i, v) do { } while (0)
 #endif
 
@@ -79,14 +89,71 @@ struct LtBars {
     uint32_t tmem_slot;
 };
 
+// ---- CTA-pair (cta_group::2) plumbing
+__device__ __forceinline__ uint32_t lt_cta_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void lt_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive (default semantics, as CUTLASS ClusterBarrier::arrive: a release.cluster arrive costs ~1200 cycles here) on the mbarrier at the same shared-memory offset in CTA `cta` of the cluster
+__device__ __forceinline__ void lt_remote_arrive(uint64_t* bar, uint32_t cta) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)), "r"(cta)
+        : "memory");
+}
+// wait with cluster-scope acquire (the leader's barriers also collect arrivals of the peer CTA)
+__device__ __forceinline__ bool lt_try_wait_cluster(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void lt_mma2(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// all MMAs issued so far by this thread arrive (once) on the mbarrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void lt_commit2(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)),
+                 "h"(static_cast<uint16_t>(3))
+                 : "memory");
+}
+__device__ __forceinline__ void lt_tmem_alloc2(uint32_t* smem_dst, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void lt_tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
 }  // namespace
 
-__global__ void __launch_bounds__(LT_THREADS, 1) rollout_lstm_tc_kernel(const __grid_constant__ LtRolloutParams p) {
+// One CTA PAIR (cluster of 2, cta_group::2) per two SMs: each CTA owns a tile of 128 trajectories (its A operands, its
+// 128 TMEM lanes, its epilogue) and streams HALF of every weight slot; the leader CTA issues M = 256 MMAs that read both
+// CTAs' shared memory, so every weight byte fetched from L2 feeds 256 trajectories.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(LT_THREADS, 1) rollout_lstm_tc_kernel(const __grid_constant__ LtRolloutParams p) {
     extern __shared__ __align__(1024) unsigned char smb[];
     const LtModel& m = p.m;
     const int T = m.window, NL = m.layers, H = p.io.H;
     const LtSmem L = lt_layout(T);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = lt_cta_rank();
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+    const int npt = (p.io.ntiles + 1) >> 1;                            // pair tiles (2 x 128 trajectories)
     LtBars* bars = reinterpret_cast<LtBars*>(smb + L.bars);
     unsigned char* const ax = smb + L.ax;
     unsigned char* const ah = smb + L.ah;
@@ -98,33 +165,36 @@ __global__ void __launch_bounds__(LT_THREADS, 1) rollout_lstm_tc_kernel(const __
     float* const ypart = reinterpret_cast<float*>(ax + 8192);          // head partials: [3][6][128], beside the layer-0 tile
 
     if (tid == 0) {
-        for (int i = 0; i < LT_NSLOTS; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 1); }
-        mbar_init(&bars->ax_full, 1);
-        mbar_init(&bars->ah_full, 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(&bars->d_full[i], 1); mbar_init(&bars->d_empty[i], LT_EPI_WARPS * 32); }
+        // the leader's barriers that gate MMA issue also take ONE relayed arrival of the peer CTA per phase
+        const uint32_t extra = rank == 0 ? 1u : 0u;
+        for (int i = 0; i < LT_NSLOTS; ++i) { mbar_init(&bars->full[i], 1 + extra); mbar_init(&bars->empty[i], 1); }
+        mbar_init(&bars->ax_full, 1 + extra);
+        mbar_init(&bars->ah_full, 1 + extra);
+        for (int i = 0; i < 2; ++i) { mbar_init(&bars->d_full[i], 1); mbar_init(&bars->d_empty[i], LT_EPI_WARPS * 32 + extra); }
         mbar_fence_init();
     }
-    if (warp == LT_EPI_WARPS + 1) { umma::tmem_alloc(&bars->tmem_slot, 512); umma::tmem_relinquish(); }
+    if (warp == LT_EPI_WARPS + 1) lt_tmem_alloc2(&bars->tmem_slot, 512);
     for (int i = tid; i < LT_HID * 8 + 8; i += blockDim.x) fcS[i] = m.blob[m.fc_off + i];
     for (int i = tid; i < 2 * T * 8 + 12; i += blockDim.x) normS[i] = p.io.norm[i];
     umma::fence_before_sync();
     __syncthreads();
+    lt_cluster_sync();                       // both CTAs' barriers and TMEM exist before any cross-CTA arrive / MMA
     umma::fence_after_sync();
     const uint32_t tbase = bars->tmem_slot;
-    const int my_tiles = (p.io.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int my_tiles = (npt - pair + npairs - 1) / npairs;
     const unsigned char* const wbase = reinterpret_cast<const unsigned char*>(m.blob + m.w_off);
 
     if (warp >= LT_EPI_WARPS) {
       asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
       if (warp == LT_EPI_WARPS) {
-        // ================================================================ weight producer: one thread feeds the ring
+        // ================================================================ weight producer: one thread feeds this CTA's half of the ring
         if (lane == 0) {
             uint32_t cnt = 0;
-            auto produce = [&](const unsigned char* src, uint32_t bytes) {
+            auto produce = [&](const unsigned char* src, uint32_t bytes) {      // src = slot base in the blob ([rank][...])
                 const uint32_t slot = cnt % LT_NSLOTS;
                 if (cnt >= LT_NSLOTS) LT_WAIT(&bars->empty[slot], ((cnt / LT_NSLOTS) - 1u) & 1u, 0, cnt);
                 mbar_expect_tx(&bars->full[slot], bytes);
-                bulk_g2s(ring + slot * LT_SLOT_BYTES, src, bytes, &bars->full[slot]);
+                bulk_g2s(ring + slot * LT_SLOT_BYTES, src + rank * bytes, bytes, &bars->full[slot]);
                 ++cnt;
                 if (blockIdx.x == 0) LT_MARK(2, cnt);
             };
@@ -134,29 +204,48 @@ __global__ void __launch_bounds__(LT_THREADS, 1) rollout_lstm_tc_kernel(const __
                         for (int f = 0; f < T; ++f)
                             for (int c = 0; c < LT_NCH; ++c) {
                                 const unsigned char* src = wbase + lt_layer_off_bytes(l) + (uint32_t)c * lt_chunk_bytes(l);
-                                if (l == 0) { produce(src, lt_x0_slot_bytes()); src += lt_x0_slot_bytes(); }
-                                else { for (int s = 0; s < 8; ++s) produce(src + s * LT_SLOT_BYTES, LT_SLOT_BYTES); src += 8 * LT_SLOT_BYTES; }
-                                if (f > 0) for (int s = 0; s < 8; ++s) produce(src + s * LT_SLOT_BYTES, LT_SLOT_BYTES);
+                                if (l == 0) { produce(src, lt_x0_slot_bytes()); src += 2 * lt_x0_slot_bytes(); }
+                                else { for (int s = 0; s < LT_SPC; ++s) produce(src + s * 2 * LT_SLOT_BYTES, LT_SLOT_BYTES); src += LT_SPC * 2 * LT_SLOT_BYTES; }
+                                if (f > 0) for (int s = 0; s < LT_SPC; ++s) produce(src + s * 2 * LT_SLOT_BYTES, LT_SLOT_BYTES);
                             }
         }
       } else if (warp == LT_EPI_WARPS + 1) {
-        // ================================================================ MMA issuer (warp converged, one elected lane issues)
-        constexpr uint32_t IDESC = lt_idesc(128, 256);
+        // ================================================================ MMA warp.  Both CTAs walk the same sequence of
+        // sync points; the peer (rank 1) only RELAYS each of its local events to the leader's barrier, the leader
+        // (rank 0) waits for both and issues the M = 256 MMAs (one elected lane) and the multicast commits.
+        constexpr uint32_t IDESC = lt_idesc(256, 256);
         const uint32_t ax_u = smem_u32(ax), ah_u = smem_u32(ah), ring_u = smem_u32(ring);
         uint32_t cnt = 0, dq = 0, axp = 0, ahp = 0;
+#ifdef MPCDL_LT_DEBUG
+        long long wcyc[6] = {0, 0, 0, 0, 0, 0};
+        const long long tstart = clock64();
+#endif
+        auto await = [&](uint64_t* bar, uint32_t parity, unsigned code, unsigned n) {
+#ifdef MPCDL_LT_DEBUG
+            const long long t0 = clock64();
+            LT_WAITC(bar, parity, code, n);
+            wcyc[code] += clock64() - t0;
+#else
+            LT_WAITC(bar, parity, code, n);
+#endif
+            if (rank != 0) {
+                if (lane == 0) lt_remote_arrive(bar, 0);
+                __syncwarp();
+            }
+        };
         // one ring slot = `nk` K=16 MMAs of A k-chunks [kc0, kc0 + 2 nk) against the slot
         auto slot_mmas = [&](uint32_t a_u, uint32_t kc0, int nk, uint32_t dcol, uint32_t& acc) {
             const uint32_t slot = cnt % LT_NSLOTS;
-            LT_WAIT(&bars->full[slot], (cnt / LT_NSLOTS) & 1u, 1, cnt);
+            await(&bars->full[slot], (cnt / LT_NSLOTS) & 1u, 1, cnt);
             umma::fence_after_sync();
-            if (lt_elect()) {
+            if (rank == 0 && lt_elect()) {
                 for (int kk = 0; kk < nk; ++kk) {
                     const uint64_t ad = umma::smem_desc_kmajor(a_u + (kc0 + 2u * kk) * LT_A_LBO, LT_A_LBO, 128u);
                     const uint64_t bd = umma::smem_desc_kmajor(ring_u + slot * LT_SLOT_BYTES + 2u * kk * LT_B_LBO, LT_B_LBO, 128u);
-                    lt_mma(dcol, ad, bd, IDESC, acc);
+                    lt_mma2(dcol, ad, bd, IDESC, acc);
                     acc = 1u;
                 }
-                umma::mma_commit(&bars->empty[slot]);
+                lt_commit2(&bars->empty[slot]);
             }
             __syncwarp();
             ++cnt;
@@ -167,22 +256,28 @@ __global__ void __launch_bounds__(LT_THREADS, 1) rollout_lstm_tc_kernel(const __
                     for (int f = 0; f < T; ++f)
                         for (int c = 0; c < LT_NCH; ++c) {
                             const uint32_t buf = dq & 1u;
-                            if (dq >= 2u) LT_WAIT(&bars->d_empty[buf], ((dq >> 1) - 1u) & 1u, 2, dq);
+                            if (dq >= 2u) await(&bars->d_empty[buf], ((dq >> 1) - 1u) & 1u, 2, dq);
                             ++dq;
                             umma::fence_after_sync();
                             const uint32_t dcol = tbase + buf * 256u;
                             uint32_t acc = 0u;
-                            if (c == 0) { LT_WAIT(&bars->ax_full, axp, 3, dq); axp ^= 1u; umma::fence_after_sync(); }
+                            if (c == 0) { await(&bars->ax_full, axp, 3, dq); axp ^= 1u; umma::fence_after_sync(); }
                             if (l == 0) slot_mmas(ax_u, 0u, 1, dcol, acc);
-                            else for (uint32_t s = 0; s < 8u; ++s) slot_mmas(ax_u, 4u * s, 2, dcol, acc);
+                            else for (uint32_t s = 0; s < (uint32_t)LT_SPC; ++s) slot_mmas(ax_u, 8u * s, 4, dcol, acc);
                             if (f > 0) {
-                                if (c == 0) { LT_WAIT(&bars->ah_full, ahp, 4, dq); ahp ^= 1u; umma::fence_after_sync(); }
-                                for (uint32_t s = 0; s < 8u; ++s) slot_mmas(ah_u, 4u * s, 2, dcol, acc);
+                                if (c == 0) { await(&bars->ah_full, ahp, 4, dq); ahp ^= 1u; umma::fence_after_sync(); }
+                                for (uint32_t s = 0; s < (uint32_t)LT_SPC; ++s) slot_mmas(ah_u, 8u * s, 4, dcol, acc);
                             }
-                            if (lt_elect()) umma::mma_commit(&bars->d_full[buf]);
+                            if (rank == 0 && lt_elect()) lt_commit2(&bars->d_full[buf]);
                             __syncwarp();
                             if (blockIdx.x == 0 && lane == 0) LT_MARK(1, dq);
                         }
+#ifdef MPCDL_LT_DEBUG
+        if (blockIdx.x < 2 && lane == 0 && p.dbg) {     // cycles the MMA warp of CTA 0 / 1 spent in each kind of wait
+            for (int i = 0; i < 6; ++i) p.dbg[48 + 8 * blockIdx.x + i] = (unsigned int)(wcyc[i] >> 10);
+            p.dbg[48 + 8 * blockIdx.x + 6] = (unsigned int)((clock64() - tstart) >> 10);
+        }
+#endif
       }
     } else {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
@@ -191,14 +286,15 @@ __global__ void __launch_bounds__(LT_THREADS, 1) rollout_lstm_tc_kernel(const __
     // ------------------------------------------------------------------ teardown
     umma::fence_before_sync();
     __syncthreads();
-    if (warp == LT_EPI_WARPS + 1) umma::tmem_dealloc(tbase, 512);
+    lt_cluster_sync();                       // the peer may still read this CTA's shared memory / signal its barriers until here
+    if (warp == LT_EPI_WARPS + 1) lt_tmem_dealloc2(tbase, 512);
 }
 
 cudaError_t launch_lstm_tc(const LtRolloutParams& p, int grid, int smem_bytes, cudaStream_t st) {
     auto k = rollout_lstm_tc_kernel;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     if (e != cudaSuccess) return e;
-    k<<<grid, LT_THREADS, smem_bytes, st>>>(p);
+    k<<<grid, LT_THREADS, smem_bytes, st>>>(p);      // grid is even: __cluster_dims__(2, 1, 1)
     return cudaGetLastError();
 }
 

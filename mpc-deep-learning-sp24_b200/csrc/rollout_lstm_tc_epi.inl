@@ -10,7 +10,8 @@
         constexpr int NEPI = LT_EPI_WARPS * 32;
         uint32_t dq = 0;
 
-        for (int tile = blockIdx.x; tile < p.io.ntiles; tile += gridDim.x) {
+        for (int pt = pair; pt < npt; pt += npairs) {
+            const int tile = 2 * pt + (int)rank;               // an odd tile count leaves the last pair's rank 1 a dummy tile
             long long n = (long long)tile * LT_TN + row;
             const bool valid = n < p.io.N;
             if (n >= p.io.N) n = p.io.N - 1;

@@ -119,10 +119,11 @@ def test_tensor_core_plans_and_errors():
     d = _lib.ModelDesc(_lib.GRU, 32, 2, 4)
     assert _lib.lib.mpcdl_blob_floats_tc(C.byref(d)) == 0
     # BF16 tcgen05 kernel of the hidden-256 LSTM (rollout_lstm_tc.cu): 128-trajectory tiles, 16 epilogue warps + one
-    # control warpgroup, a per-CTA scratch of 2 x window operand tiles; everything else refuses the precision
+    # control warpgroup, CTA pairs (even grid), a per-CTA scratch of 2 x window operand tiles; everything else refuses the precision
     p = ops.plan(2, 256, 4, 4, 65536, 100, precision="bf16")
     assert p["variant"] == 6 and p["tile_traj"] == 128 and p["threads"] == 640 and p["grid"] == 148 and p["ntiles"] == 512
     assert p["smem_bytes"] <= 232448
+    assert ops.plan(2, 256, 4, 4, 129, 5, precision="bf16")["grid"] == 2 and ops.plan(2, 256, 4, 4, 3 * 128, 5, precision="bf16")["grid"] == 4
     a = _lib.RolloutArgs()
     a.model, a.precision, a.N, a.H = _lib.ModelDesc(2, 256, 4, 4), 3, 1000, 5
     assert _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a)) == 8 * 2 * 4 * 128 * 256 * 2

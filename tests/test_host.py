@@ -270,9 +270,10 @@ def test_pack_mlp_tensor_core_layout():
 
 def test_pack_lstm256_bf16_layout():
     """mpcdl_pack_rnn_tc for the hidden-256 LSTM (rollout_lstm_tc.cu, BASELINE config 4) against a numpy restatement:
-    BF16 round-to-nearest-even, per layer / 64-unit chunk the x slots then the h slots, every slot the canonical
-    K-major UMMA block [k/8][n/8][8 rows][8 k] with row n = gate n/64, unit 64*chunk + n%64; layer 0 holds [W | W]
-    (K = 16) against the [x_hi | x_lo] operand."""
+    BF16 round-to-nearest-even, per layer / 64-unit chunk the x slots then the h slots (64 k each), every slot
+    [CTA rank][k/8][n/8][8 rows][8 k] -- each CTA of the pair streams the canonical K-major UMMA block of ITS 128 of the
+    chunk's 256 gate rows -- with row n = gate n/64, unit 64*chunk + n%64; layer 0 holds [W | W] (K = 16) against the
+    [x_hi | x_lo] operand."""
     import numpy as np
     import torch
     from mpcdl import _lib, pack
@@ -301,7 +302,8 @@ def test_pack_lstm256_bf16_layout():
     def slot(W, c, ks):                      # -> the [256 rows][len(ks)] block of chunk c in slot order
         rows = np.array([(n // 64) * h + c * 64 + n % 64 for n in range(256)])
         blk = bf16(W[rows][:, ks])                                                                  # [n][kk]
-        return blk.reshape(32, 8, len(ks) // 8, 8).transpose(2, 0, 1, 3).reshape(-1)               # [kk/8][n/8][n%8][kk%8]
+        return np.concatenate([blk[128 * r:128 * r + 128].reshape(16, 8, len(ks) // 8, 8).transpose(2, 0, 1, 3).reshape(-1)
+                               for r in range(2)])                                                  # [rank][kk/8][n/8][n%8][kk%8]
 
     for l in range(L):
         wi, wh = sd[f"lstm.weight_ih_l{l}"].numpy(), sd[f"lstm.weight_hh_l{l}"].numpy()
@@ -311,12 +313,12 @@ def test_pack_lstm256_bf16_layout():
                 assert np.array_equal(w16[p:p + want.size], want), (l, c, "x0")
                 p += want.size
             else:
-                for s in range(8):
-                    want = slot(wi, c, np.arange(32 * s, 32 * s + 32))
+                for s in range(4):
+                    want = slot(wi, c, np.arange(64 * s, 64 * s + 64))
                     assert np.array_equal(w16[p:p + want.size], want), (l, c, "x", s)
                     p += want.size
-            for s in range(8):
-                want = slot(wh, c, np.arange(32 * s, 32 * s + 32))
+            for s in range(4):
+                want = slot(wh, c, np.arange(64 * s, 64 * s + 64))
                 assert np.array_equal(w16[p:p + want.size], want), (l, c, "h", s)
                 p += want.size
     assert p == w16.size

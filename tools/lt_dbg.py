@@ -17,9 +17,13 @@ NAMES = ["producer:empty", "mma:full", "mma:d_empty", "mma:ax_full", "mma:ah_ful
 def report():
     d = dbg.numpy().view("uint32")
     print(f"progress: epilogue chunks {d[0]}  mma chunks {d[1]}  slots produced {d[2]}")
-    for i, n in enumerate(NAMES):
-        if d[16 + 2 * i]:
-            print(f"  TIMEOUT {n}: cta {d[16 + 2 * i] & 0xFFFF} count {d[17 + 2 * i]}")
+    for r in range(2):
+        w = d[48 + 8 * r:48 + 8 * r + 7]
+        print(f"  MMA warp of CTA {r}: kcycles waiting full {w[1]} d_empty {w[2]} ax_full {w[3]} ah_full {w[4]} | total {w[6]}")
+    for r in range(2):
+        for i, n in enumerate(NAMES):
+            if d[16 + 2 * (i + 8 * r)]:
+                print(f"  TIMEOUT rank {r} {n}: cta {d[16 + 2 * (i + 8 * r)] & 0xFFFF} count {d[17 + 2 * (i + 8 * r)]}")
 init, U = synth.make_inputs(synth.load_rows(), N, H, window=W, seed=3)
 try:
     y = m.rollout(init.to(dev), U.to(dev), ST, precision="bf16")[0]
