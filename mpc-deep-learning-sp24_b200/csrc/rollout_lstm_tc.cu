@@ -85,7 +85,7 @@ __device__ __forceinline__ void lt_wait_cluster(uint64_t* bar, uint32_t parity) 
 #endif
 
 struct LtBars {
-    uint64_t full[LT_NSLOTS], empty[LT_NSLOTS], ax_full, ah_full, d_full[2], d_empty[2];
+    uint64_t full[LT_NSLOTS], empty[LT_NSLOTS], ax_full, ah_full[2], d_full[2], d_empty[2];   // ah_full: units 0..191 | 192..255
     uint32_t tmem_slot;
 };
 
@@ -169,7 +169,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(LT_THREADS, 1) rollo
         const uint32_t extra = rank == 0 ? 1u : 0u;
         for (int i = 0; i < LT_NSLOTS; ++i) { mbar_init(&bars->full[i], 1 + extra); mbar_init(&bars->empty[i], 1); }
         mbar_init(&bars->ax_full, 1 + extra);
-        mbar_init(&bars->ah_full, 1 + extra);
+        mbar_init(&bars->ah_full[0], 1 + extra);
+        mbar_init(&bars->ah_full[1], 1 + extra);
         for (int i = 0; i < 2; ++i) { mbar_init(&bars->d_full[i], 1); mbar_init(&bars->d_empty[i], LT_EPI_WARPS * 32 + extra); }
         mbar_fence_init();
     }
@@ -265,8 +266,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(LT_THREADS, 1) rollo
                             if (l == 0) slot_mmas(ax_u, 0u, 1, dcol, acc);
                             else for (uint32_t s = 0; s < (uint32_t)LT_SPC; ++s) slot_mmas(ax_u, 8u * s, 4, dcol, acc);
                             if (f > 0) {
-                                if (c == 0) { await(&bars->ah_full, ahp, 4, dq); ahp ^= 1u; umma::fence_after_sync(); }
-                                for (uint32_t s = 0; s < (uint32_t)LT_SPC; ++s) slot_mmas(ah_u, 8u * s, 4, dcol, acc);
+                                for (uint32_t s = 0; s < (uint32_t)LT_SPC; ++s) {
+                                    // h_{f-1} arrives in two pieces: units 0..191 while the previous cell's last chunk is still in
+                                    // its epilogue, units 192..255 (that chunk's output) right after it
+                                    if (c == 0 && s == 0) { await(&bars->ah_full[0], ahp, 4, dq); umma::fence_after_sync(); }
+                                    if (c == 0 && s == LT_SPC - 1) { await(&bars->ah_full[1], ahp, 4, dq); ahp ^= 1u; umma::fence_after_sync(); }
+                                    slot_mmas(ah_u, 8u * s, 4, dcol, acc);
+                                }
                             }
                             if (rank == 0 && lt_elect()) lt_commit2(&bars->d_full[buf]);
                             __syncwarp();

@@ -21,6 +21,25 @@
                 const float* w = p.io.init + n * p.io.init_mul * T * 8;
                 for (int i = 0; i < T * 8; ++i) xwin[i * LT_TN + row] = __ldg(w + i);
             }
+            // layer-0 operand tile of frame f: z-scored [hi(8) | lo(8)] bf16, written by the owner threads (A_x must be free)
+            auto stage_l0 = [&](int f) {
+                if (owner) {
+                    int pf = base + f; if (pf >= T) pf -= T;
+                    float xn[8], lo[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        xn[k] = __fdiv_rn(__fsub_rn(xwin[(pf * 8 + k) * LT_TN + row], normS[f * 8 + k]), normS[T * 8 + f * 8 + k]);
+                        lo[k] = xn[k] - lt_bf16_round(xn[k]);
+                    }
+                    *reinterpret_cast<uint4*>(ax + rowoff) =
+                        make_uint4(lt_pack(xn[0], xn[1]), lt_pack(xn[2], xn[3]), lt_pack(xn[4], xn[5]), lt_pack(xn[6], xn[7]));
+                    *reinterpret_cast<uint4*>(ax + LT_A_LBO + rowoff) =
+                        make_uint4(lt_pack(lo[0], lo[1]), lt_pack(lo[2], lo[3]), lt_pack(lo[4], lo[5]), lt_pack(lo[6], lo[7]));
+                    umma::fence_proxy_async_smem();
+                    named_bar_sync(2, LT_TN);
+                    if (tid == 0) mbar_arrive(&bars->ax_full);
+                }
+            };
             for (int t = 0; t < H; ++t) {
                 float u[2] = {0.f, 0.f};
                 if (owner) { const float2 uu = load_control(p.io, n, t); u[0] = uu.x; u[1] = uu.y; }
@@ -33,24 +52,9 @@
 #pragma unroll
                     for (int i = 0; i < LT_NCH * 16; ++i) cst[i] = 0.f;        // stateless: (h, c) = 0 at every call (deep_models.py:82-83)
                     for (int f = 0; f < T; ++f) {
-                        if (l == 0) {
-                            if (owner) {     // layer-0 operand tile: z-scored frame f as [hi(8) | lo(8)] bf16
-                                int pf = base + f; if (pf >= T) pf -= T;
-                                float xn[8], lo[8];
-#pragma unroll
-                                for (int k = 0; k < 8; ++k) {
-                                    xn[k] = __fdiv_rn(__fsub_rn(xwin[(pf * 8 + k) * LT_TN + row], normS[f * 8 + k]), normS[T * 8 + f * 8 + k]);
-                                    lo[k] = xn[k] - lt_bf16_round(xn[k]);
-                                }
-                                *reinterpret_cast<uint4*>(ax + rowoff) =
-                                    make_uint4(lt_pack(xn[0], xn[1]), lt_pack(xn[2], xn[3]), lt_pack(xn[4], xn[5]), lt_pack(xn[6], xn[7]));
-                                *reinterpret_cast<uint4*>(ax + LT_A_LBO + rowoff) =
-                                    make_uint4(lt_pack(lo[0], lo[1]), lt_pack(lo[2], lo[3]), lt_pack(lo[4], lo[5]), lt_pack(lo[6], lo[7]));
-                                umma::fence_proxy_async_smem();
-                                named_bar_sync(2, LT_TN);
-                                if (tid == 0) mbar_arrive(&bars->ax_full);
-                            }
-                        }
+                        if (l == 0 && f == 0) stage_l0(0);
+                        int l2 = l, f2 = f + 1;                                  // the next cell
+                        if (f2 == T) { l2 = l + 1; f2 = 0; }
                         const bool last = l == NL - 1 && f == T - 1;
                         unsigned char* const hout = scratch + (size_t)((l & 1) * T + f) * LT_A_BYTES;
 #pragma unroll
@@ -58,6 +62,22 @@
                             const uint32_t buf = dq & 1u;
                             LT_WAIT(&bars->d_full[buf], (dq >> 1) & 1u, 5, dq);
                             ++dq;
+                            if (c == LT_NCH - 1 && l2 < NL) {
+                                // every MMA of this cell is complete: A_x / A_h are free.  Stage what the next cell needs and
+                                // what already exists, so its x part and three quarters of its h part run under this epilogue
+                                if (l2 == 0) stage_l0(f2);
+                                else if (T > 1 && tid == 0) {
+                                    const unsigned char* src = scratch + (size_t)(((l2 - 1) & 1) * T + f2) * LT_A_BYTES;
+                                    mbar_expect_tx(&bars->ax_full, LT_A_BYTES);
+                                    bulk_g2s(ax, src, LT_A_BYTES / 2, &bars->ax_full);
+                                    bulk_g2s(ax + LT_A_BYTES / 2, src + LT_A_BYTES / 2, LT_A_BYTES / 2, &bars->ax_full);
+                                }
+                                if (f2 > 0 && tid == 0) {        // units 0..191 of h_f (chunks 0..2: fenced + barrier below)
+                                    mbar_expect_tx(&bars->ah_full[0], 3 * LT_A_BYTES / 4);
+                                    bulk_g2s(ah, hout, LT_A_BYTES / 2, &bars->ah_full[0]);
+                                    bulk_g2s(ah + LT_A_BYTES / 2, hout + LT_A_BYTES / 2, LT_A_BYTES / 4, &bars->ah_full[0]);
+                                }
+                            }
                             if (blockIdx.x == 0 && tid == 0) LT_MARK(0, dq);
                             umma::fence_after_sync();
 #pragma unroll
@@ -93,27 +113,26 @@
                             }
                             umma::fence_before_sync();
                             mbar_arrive(&bars->d_empty[buf]);
+                            if (c == LT_NCH - 2 && f2 > 0 && l2 < NL) {      // chunks 0..2 of h_f are in the scratch for the early A_h load
+                                __threadfence();
+                                lt_fence_async_global();
+                                named_bar_sync(1, NEPI);
+                            }
                         }
-                        // ---- end of the cell: h_f is in the scratch; the next cell's operand tiles are re-loaded by TMA
+                        // ---- end of the cell: all of h_f is in the scratch; the rest of the next cell's operands follows by TMA
                         __threadfence();
                         lt_fence_async_global();
                         named_bar_sync(1, NEPI);
-                        if (tid == 0) {
-                            int l2 = l, f2 = f + 1;
-                            if (f2 == T) { l2 = l + 1; f2 = 0; }
-                            if (l2 < NL) {
-                                if (l2 > 0) {
-                                    const unsigned char* src = scratch + (size_t)(((l2 - 1) & 1) * T + f2) * LT_A_BYTES;
-                                    mbar_expect_tx(&bars->ax_full, LT_A_BYTES);
-                                    bulk_g2s(ax, src, LT_A_BYTES / 2, &bars->ax_full);
-                                    bulk_g2s(ax + LT_A_BYTES / 2, src + LT_A_BYTES / 2, LT_A_BYTES / 2, &bars->ax_full);
-                                }
-                                if (f2 > 0) {
-                                    const unsigned char* src = scratch + (size_t)((l2 & 1) * T + (f2 - 1)) * LT_A_BYTES;
-                                    mbar_expect_tx(&bars->ah_full, LT_A_BYTES);
-                                    bulk_g2s(ah, src, LT_A_BYTES / 2, &bars->ah_full);
-                                    bulk_g2s(ah + LT_A_BYTES / 2, src + LT_A_BYTES / 2, LT_A_BYTES / 2, &bars->ah_full);
-                                }
+                        if (tid == 0 && l2 < NL) {
+                            if (l2 > 0 && T == 1) {              // window 1: the next layer's input IS this cell's output
+                                const unsigned char* src = scratch + (size_t)(((l2 - 1) & 1) * T + f2) * LT_A_BYTES;
+                                mbar_expect_tx(&bars->ax_full, LT_A_BYTES);
+                                bulk_g2s(ax, src, LT_A_BYTES / 2, &bars->ax_full);
+                                bulk_g2s(ax + LT_A_BYTES / 2, src + LT_A_BYTES / 2, LT_A_BYTES / 2, &bars->ax_full);
+                            }
+                            if (f2 > 0) {                        // units 192..255 of h_f
+                                mbar_expect_tx(&bars->ah_full[1], LT_A_BYTES / 4);
+                                bulk_g2s(ah + 3 * (LT_A_BYTES / 4), hout + 3 * (LT_A_BYTES / 4), LT_A_BYTES / 4, &bars->ah_full[1]);
                             }
                         }
                     }
