@@ -48,9 +48,10 @@ struct LtRolloutParams {
     NoiseParams nz;             // always disabled (owner_finish reads nz.enabled)
     IoParams io;
     unsigned int* dbg;          // development aid (MPCDL_LT_DEBUG builds): host-mapped words, else unused
-    unsigned char* scratch;     // per CTA: [2 layer parities][T frames] A tiles of 64 KB (the layer output sequences)
+    unsigned char* scratch;     // per CTA: [T frames] A tiles of 64 KB: the current layer's output sequence, written IN PLACE
+                                // over the previous layer's (cell (l, f) overwrites slot f after loading it as its x operand)
 };
-__host__ __device__ inline size_t lt_scratch_bytes_per_cta(int window) { return (size_t)2 * window * LT_A_BYTES; }
+__host__ __device__ inline size_t lt_scratch_bytes_per_cta(int window) { return (size_t)window * LT_A_BYTES; }
 
 struct LtSmem {        // byte offsets
     int ax, ah, ring, xwin, bias, fc, norm, bars, total;

@@ -56,7 +56,7 @@
                         int l2 = l, f2 = f + 1;                                  // the next cell
                         if (f2 == T) { l2 = l + 1; f2 = 0; }
                         const bool last = l == NL - 1 && f == T - 1;
-                        unsigned char* const hout = scratch + (size_t)((l & 1) * T + f) * LT_A_BYTES;
+                        unsigned char* const hout = scratch + (size_t)f * LT_A_BYTES;       // in place: slot f held layer l-1's frame f (this cell's x, already in A_x)
 #pragma unroll
                         for (int c = 0; c < LT_NCH; ++c) {
                             const uint32_t buf = dq & 1u;
@@ -67,7 +67,7 @@
                                 // what already exists, so its x part and three quarters of its h part run under this epilogue
                                 if (l2 == 0) stage_l0(f2);
                                 else if (T > 1 && tid == 0) {
-                                    const unsigned char* src = scratch + (size_t)(((l2 - 1) & 1) * T + f2) * LT_A_BYTES;
+                                    const unsigned char* src = scratch + (size_t)f2 * LT_A_BYTES;
                                     mbar_expect_tx(&bars->ax_full, LT_A_BYTES);
                                     bulk_g2s(ax, src, LT_A_BYTES / 2, &bars->ax_full);
                                     bulk_g2s(ax + LT_A_BYTES / 2, src + LT_A_BYTES / 2, LT_A_BYTES / 2, &bars->ax_full);
@@ -125,7 +125,7 @@
                         named_bar_sync(1, NEPI);
                         if (tid == 0 && l2 < NL) {
                             if (l2 > 0 && T == 1) {              // window 1: the next layer's input IS this cell's output
-                                const unsigned char* src = scratch + (size_t)(((l2 - 1) & 1) * T + f2) * LT_A_BYTES;
+                                const unsigned char* src = scratch + (size_t)f2 * LT_A_BYTES;
                                 mbar_expect_tx(&bars->ax_full, LT_A_BYTES);
                                 bulk_g2s(ax, src, LT_A_BYTES / 2, &bars->ax_full);
                                 bulk_g2s(ax + LT_A_BYTES / 2, src + LT_A_BYTES / 2, LT_A_BYTES / 2, &bars->ax_full);
