@@ -29,7 +29,7 @@ enum { MPCDL_MLP = 0, MPCDL_GRU = 1, MPCDL_LSTM = 2 };
  * modes run the [128 x 64].[64 x 64|192|256] layer / gate contractions on tcgen05 (hidden 64; GRU/LSTM window 4):
  * TF32X3 = three TF32 passes on hi/lo split operands (FP32-class accuracy, bound stated in DESIGN.md 5),
  * TF32 = one TF32 pass + MUFU.TANH activations.  State, accumulation, statistics and cost stay FP32.
- * BF16 = the wide LSTM (hidden 256, window <= 4, stateless, no noise net): gate GEMMs [128 x 256].[256 x 1024] on
+ * BF16 = the wide LSTM (hidden 256, stateless, no noise net): gate GEMMs [128 x 256].[256 x 1024] on
  * tcgen05 with BF16 operands, FP32 accumulation, FP32 cell state; needs a device scratch (mpcdl_rollout_scratch_bytes). */
 enum { MPCDL_PREC_FP32 = 0, MPCDL_PREC_TF32X3 = 1, MPCDL_PREC_TF32 = 2, MPCDL_PREC_BF16 = 3 };
 enum { MPCDL_ACT_IDENTITY = 0, MPCDL_ACT_RELU = 1, MPCDL_ACT_TANH = 2, MPCDL_ACT_SIGMOID = 3 };

@@ -350,7 +350,7 @@ int check_args(const mpcdl_rollout_args* a) {
     if (a->model.kind != MPCDL_MLP && a->stateful && !a->carry) return fail(MPCDL_ERR_ARG, "stateful rollout needs a carry buffer");
     if (a->precision == MPCDL_PREC_BF16) {
         if (!lt_supported(a->model))
-            return fail(MPCDL_ERR_UNSUPPORTED, "MPCDL_PREC_BF16 is the LSTM hidden=%d kernel (window <= 4); got kind=%d hidden=%d window=%d",
+            return fail(MPCDL_ERR_UNSUPPORTED, "MPCDL_PREC_BF16 is the LSTM hidden=%d kernel; got kind=%d hidden=%d window=%d",
                         LT_HID, a->model.kind, a->model.hidden, a->model.window);
         if (a->stateful || a->noise_wblob) return fail(MPCDL_ERR_UNSUPPORTED, "MPCDL_PREC_BF16: stateless models without the residual-noise net only; use MPCDL_PREC_FP32");
         if (!a->wblob_tc) return fail(MPCDL_ERR_ARG, "MPCDL_PREC_BF16 needs wblob_tc (mpcdl_pack_rnn_tc)");

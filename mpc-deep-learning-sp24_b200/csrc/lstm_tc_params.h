@@ -13,7 +13,7 @@ constexpr int LT_NCH = LT_HID / LT_CH; // 4 chunks per cell
 constexpr int LT_KS = 64;              // K rows per weight slot: per CTA [128 gate rows][64 k] bf16 = 16 KB = four K=16 MMAs
 constexpr int LT_SPC = LT_HID / LT_KS; // slots per 256-deep operand (4)
 constexpr int LT_SLOT_BYTES = 128 * LT_KS * 2;        // per CTA of the pair (its half of the 256 gate rows)
-constexpr int LT_NSLOTS = 4;
+constexpr int LT_NSLOTS = 5;           // 80 KB ring: the weight stream is latency-bound (L2 -> SM ~ 1.9 k cycles under load)
 constexpr int LT_EPI_WARPS = 16;       // lane quarter = warp % 4, unit group (16 of a chunk's 64) = warp / 4
 constexpr int LT_THREADS = (LT_EPI_WARPS + 4) * 32;   // + one control warpgroup: weight producer warp, MMA issuer warp, two idle
                                                       // (setmaxnreg moves registers between whole warpgroups)
@@ -51,10 +51,12 @@ struct LtRolloutParams {
     unsigned char* scratch;     // per CTA: [T frames] A tiles of 64 KB: the current layer's output sequence, written IN PLACE
                                 // over the previous layer's (cell (l, f) overwrites slot f after loading it as its x operand)
 };
-__host__ __device__ inline size_t lt_scratch_bytes_per_cta(int window) { return (size_t)window * LT_A_BYTES; }
+__host__ __device__ inline size_t lt_scratch_bytes_per_cta(int window) {      // + the raw window frames [T][8][128] FP32 (row-private)
+    return (size_t)window * LT_A_BYTES + (size_t)window * 8 * LT_TN * 4;
+}
 
 struct LtSmem {        // byte offsets
-    int ax, ah, ring, xwin, bias, fc, norm, bars, total;
+    int ax, ah, ring, bias, norm, bars, total;
 };
 __host__ __device__ inline LtSmem lt_layout(int window) {
     LtSmem L;
@@ -62,9 +64,7 @@ __host__ __device__ inline LtSmem lt_layout(int window) {
     L.ax = o;    o += LT_A_BYTES;                       // also: layer-0 tile [0, 4 KB), head partials [8 KB, 17 KB)
     L.ah = o;    o += LT_A_BYTES;
     L.ring = o;  o += LT_NSLOTS * LT_SLOT_BYTES;
-    L.xwin = o;  o += window * 8 * LT_TN * 4;           // raw frames [T][8][128] FP32
     L.bias = o;  o += 1024 * 4;                         // current layer
-    L.fc = o;    o += (LT_HID * 8 + 8) * 4;
     L.norm = o;  o += ((2 * window * 8 + 12 + 3) / 4 * 4) * 4;
     L.bars = o;  o += 256;
     L.total = o;

@@ -158,9 +158,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(LT_THREADS, 1) rollo
     unsigned char* const ax = smb + L.ax;
     unsigned char* const ah = smb + L.ah;
     unsigned char* const ring = smb + L.ring;
-    float* const xwin = reinterpret_cast<float*>(smb + L.xwin);
+    // raw window frames [T][8][128] FP32: row-private (only the owner thread of a trajectory touches its column), kept in
+    // the per-CTA scratch (L1/L2) so that shared memory holds a fifth ring slot
+    float* const xwin = reinterpret_cast<float*>(p.scratch + (size_t)blockIdx.x * lt_scratch_bytes_per_cta(T) + (size_t)T * LT_A_BYTES);
     float* const biasS = reinterpret_cast<float*>(smb + L.bias);
-    float* const fcS = reinterpret_cast<float*>(smb + L.fc);
+    const float* const fcG = m.blob + m.fc_off;                         // full_c head [256][8] + bias[8]: read through L1 (once per step)
     float* const normS = reinterpret_cast<float*>(smb + L.norm);
     float* const ypart = reinterpret_cast<float*>(ax + 8192);          // head partials: [3][6][128], beside the layer-0 tile
 
@@ -175,7 +177,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(LT_THREADS, 1) rollo
         mbar_fence_init();
     }
     if (warp == LT_EPI_WARPS + 1) lt_tmem_alloc2(&bars->tmem_slot, 512);
-    for (int i = tid; i < LT_HID * 8 + 8; i += blockDim.x) fcS[i] = m.blob[m.fc_off + i];
     for (int i = tid; i < 2 * T * 8 + 12; i += blockDim.x) normS[i] = p.io.norm[i];
     umma::fence_before_sync();
     __syncthreads();

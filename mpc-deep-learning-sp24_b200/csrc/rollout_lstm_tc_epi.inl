@@ -101,11 +101,11 @@
                                 *reinterpret_cast<uint4*>(hout + (size_t)(c * 8 + g * 2 + half) * LT_A_LBO + rowoff) =
                                     make_uint4(lt_pack(hv[0], hv[1]), lt_pack(hv[2], hv[3]), lt_pack(hv[4], hv[5]), lt_pack(hv[6], hv[7]));
                                 if (last) {                                        // full_c head on the FP32 h of the last layer's last frame
-                                    const float* wf = fcS + (c * 64 + u0) * 8;
+                                    const float* wf = fcG + (c * 64 + u0) * 8;
 #pragma unroll
                                     for (int j = 0; j < 8; ++j) {
-                                        const float4 w0 = *reinterpret_cast<const float4*>(wf + j * 8);
-                                        const float2 w1 = *reinterpret_cast<const float2*>(wf + j * 8 + 4);
+                                        const float4 w0 = __ldg(reinterpret_cast<const float4*>(wf + j * 8));
+                                        const float2 w1 = __ldg(reinterpret_cast<const float2*>(wf + j * 8 + 4));
                                         y[0] = fmaf(hv[j], w0.x, y[0]); y[1] = fmaf(hv[j], w0.y, y[1]); y[2] = fmaf(hv[j], w0.z, y[2]);
                                         y[3] = fmaf(hv[j], w0.w, y[3]); y[4] = fmaf(hv[j], w1.x, y[4]); y[5] = fmaf(hv[j], w1.y, y[5]);
                                     }
@@ -147,7 +147,7 @@
 #pragma unroll
                     for (int d = 0; d < 6; ++d)
                         y[d] = y[d] + ypart[(0 * 6 + d) * LT_TN + row] + ypart[(1 * 6 + d) * LT_TN + row] + ypart[(2 * 6 + d) * LT_TN + row] +
-                               fcS[LT_HID * 8 + d];
+                               __ldg(fcG + LT_HID * 8 + d);
                     float nxt[6];
                     owner_finish(p, norm_l, y, nullptr, 1, 0, n, valid, t, u, nxt, cost);
                     // window shift: the oldest physical slot takes the new frame [s_{t+1}, u_t]
