@@ -686,7 +686,9 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
         build_lt_offsets(a->model, q.m);
         q.m.blob = a->wblob_tc;
         q.scratch = static_cast<unsigned char*>(a->scratch);
+#ifdef MPCDL_LT_DEBUG      // development builds only (make DEFS=-DMPCDL_LT_DEBUG, tools/lt_dbg.py): host-mapped progress words
         if (const char* e = getenv("MPCDL_LT_DBG")) q.dbg = reinterpret_cast<unsigned int*>(strtoull(e, nullptr, 0));
+#endif
         fill_io(q.io, *a, lp.ntiles);
         cudaError_t e = launch_lstm_tc(q, lp.grid, lp.smem_bytes, st);
         if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "BF16 LSTM kernel launch failed: %s (smem=%d)", cudaGetErrorString(e), lp.smem_bytes);
