@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- trajectory-steps/s of the fused rollout path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c3s|c4|c5|c5g] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c3s|c3l|c4|c5|c5g|c5m|c5gm|c4m] [--precision fp32|tf32x3|tf32|bf16] [--impl reference]
 
 A "step" is one whole-horizon rollout of the workload's batch of control sequences (one kernel
 launch).  Default workload = BASELINE.json configs[1] (C2): Basic_64_4_32, 4096 control samples x
@@ -64,6 +64,9 @@ WORKLOADS = {
                 ckpt="Basic_64_4_32", N=1048576, H=50, noise=False, states=False, flop=34560, cpu_n=65536, mppi=True),
     "c5gm": dict(desc="MPPI iteration, GRU_64_4_4_16_False, 1048576 samples x horizon 100 (in-kernel control sampling + softmin update)",
                  ckpt="GRU_64_4_4_16_False", N=1048576, H=100, noise=False, states=False, flop=701184, cpu_n=2048, mppi=True),
+    "c4m": dict(desc="MPPI iteration, LSTM hidden 256 x 4 layers (seeded random init), window 4, 65536 samples x horizon 50 "
+                     "(in-kernel control sampling + softmin update)",
+                ckpt="LSTM_256_4_4_0_False", N=65536, H=50, noise=False, states=False, flop=14748672, cpu_n=256, mppi=True),
 }
 
 
