@@ -369,7 +369,7 @@ def run_native(args, w):
         ach_tf = alg_flop / (k_ms * 1e-3) / 1e12
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload if prec == "fp32" else f"{args.workload}_{prec}")
         except Exception:
             pass
         if prec == "fp32":
