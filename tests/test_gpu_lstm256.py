@@ -139,3 +139,34 @@ def test_bf16_rejects_unsupported(gold_stats):
         m.rollout(win, U, None, precision="tf32")
     with pytest.raises(RuntimeError):           # CPU tensors: no fallback
         m.rollout(win.cpu(), U.cpu(), None, precision="bf16")
+
+
+def test_bf16_lstm256_full_size_properties(gold_stats):
+    """BASELINE config 4 at its full size (65 536 trajectories x horizon 100, 512 tiles on 74 CTA pairs):
+    size-independent properties instead of an oracle run -- (1) a trajectory's result does not depend on which tile /
+    CTA / wave it lands in: rolling out a permutation of the batch gives the permuted result BIT FOR BIT;
+    (2) a 256-trajectory sample agrees with the FP32 FFMA kernel on the same trajectories within the T3 bound over
+    the whole horizon; (3) costs equal the cost recomputed from the returned states."""
+    from mpcdl import synth
+    from oracle import rollout_ref as R
+    m, _ = _pair(4)
+    st = gold_stats[1]
+    N, H = 65536, 100
+    rows = synth.load_rows()
+    init, U = synth.make_inputs(rows, N, H, window=4, seed=0)
+    init, U = init.to(_dev()), U.to(_dev())
+    cost = tuple(c.to(_dev()) for c in synth.make_cost(rows, H))
+    s, c = m.rollout(init, U, st, precision="bf16", cost=cost)
+    assert not torch.isnan(s).any()
+    perm = torch.randperm(N, generator=torch.Generator().manual_seed(1)).to(_dev())
+    sp, cp = m.rollout(init[perm].contiguous(), U[perm].contiguous(), st, precision="bf16", cost=cost)
+    assert torch.equal(sp, s[perm]) and torch.equal(cp, c[perm])
+    del sp, cp
+    idx = perm[:256]
+    s32 = m.rollout(init[idx].contiguous(), U[idx].contiguous(), st, precision="fp32")[0]
+    q = _quantiles(R.rel_err(s[idx].cpu(), s32.cpu().double()))
+    for a, b in zip(q, QUANT):
+        assert a <= b, (q, QUANT)
+    ref, qw, rw = cost
+    want = (((s[idx] - ref[None]) ** 2) * qw).sum((1, 2)) + ((U[idx] ** 2) * rw).sum((1, 2))
+    assert ((c[idx] - want).abs() / want.abs()).max().item() <= 1e-4
