@@ -157,3 +157,32 @@ def test_mppi_entry_points_without_device():
     r.ctrl_lo, r.ctrl_hi = (C.c_float * 2)(1.0, 0.0), (C.c_float * 2)(0.0, 1.0)
     p = _lib.Plan()
     assert lib.mpcdl_rollout_plan(C.byref(r), C.byref(p)) == -1 and b"ctrl_lo" in lib.mpcdl_last_error()
+
+
+def test_ctypes_mirror_matches_the_compiled_header(tmp_path):
+    """The ctypes structures must have the layout a C compiler gives include/mpcdl.h: compile a probe with gcc that
+    prints sizeof / offsetof of every structure the binding mirrors and compare field by field."""
+    import shutil
+    import subprocess
+    from mpcdl import _lib
+    if shutil.which("gcc") is None:
+        pytest.skip("gcc not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    structs = {"mpcdl_rollout_args": _lib.RolloutArgs, "mpcdl_noise_args": _lib.NoiseArgs, "mpcdl_mppi_args": _lib.MppiArgs,
+               "mpcdl_plan": _lib.Plan, "mpcdl_model_desc": _lib.ModelDesc}
+    cfield = {"lam": "lambda"}                       # `lambda` is a Python keyword: the mirror calls it lam
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "mpcdl.h"', 'int main(void) {']
+    for cname, cls in structs.items():
+        lines.append(f'  printf("{cname} %zu\\n", sizeof({cname}));')
+        for fname, _ in cls._fields_:
+            lines.append(f'  printf("{cname}.{fname} %zu\\n", offsetof({cname}, {cfield.get(fname, fname)}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "probe.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "probe"
+    subprocess.run(["gcc", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)], check=True)
+    out = dict(l.split() for l in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    for cname, cls in structs.items():
+        assert int(out[cname]) == C.sizeof(cls), cname
+        for fname, _ in cls._fields_:
+            assert int(out[f"{cname}.{fname}"]) == getattr(cls, fname).offset, f"{cname}.{fname}"
