@@ -42,6 +42,19 @@ def _f32c(t: Optional[torch.Tensor], name: str, dev=None) -> int:
     return t.data_ptr()
 
 
+_BLOB_FLOATS = {}     # (tensor_core, kind, hidden, layers, window) -> floats: a pure function of the description
+
+
+def _blob_floats(desc, tc: bool) -> int:
+    key = (tc, desc.kind, desc.hidden, desc.layers, desc.window)
+    n = _BLOB_FLOATS.get(key)
+    if n is None:
+        n = (_lib.lib.mpcdl_blob_floats_tc if tc else _lib.lib.mpcdl_blob_floats)(C.byref(desc))
+        if n:
+            _BLOB_FLOATS[key] = n
+    return n
+
+
 def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob, noise_cfg,
                   eps, seed, traj_offset, cost_ref, cost_w, return_states, return_costs, tune, precision=0, wblob_tc=None,
                   ctrl=(), ctrl_seed=0, n_samples=0, shared_init=False):
@@ -67,14 +80,14 @@ def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, state
     a.model = _lib.ModelDesc(kind, hidden, layers, T)
     a.precision = int(precision)
     if a.precision != 0:
-        need = _lib.lib.mpcdl_blob_floats_tc(C.byref(a.model))
+        need = _blob_floats(a.model, True)
         if need == 0:
             _lib.check(-2)
         if wblob_tc is None or wblob_tc.numel() != need:
             raise RuntimeError(f"mpcdl: tensor-core precision needs wblob_tc with {need} floats (pack_rnn(..., tensor_core=True))")
         a.wblob_tc = _f32c(wblob_tc, "wblob_tc", dev)
     else:
-        need = _lib.lib.mpcdl_blob_floats(C.byref(a.model))
+        need = _blob_floats(a.model, False)
         if need == 0:
             _lib.check(-2)
         if wblob.numel() != need:
@@ -120,15 +133,18 @@ def _rollout_impl(kind: int, wblob, norm, init, U, hidden, layers, window, state
         a.ctrl_sigma, a.ctrl_lo, a.ctrl_hi = (C.c_float * 2)(*ctrl[0:2]), (C.c_float * 2)(*ctrl[2:4]), (C.c_float * 2)(*ctrl[4:6])
         a.ctrl_seed = ctrl_seed & 0xFFFFFFFFFFFFFFFF
     a.shared_init = int(bool(shared_init))
-    nscratch = _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a))
+    nscratch = _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a)) if a.precision == _lib.PRECISION["bf16"] else 0
     if nscratch:
         # per-CTA layer output sequences of the BF16 LSTM-256 kernel; from the caching allocator, so the buffer is
         # tied to the current stream like every other tensor of the call
         scratch = torch.empty(nscratch, device=dev, dtype=torch.uint8)
         a.scratch, a.scratch_bytes = scratch.data_ptr(), nscratch
-    with torch.cuda.device(dev):
-        stream = torch.cuda.current_stream(dev).cuda_stream
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    if torch.cuda.current_device() == dev.index:         # the launch goes to the CURRENT device: switch only when needed
         _lib.check(_lib.lib.mpcdl_rollout(C.byref(a), C.c_void_p(stream)))
+    else:
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib.mpcdl_rollout(C.byref(a), C.c_void_p(stream)))
     return states, costs
 
 
