@@ -38,6 +38,25 @@ class _Packed:
 class _RolloutMixin:
     KIND = None
 
+    def _params(self):
+        """The module's Parameter objects, enumerated once (nn.Module.parameters() walks the module tree: ~40 us per
+        call, a third of the host time of a rollout).  In-place updates are still seen through the version counters in
+        _Packed; .to() / load_state_dict() drop the list.  After REPLACING a Parameter object by hand, call
+        ``model._plist = None``."""
+        pl = self.__dict__.get("_plist")
+        if pl is None:
+            pl = list(self.parameters())
+            self.__dict__["_plist"] = pl
+        return pl
+
+    def _apply(self, fn, *args, **kwargs):
+        self.__dict__["_plist"] = None
+        return super()._apply(fn, *args, **kwargs)
+
+    def load_state_dict(self, *args, **kwargs):
+        self.__dict__["_plist"] = None
+        return super().load_state_dict(*args, **kwargs)
+
     def _desc(self):
         raise NotImplementedError
 
@@ -142,13 +161,13 @@ class Basic_Model(_RolloutMixin, nn.Module):
         return self._hidden, self._nlayers, 0
 
     def _blob(self, device):
-        return self._packed.get(list(self.parameters()), device,
+        return self._packed.get(self._params(), device,
                                 lambda: pack.pack_mlp(self.state_dict(), self._hidden, self._nlayers))
 
     def _blob_tc(self, device):
         if not hasattr(self, "_packed_tc"):
             self._packed_tc = _Packed()
-        return self._packed_tc.get(list(self.parameters()), device,
+        return self._packed_tc.get(self._params(), device,
                                    lambda: pack.pack_mlp(self.state_dict(), self._hidden, self._nlayers, tensor_core=True))
 
     def forward(self, x):
@@ -181,13 +200,13 @@ class _RNNBase(_RolloutMixin, nn.Module):
         return self.hidden, self.layers, self._window
 
     def _blob(self, device):
-        return self._packed.get(list(self.parameters()), device,
+        return self._packed.get(self._params(), device,
                                 lambda: pack.pack_rnn(self.state_dict(), self.KIND, self.hidden, self.layers, self._window))
 
     def _blob_tc(self, device):
         if not hasattr(self, "_packed_tc"):
             self._packed_tc = _Packed()
-        return self._packed_tc.get(list(self.parameters()), device,
+        return self._packed_tc.get(self._params(), device,
                                    lambda: pack.pack_rnn(self.state_dict(), self.KIND, self.hidden, self.layers, self._window,
                                                          tensor_core=True))
 
