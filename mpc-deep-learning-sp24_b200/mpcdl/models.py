@@ -302,8 +302,15 @@ class FeedforwardNoiseModel(nn.Module):
     def cfg(self):
         return [self.history, self.size, self.n_layers, _lib.ACT[self.activation]]
 
+    def _apply(self, fn, *args, **kwargs):
+        self.__dict__["_plist"] = None
+        return super()._apply(fn, *args, **kwargs)
+
     def packed(self, device):
-        return self._packed.get(list(self.model.parameters()), device,
+        pl = self.__dict__.get("_plist")                 # enumerated once, like _RolloutMixin._params
+        if pl is None:
+            pl = self.__dict__["_plist"] = list(self.model.parameters())
+        return self._packed.get(pl, device,
                                 lambda: pack.pack_noise(self.model.state_dict(), self.history, self.size, self.n_layers))
 
     def forward(self, q, u, eps=None, return_params=False):
