@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "../../include/mpcdl.h"
@@ -85,14 +86,42 @@ double mlp2_cycles(const Mlp2Cand& c, int TN) {
     return 6596.0 + (TN - 128) * 39.3;
 }
 
-int g_num_sms = 0, g_cc_major = 0;
-int device_info() {
-    if (g_num_sms) return MPCDL_OK;
+// Attributes of the CURRENT CUDA device, queried once per device ordinal under a mutex (a process may drive several
+// devices, and two threads may make their first call at once).  This table and the thread-local error string are the
+// only process-wide state of the library.  A failed query is not cached.
+struct DevInfo { int sms = 0, cc_major = 0; };
+constexpr int kMaxDevices = 64;
+DevInfo g_dev[kMaxDevices];
+std::mutex g_dev_mu;
+
+const DevInfo* device_info(bool quiet = false) {
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
-    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&g_cc_major, cudaDevAttrComputeCapabilityMajor, dev);
-    if (e != cudaSuccess) { g_num_sms = 0; return fail(MPCDL_ERR_CUDA, "CUDA device query failed: %s", cudaGetErrorString(e)); }
+    if (e == cudaSuccess && (dev < 0 || dev >= kMaxDevices)) e = cudaErrorInvalidDevice;
+    if (e == cudaSuccess) {
+        std::lock_guard<std::mutex> lk(g_dev_mu);
+        DevInfo& d = g_dev[dev];
+        if (d.sms) return &d;
+        int sms = 0, cc = 0;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&cc, cudaDevAttrComputeCapabilityMajor, dev);
+        if (e == cudaSuccess && sms > 0) { d.cc_major = cc; d.sms = sms; return &d; }
+    }
+    if (quiet) (void)cudaGetLastError();
+    else fail(MPCDL_ERR_CUDA, "CUDA device query failed: %s", cudaGetErrorString(e));
+    return nullptr;
+}
+// SM count the planner sizes grids (and the BF16 scratch) for: the current device's, or a B200's 148 when there is no
+// device (planning and the CPU-side tests work without a GPU)
+int planning_sms() {
+    const DevInfo* d = device_info(true);
+    return d ? d->sms : 148;
+}
+// current device must be sm_100: status code + the device's attributes
+int sm100_device(const DevInfo*& d) {
+    d = device_info();
+    if (!d) return MPCDL_ERR_CUDA;
+    if (d->cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", d->cc_major);
     return MPCDL_OK;
 }
 
@@ -624,7 +653,7 @@ int mpcdl_pack_noise(int history, int size, int n_layers, const float* const* W,
 size_t mpcdl_rollout_scratch_bytes(const mpcdl_rollout_args* a) {
     if (!a || a->precision != MPCDL_PREC_BF16 || !lt_supported(a->model) || a->N < 1) return 0;
     LtPlan lp;
-    make_lt_plan(*a, lp, g_num_sms ? g_num_sms : 148);
+    make_lt_plan(*a, lp, planning_sms());
     return (size_t)lp.grid * lt_scratch_bytes_per_cta(a->model.window);
 }
 
@@ -632,7 +661,7 @@ int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
     int rc = check_args(a);
     if (rc) return rc;
     if (!out) return fail(MPCDL_ERR_ARG, "plan is NULL");
-    int sms = g_num_sms ? g_num_sms : 148;                   // planning works without a device (B200 = 148 SMs)
+    const int sms = planning_sms();
     if (is_lt(*a)) {
         LtPlan lp;
         make_lt_plan(*a, lp, sms);
@@ -674,13 +703,13 @@ int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
 int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     int rc = check_args(a);
     if (rc) return rc;
-    rc = device_info();
-    if (rc) return rc;
-    if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    const int num_sms = di->sms;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (is_lt(*a)) {
         LtPlan lp;
-        make_lt_plan(*a, lp, g_num_sms);
+        make_lt_plan(*a, lp, num_sms);
         LtRolloutParams q;
         memset(&q, 0, sizeof(q));
         build_lt_offsets(a->model, q.m);
@@ -696,7 +725,7 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     }
     if (a->precision != MPCDL_PREC_FP32 && a->model.kind == MPCDL_MLP) {
         McPlan mp;
-        rc = make_mc_plan(*a, mp, g_num_sms);
+        rc = make_mc_plan(*a, mp, num_sms);
         if (rc) return rc;
         McRolloutParams q;
         memset(&q, 0, sizeof(q));
@@ -709,7 +738,7 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     }
     if (a->precision != MPCDL_PREC_FP32) {
         TcPlan tp;
-        rc = make_tc_plan(*a, tp, g_num_sms);
+        rc = make_tc_plan(*a, tp, num_sms);
         if (rc) return rc;
         TcRolloutParams q;
         memset(&q, 0, sizeof(q));
@@ -725,7 +754,7 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
         return MPCDL_OK;
     }
     Plan pl;
-    rc = make_plan(*a, pl, g_num_sms);
+    rc = make_plan(*a, pl, num_sms);
     if (rc) return rc;
 
     RolloutParams p;
@@ -752,9 +781,8 @@ int mpcdl_noise_forward(const mpcdl_noise_args* a, void* stream) {
     if (a->size < 4 || a->size > 64 || a->size % 4) return fail(MPCDL_ERR_UNSUPPORTED, "noise size=%d must be a multiple of 4 in [4,64]", a->size);
     if (a->n_layers < 0 || a->n_layers > MAX_NOISE_LAYERS) return fail(MPCDL_ERR_UNSUPPORTED, "noise n_layers=%d outside [0,%d]", a->n_layers, MAX_NOISE_LAYERS);
     if (a->act < MPCDL_ACT_IDENTITY || a->act > MPCDL_ACT_SIGMOID) return fail(MPCDL_ERR_UNSUPPORTED, "noise activation %d unsupported", a->act);
-    int rc = device_info();
-    if (rc) return rc;
-    if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
     AuxParams p;
     memset(&p, 0, sizeof(p));
     p.nz.blob = a->noise_wblob; p.nz.enabled = 1; p.nz.hist = a->history; p.nz.size = a->size; p.nz.nlayers = a->n_layers;
@@ -765,7 +793,7 @@ int mpcdl_noise_forward(const mpcdl_noise_args* a, void* stream) {
     p.ntiles = (int)((a->N + AUX_TN - 1) / AUX_TN);
     const int smem = aux_smem_bytes(p.nz.blob_floats, p.nz.in_dim, p.nz.size);
     if (smem > SMEM_LIMIT) return fail(MPCDL_ERR_UNSUPPORTED, "noise net needs %d bytes of shared memory", smem);
-    cudaError_t e = launch_aux(p, a->closed_loop != 0, std::min(p.ntiles, g_num_sms), smem, static_cast<cudaStream_t>(stream));
+    cudaError_t e = launch_aux(p, a->closed_loop != 0, std::min(p.ntiles, di->sms), smem, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "noise kernel launch failed: %s", cudaGetErrorString(e));
     return MPCDL_OK;
 }
@@ -774,9 +802,8 @@ size_t mpcdl_mppi_workspace_floats(int H) { return H < 1 ? 0 : (size_t)MPPI_GRID
 
 int mpcdl_mppi_min(const float* costs, int64_t N, float* workspace, float* cmin_out, void* stream) {
     if (!costs || !workspace || !cmin_out || N < 1) return fail(MPCDL_ERR_ARG, "mpcdl_mppi_min: bad arguments");
-    int rc = device_info();
-    if (rc) return rc;
-    if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
     cudaError_t e = launch_mppi_min(costs, N, workspace, cmin_out, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "mppi_min launch failed: %s", cudaGetErrorString(e));
     return MPCDL_OK;
@@ -787,9 +814,8 @@ int mpcdl_mppi_reduce(const mpcdl_mppi_args* a, void* stream) {
     if (!a->costs || !a->U || !a->workspace || !a->sums) return fail(MPCDL_ERR_ARG, "costs/U/workspace/sums must be non-NULL device pointers");
     if (a->N < 1 || a->H < 1 || a->H > MPPI_MAX_H) return fail(MPCDL_ERR_ARG, "N=%lld must be >= 1 and H=%d in [1,%d]", (long long)a->N, a->H, MPPI_MAX_H);
     if (!(a->lambda > 0.f)) return fail(MPCDL_ERR_ARG, "lambda must be > 0");
-    int rc = device_info();
-    if (rc) return rc;
-    if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     MppiParams p;
     memset(&p, 0, sizeof(p));
@@ -808,9 +834,8 @@ int mpcdl_mppi_reduce(const mpcdl_mppi_args* a, void* stream) {
 
 int mpcdl_error_metrics(const float* output, const float* labels, int64_t B, float* mae, float* rmse, void* stream) {
     if (!output || !labels || !mae || !rmse || B < 1) return fail(MPCDL_ERR_ARG, "mpcdl_error_metrics: bad arguments");
-    int rc = device_info();
-    if (rc) return rc;
-    if (g_cc_major != 10) return fail(MPCDL_ERR_DEVICE, "mpcdl kernels are built for sm_100a only (device is sm_%d*)", g_cc_major);
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
     cudaError_t e = launch_error_metrics(output, labels, B, mae, rmse, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "error_metrics launch failed: %s", cudaGetErrorString(e));
     return MPCDL_OK;

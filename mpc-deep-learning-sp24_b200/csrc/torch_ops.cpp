@@ -1,0 +1,321 @@
+// torch.ops.mpcdl.* -- the compiled operator boundary of the fused rollout path (TORCH_LIBRARY, CUDA key only).
+//
+// Every operator checks its tensors (CUDA, float32, contiguous, same device, shapes), fills the plain-C argument
+// struct of include/mpcdl.h and calls the C ABI on at::cuda::getCurrentCUDAStream().  No torch kernel runs here and
+// there is no CPU implementation: CPU tensors fail in the dispatcher.  The ctypes binding (mpcdl/_lib.py) stays for
+// hosts without torch and for the packers / planner.
+//
+// Reference surface replaced: Basic_Model.forward model_scripts/basic_model.py:58-61, GRU_Model.forward /
+// LSTM_Model.forward model_scripts/deep_models.py:60-66 / 85-92, FeedforwardNoiseModel.forward model_scripts/noise_model.py:34-40,
+// DynamicsNN.get_prediction noise_model.py:113-125, the feedback loop of run_dynamics_model scripts/test_model.py:67-87 and
+// the per-sample metrics of eval_models.calc_error model_scripts/eval_models.py:91-92.
+#include <ATen/ATen.h>
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <torch/library.h>
+
+#include <cstring>
+#include <tuple>
+
+#include "../../include/mpcdl.h"
+
+namespace {
+
+using at::Tensor;
+using OptTensor = std::optional<Tensor>;
+
+void check_status(int rc) { TORCH_CHECK(rc == MPCDL_OK, "mpcdl error ", rc, ": ", mpcdl_last_error()); }
+
+// float32 + CUDA + contiguous + on `dev`; returns the raw device pointer
+float* f32c(const Tensor& t, const char* name, const c10::Device& dev) {
+    TORCH_CHECK(t.scalar_type() == at::kFloat, "mpcdl: ", name, " must be float32, got ", t.scalar_type());
+    TORCH_CHECK(t.is_cuda(), "mpcdl: ", name, " must be a CUDA tensor (no CPU fallback), got ", t.device());
+    TORCH_CHECK(t.device() == dev, "mpcdl: ", name, " is on ", t.device(), ", expected ", dev);
+    TORCH_CHECK(t.is_contiguous(), "mpcdl: ", name, " must be contiguous");
+    return static_cast<float*>(t.data_ptr());
+}
+float* f32c(const OptTensor& t, const char* name, const c10::Device& dev) {
+    return t.has_value() && t->defined() ? f32c(*t, name, dev) : nullptr;
+}
+bool has(const OptTensor& t) { return t.has_value() && t->defined(); }
+
+std::tuple<Tensor, Tensor> rollout(int kind, const OptTensor& wblob, const Tensor& norm, const Tensor& init, const Tensor& U,
+                                   int64_t hidden, int64_t layers, int64_t window, bool stateful, const OptTensor& carry,
+                                   const OptTensor& noise_wblob, at::IntArrayRef noise_cfg, const OptTensor& eps, int64_t seed,
+                                   int64_t traj_offset, const OptTensor& cost_ref, at::ArrayRef<double> cost_w, bool return_states,
+                                   bool return_costs, at::IntArrayRef tune, int64_t precision, const OptTensor& wblob_tc,
+                                   at::ArrayRef<double> ctrl, int64_t ctrl_seed, int64_t n_samples, bool shared_init,
+                                   const OptTensor& out_states, const OptTensor& out_costs) {
+    TORCH_CHECK(U.is_cuda(), "mpcdl: U must be a CUDA tensor (no CPU fallback), got ", U.device());
+    const c10::Device dev = U.device();
+    const int T = kind == MPCDL_MLP ? 0 : (int)window;
+    int64_t N, H;
+    if (!ctrl.empty()) {
+        // MPPI call: U is the nominal sequence [H,2]; the N sampled sequences exist only in registers
+        TORCH_CHECK(ctrl.size() == 6 && U.dim() == 2 && U.size(1) == 2 && n_samples >= 1,
+                    "mpcdl: sampled controls need U [H,2], ctrl = sigma[2]+lo[2]+hi[2] and n_samples >= 1; got U ", U.sizes());
+        N = n_samples; H = U.size(0);
+    } else {
+        TORCH_CHECK(U.dim() == 3 && U.size(2) == 2, "mpcdl: U must be [N,H,2], got ", U.sizes());
+        N = U.size(0); H = U.size(1);
+    }
+    {
+        const int64_t lead = shared_init ? 0 : 1;
+        const bool ok = kind == MPCDL_MLP ? (init.dim() == lead + 1 && init.size(lead) == 6)
+                                          : (init.dim() == lead + 2 && init.size(lead) == T && init.size(lead + 1) == 8);
+        TORCH_CHECK(ok && (shared_init || init.size(0) == N), "mpcdl: init must be ", shared_init ? "" : "[N] + ",
+                    kind == MPCDL_MLP ? "[6]" : "[window,8]", " with N = ", N, ", got ", init.sizes());
+    }
+    const int nt = T > 0 ? T : 1;
+    TORCH_CHECK(norm.numel() == 2 * nt * 8 + 12, "mpcdl: norm must hold ", 2 * nt * 8 + 12, " floats (f_mean,f_std [", nt,
+                ",8]; l_mean,l_std [6])");
+    mpcdl_rollout_args a;
+    std::memset(&a, 0, sizeof(a));
+    a.model.kind = kind; a.model.hidden = (int32_t)hidden; a.model.layers = (int32_t)layers; a.model.window = T;
+    a.precision = (int32_t)precision;
+    if (a.precision != MPCDL_PREC_FP32) {
+        const size_t need = mpcdl_blob_floats_tc(&a.model);
+        if (need == 0) check_status(MPCDL_ERR_UNSUPPORTED);
+        TORCH_CHECK(has(wblob_tc) && (size_t)wblob_tc->numel() == need, "mpcdl: tensor-core precision needs wblob_tc with ", need,
+                    " floats (pack_rnn(..., tensor_core=True))");
+        a.wblob_tc = f32c(wblob_tc, "wblob_tc", dev);
+    } else {
+        const size_t need = mpcdl_blob_floats(&a.model);
+        if (need == 0) check_status(MPCDL_ERR_UNSUPPORTED);
+        TORCH_CHECK(has(wblob) && (size_t)wblob->numel() == need, "mpcdl: wblob has ", has(wblob) ? wblob->numel() : 0,
+                    " floats, model needs ", need);
+        a.wblob = f32c(wblob, "wblob", dev);
+    }
+    a.stateful = stateful && kind != MPCDL_MLP;
+    a.norm = f32c(norm, "norm", dev);
+    a.init = f32c(init, "init", dev);
+    a.U = f32c(U, "U", dev);
+    // caller-owned result buffers (a pipeline that overlaps the copy-out keeps one pair per slot) or fresh ones
+    Tensor states, costs;
+    if (return_states && has(out_states)) {
+        TORCH_CHECK(out_states->dim() == 3 && out_states->size(0) == N && out_states->size(1) == H && out_states->size(2) == 6,
+                    "mpcdl: out_states must be [", N, ",", H, ",6], got ", out_states->sizes());
+        f32c(*out_states, "out_states", dev);
+        states = *out_states;
+    } else {
+        states = return_states ? at::empty({N, H, 6}, U.options()) : at::empty({0}, U.options());
+    }
+    if (return_costs && has(out_costs)) {
+        TORCH_CHECK(out_costs->dim() == 1 && out_costs->size(0) == N, "mpcdl: out_costs must be [", N, "], got ", out_costs->sizes());
+        f32c(*out_costs, "out_costs", dev);
+        costs = *out_costs;
+    } else {
+        costs = return_costs ? at::empty({N}, U.options()) : at::empty({0}, U.options());
+    }
+    a.states = return_states ? static_cast<float*>(states.data_ptr()) : nullptr;
+    a.costs = return_costs ? static_cast<float*>(costs.data_ptr()) : nullptr;
+    if (has(cost_ref)) {
+        TORCH_CHECK(cost_ref->dim() == 2 && cost_ref->size(0) == H && cost_ref->size(1) == 6 && cost_w.size() == 8,
+                    "mpcdl: cost_ref must be [H,6] and cost_w = qw[6] + rw[2]");
+        a.cost_ref = f32c(cost_ref, "cost_ref", dev);
+    }
+    if (cost_w.size() == 8) {
+        for (int i = 0; i < 6; ++i) a.cost_qw[i] = (float)cost_w[i];
+        for (int i = 0; i < 2; ++i) a.cost_rw[i] = (float)cost_w[6 + i];
+    }
+    if (has(noise_wblob)) {
+        TORCH_CHECK(noise_cfg.size() == 4, "mpcdl: noise_cfg = [history, size, n_layers, act]");
+        TORCH_CHECK((size_t)noise_wblob->numel() == mpcdl_noise_blob_floats((int)noise_cfg[0], (int)noise_cfg[1], (int)noise_cfg[2]),
+                    "mpcdl: noise_wblob size does not match noise_cfg");
+        a.noise_wblob = f32c(noise_wblob, "noise_wblob", dev);
+        a.noise_history = (int32_t)noise_cfg[0]; a.noise_size = (int32_t)noise_cfg[1];
+        a.noise_layers = (int32_t)noise_cfg[2]; a.noise_act = (int32_t)noise_cfg[3];
+        if (has(eps)) {
+            TORCH_CHECK(eps->dim() == 3 && eps->size(0) == N && eps->size(1) == H && eps->size(2) == 6,
+                        "mpcdl: eps must be [N,H,6], got ", eps->sizes());
+            a.eps = f32c(eps, "eps", dev);
+        }
+    }
+    a.seed = (uint64_t)seed;
+    a.traj_offset = traj_offset;
+    if (a.stateful) {
+        const int64_t planes = layers * (kind == MPCDL_LSTM ? 2 : 1);
+        TORCH_CHECK(has(carry) && carry->dim() == 3 && carry->size(0) == planes && carry->size(1) == N && carry->size(2) == hidden,
+                    "mpcdl: stateful rollout needs carry [", planes, ",", N, ",", hidden, "]");
+        a.carry = f32c(carry, "carry", dev);
+    }
+    a.N = N; a.H = (int32_t)H;
+    if (tune.size() == 4) { a.tune_rt = (int32_t)tune[0]; a.tune_ntg = (int32_t)tune[1]; a.tune_nslots = (int32_t)tune[2]; a.tune_kc = (int32_t)tune[3]; }
+    if (!ctrl.empty()) {
+        a.sample_controls = 1;
+        for (int i = 0; i < 2; ++i) { a.ctrl_sigma[i] = (float)ctrl[i]; a.ctrl_lo[i] = (float)ctrl[2 + i]; a.ctrl_hi[i] = (float)ctrl[4 + i]; }
+        a.ctrl_seed = (uint64_t)ctrl_seed;
+    }
+    a.shared_init = shared_init;
+    c10::cuda::CUDAGuard guard(dev);                     // the launch goes to the tensors' device
+    Tensor scratch;
+    if (a.precision == MPCDL_PREC_BF16) {
+        // per-CTA layer output sequences of the BF16 LSTM-256 kernel; from the caching allocator, so the buffer is tied to
+        // the current stream like every other tensor of the call
+        const size_t nscratch = mpcdl_rollout_scratch_bytes(&a);
+        if (nscratch) {
+            scratch = at::empty({(int64_t)nscratch}, U.options().dtype(at::kByte));
+            a.scratch = scratch.data_ptr(); a.scratch_bytes = nscratch;
+        }
+    }
+    check_status(mpcdl_rollout(&a, at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return {states, costs};
+}
+
+#define MPCDL_ROLLOUT_ARGS                                                                                                          \
+    const OptTensor &wblob, const Tensor &norm, const Tensor &init, const Tensor &U, int64_t hidden, int64_t layers, int64_t window, \
+        bool stateful, const OptTensor &carry, const OptTensor &noise_wblob, at::IntArrayRef noise_cfg, const OptTensor &eps,        \
+        int64_t seed, int64_t traj_offset, const OptTensor &cost_ref, at::ArrayRef<double> cost_w, bool return_states,              \
+        bool return_costs, at::IntArrayRef tune, int64_t precision, const OptTensor &wblob_tc, at::ArrayRef<double> ctrl,           \
+        int64_t ctrl_seed, int64_t n_samples, bool shared_init, const OptTensor &out_states, const OptTensor &out_costs
+#define MPCDL_ROLLOUT_PASS                                                                                                          \
+    wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob, noise_cfg, eps, seed, traj_offset, cost_ref, cost_w, \
+        return_states, return_costs, tune, precision, wblob_tc, ctrl, ctrl_seed, n_samples, shared_init, out_states, out_costs
+
+std::tuple<Tensor, Tensor> rollout_mlp(MPCDL_ROLLOUT_ARGS) { return rollout(MPCDL_MLP, MPCDL_ROLLOUT_PASS); }
+std::tuple<Tensor, Tensor> rollout_gru(MPCDL_ROLLOUT_ARGS) { return rollout(MPCDL_GRU, MPCDL_ROLLOUT_PASS); }
+std::tuple<Tensor, Tensor> rollout_lstm(MPCDL_ROLLOUT_ARGS) { return rollout(MPCDL_LSTM, MPCDL_ROLLOUT_PASS); }
+
+// ---------------------------------------------------------------------------- noise net / error metrics / MPPI update
+void noise_args(mpcdl_noise_args& a, const Tensor& noise_wblob, at::IntArrayRef cfg, const c10::Device& dev) {
+    std::memset(&a, 0, sizeof(a));
+    TORCH_CHECK(cfg.size() == 4, "mpcdl: noise_cfg = [history, size, n_layers, act]");
+    TORCH_CHECK((size_t)noise_wblob.numel() == mpcdl_noise_blob_floats((int)cfg[0], (int)cfg[1], (int)cfg[2]),
+                "mpcdl: noise_wblob size does not match noise_cfg");
+    a.noise_wblob = f32c(noise_wblob, "noise_wblob", dev);
+    a.history = (int32_t)cfg[0]; a.size = (int32_t)cfg[1]; a.n_layers = (int32_t)cfg[2]; a.act = (int32_t)cfg[3];
+}
+
+// FeedforwardNoiseModel.forward (model_scripts/noise_model.py:34-40): q [B,6*hist], u [B,2*hist] -> [B,6]
+std::tuple<Tensor, Tensor, Tensor> noise_forward(const Tensor& noise_wblob, at::IntArrayRef cfg, const Tensor& q, const Tensor& u,
+                                                 const OptTensor& eps, int64_t seed, int64_t traj_offset, int64_t step0,
+                                                 bool return_params) {
+    TORCH_CHECK(q.is_cuda(), "mpcdl: q must be a CUDA tensor (no CPU fallback), got ", q.device());
+    const c10::Device dev = q.device();
+    mpcdl_noise_args a;
+    noise_args(a, noise_wblob, cfg, dev);
+    const int64_t hist = a.history;
+    TORCH_CHECK(q.dim() == 2 && q.size(1) == 6 * hist && u.dim() == 2 && u.size(0) == q.size(0) && u.size(1) == 2 * hist,
+                "mpcdl: noise forward needs q [B,", 6 * hist, "] and u [B,", 2 * hist, "], got ", q.sizes(), " ", u.sizes());
+    const int64_t B = q.size(0);
+    a.q = f32c(q, "q", dev); a.u = f32c(u, "u", dev);
+    if (has(eps)) {
+        TORCH_CHECK(eps->dim() == 2 && eps->size(0) == B && eps->size(1) == 6, "mpcdl: eps must be [B,6], got ", eps->sizes());
+        a.eps = f32c(eps, "eps", dev);
+    }
+    a.seed = (uint64_t)seed; a.traj_offset = traj_offset; a.step0 = (int32_t)step0;
+    Tensor out = at::empty({B, 6}, q.options());
+    Tensor mu = return_params ? at::empty({B, 6}, q.options()) : at::empty({0}, q.options());
+    Tensor scale = return_params ? at::empty({B, 6}, q.options()) : at::empty({0}, q.options());
+    a.out = static_cast<float*>(out.data_ptr());
+    if (return_params) { a.mu = static_cast<float*>(mu.data_ptr()); a.scale = static_cast<float*>(scale.data_ptr()); }
+    a.N = B; a.H = 1;
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_noise_forward(&a, at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return {out, mu, scale};
+}
+
+// DynamicsNN.get_prediction fed back on itself (noise_model.py:113-125, test_model.py:67-87), fused over H
+Tensor dynamics_nn_rollout(const Tensor& noise_wblob, at::IntArrayRef cfg, const Tensor& q0, const Tensor& U, const OptTensor& eps,
+                           int64_t seed, int64_t traj_offset) {
+    TORCH_CHECK(U.is_cuda(), "mpcdl: U must be a CUDA tensor (no CPU fallback), got ", U.device());
+    const c10::Device dev = U.device();
+    mpcdl_noise_args a;
+    noise_args(a, noise_wblob, cfg, dev);
+    TORCH_CHECK(U.dim() == 3 && U.size(2) == 2 && q0.dim() == 2 && q0.size(0) == U.size(0) && q0.size(1) == 6,
+                "mpcdl: DynamicsNN rollout needs q0 [N,6] and U [N,H,2], got ", q0.sizes(), " ", U.sizes());
+    const int64_t N = U.size(0), H = U.size(1);
+    a.closed_loop = 1;
+    a.q = f32c(q0, "q0", dev); a.u = f32c(U, "U", dev);
+    if (has(eps)) {
+        TORCH_CHECK(eps->dim() == 3 && eps->size(0) == N && eps->size(1) == H && eps->size(2) == 6, "mpcdl: eps must be [N,H,6], got ",
+                    eps->sizes());
+        a.eps = f32c(eps, "eps", dev);
+    }
+    a.seed = (uint64_t)seed; a.traj_offset = traj_offset;
+    Tensor out = at::empty({N, H, 6}, U.options());
+    a.out = static_cast<float*>(out.data_ptr());
+    a.N = N; a.H = (int32_t)H;
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_noise_forward(&a, at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return out;
+}
+
+// per-sample MAE / RMSE of eval_models.calc_error (model_scripts/eval_models.py:91-92)
+std::tuple<Tensor, Tensor> error_metrics(const Tensor& output, const Tensor& labels) {
+    TORCH_CHECK(output.is_cuda(), "mpcdl: output must be a CUDA tensor (no CPU fallback), got ", output.device());
+    const c10::Device dev = output.device();
+    TORCH_CHECK(output.dim() == 2 && output.size(1) == 6 && output.sizes() == labels.sizes(),
+                "mpcdl: error_metrics needs output and labels [B,6], got ", output.sizes(), " ", labels.sizes());
+    const int64_t B = output.size(0);
+    Tensor mae = at::empty({B}, output.options()), rmse = at::empty({B}, output.options());
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_error_metrics(f32c(output, "output", dev), f32c(labels, "labels", dev), B, static_cast<float*>(mae.data_ptr()),
+                                     static_cast<float*>(rmse.data_ptr()), at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return {mae, rmse};
+}
+
+Tensor mppi_min(const Tensor& costs) {
+    TORCH_CHECK(costs.is_cuda(), "mpcdl: costs must be a CUDA tensor (no CPU fallback), got ", costs.device());
+    const c10::Device dev = costs.device();
+    Tensor ws = at::empty({(int64_t)mpcdl_mppi_workspace_floats(1)}, costs.options());
+    Tensor out = at::empty({1}, costs.options());
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_mppi_min(f32c(costs, "costs", dev), costs.numel(), static_cast<float*>(ws.data_ptr()),
+                                static_cast<float*>(out.data_ptr()), at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return out;
+}
+
+// sums [2H+2] = [sum_n w_n (u_n - U) per (t, channel), sum_n w_n, cmin]; include/mpcdl.h mpcdl_mppi_reduce
+Tensor mppi_reduce(const Tensor& costs, const Tensor& U, at::ArrayRef<double> ctrl, int64_t ctrl_seed, int64_t traj_offset, double lam,
+                   const OptTensor& cmin) {
+    TORCH_CHECK(costs.is_cuda(), "mpcdl: costs must be a CUDA tensor (no CPU fallback), got ", costs.device());
+    const c10::Device dev = costs.device();
+    TORCH_CHECK(U.dim() == 2 && U.size(1) == 2 && ctrl.size() == 6 && costs.dim() == 1,
+                "mpcdl: mppi_reduce needs costs [N], U [H,2], ctrl = sigma[2]+lo[2]+hi[2]");
+    const int64_t H = U.size(0);
+    mpcdl_mppi_args a;
+    std::memset(&a, 0, sizeof(a));
+    a.costs = f32c(costs, "costs", dev); a.N = costs.numel(); a.traj_offset = traj_offset; a.H = (int32_t)H;
+    a.U = f32c(U, "U", dev);
+    for (int i = 0; i < 2; ++i) { a.ctrl_sigma[i] = (float)ctrl[i]; a.ctrl_lo[i] = (float)ctrl[2 + i]; a.ctrl_hi[i] = (float)ctrl[4 + i]; }
+    a.ctrl_seed = (uint64_t)ctrl_seed; a.lambda = (float)lam;
+    if (has(cmin)) a.cmin = f32c(cmin, "cmin", dev);
+    Tensor ws = at::empty({(int64_t)mpcdl_mppi_workspace_floats((int)H)}, costs.options());
+    Tensor sums = at::empty({2 * H + 2}, costs.options());
+    a.workspace = static_cast<float*>(ws.data_ptr()); a.sums = static_cast<float*>(sums.data_ptr());
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_mppi_reduce(&a, at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return sums;
+}
+
+}  // namespace
+
+#define MPCDL_ROLLOUT_SCHEMA                                                                                                          \
+    "(Tensor? wblob, Tensor norm, Tensor init, Tensor U, int hidden, int layers, int window, bool stateful, Tensor(a!)? carry, "       \
+    "Tensor? noise_wblob, int[] noise_cfg, Tensor? eps, int seed, int traj_offset, Tensor? cost_ref, float[] cost_w, "                \
+    "bool return_states, bool return_costs, int[] tune, int precision, Tensor? wblob_tc, float[] ctrl, int ctrl_seed, "               \
+    "int n_samples, bool shared_init, Tensor(b!)? out_states, Tensor(c!)? out_costs) -> (Tensor, Tensor)"
+
+TORCH_LIBRARY(mpcdl, m) {
+    m.def("rollout_mlp" MPCDL_ROLLOUT_SCHEMA);
+    m.def("rollout_gru" MPCDL_ROLLOUT_SCHEMA);
+    m.def("rollout_lstm" MPCDL_ROLLOUT_SCHEMA);
+    m.def("noise_forward(Tensor noise_wblob, int[] noise_cfg, Tensor q, Tensor u, Tensor? eps, int seed, int traj_offset, int step0, "
+          "bool return_params) -> (Tensor, Tensor, Tensor)");
+    m.def("dynamics_nn_rollout(Tensor noise_wblob, int[] noise_cfg, Tensor q0, Tensor U, Tensor? eps, int seed, int traj_offset) -> Tensor");
+    m.def("error_metrics(Tensor output, Tensor labels) -> (Tensor, Tensor)");
+    m.def("mppi_reduce(Tensor costs, Tensor U, float[] ctrl, int ctrl_seed, int traj_offset, float lam, Tensor? cmin) -> Tensor");
+    m.def("mppi_min(Tensor costs) -> Tensor");
+}
+
+TORCH_LIBRARY_IMPL(mpcdl, CUDA, m) {
+    m.impl("rollout_mlp", &rollout_mlp);
+    m.impl("rollout_gru", &rollout_gru);
+    m.impl("rollout_lstm", &rollout_lstm);
+    m.impl("noise_forward", &noise_forward);
+    m.impl("dynamics_nn_rollout", &dynamics_nn_rollout);
+    m.impl("error_metrics", &error_metrics);
+    m.impl("mppi_reduce", &mppi_reduce);
+    m.impl("mppi_min", &mppi_min);
+}

@@ -64,38 +64,50 @@ class _RolloutMixin:
         raise NotImplementedError
 
     @staticmethod
-    def _tkey(t):
-        return (t.data_ptr(), t._version, str(t.device)) if isinstance(t, torch.Tensor) else id(t)
+    def _same(held, vals):
+        """True if `vals` are the very tensor objects the cache holds, unchanged (version counters).  The cache keeps
+        the source tensors alive, so neither an id nor a data pointer can be recycled under it; anything that is not a
+        torch tensor (lists, numpy arrays, python floats) is never cached -- it is converted on every call.
+        Blind spot, as for ``_Packed``: writes through ``.data`` do not move the version counter."""
+        return len(held) == len(vals) and all(a is b and a._version == v for (a, v), b in zip(held, vals))
 
     def _norm(self, stats, device):
-        """Device copy of the statistics vector, cached on the identity/version of the stats tensors
-        (no per-call host work: the planner calls rollout() in a tight loop)."""
+        """Device copy of the statistics vector (28 / 76 floats).  Cached only for torch tensors (see ``_same``)."""
         if stats is None:
             key = ("identity", str(device), self._desc()[2])
             if getattr(self, "_norm_key", None) != key:
-                self._norm_buf = pack.identity_norm(self._desc()[2]).to(device)
+                self._norm_id = pack.identity_norm(self._desc()[2]).to(device)
                 self._norm_key = key
-            return self._norm_buf
-        key = (str(device),) + tuple(self._tkey(stats[k]) for k in ("f_mean", "f_std", "l_mean", "l_std"))
-        if getattr(self, "_norm_key", None) != key:
-            self._norm_buf = pack.pack_norm({k: torch.as_tensor(v).detach().cpu() for k, v in stats.items()}).to(device)
-            self._norm_key = key
-        return self._norm_buf
+            return self._norm_id
+        vals = [stats[k] for k in ("f_mean", "f_std", "l_mean", "l_std")]
+        cacheable = all(isinstance(v, torch.Tensor) for v in vals)
+        c = self.__dict__.get("_norm_cache")
+        if cacheable and c is not None and c[0] == device and self._same(c[1], vals):
+            return c[2]
+        buf = pack.pack_norm({k: torch.as_tensor(v).detach().cpu() for k, v in stats.items()}).to(device)
+        self.__dict__["_norm_cache"] = (device, [(v, v._version) for v in vals], buf) if cacheable else None
+        return buf
 
     def _cost(self, cost, device):
-        """(ref [H,6], qw [6], rw [2]) -> (device ref, 8 python floats), cached like the statistics so
-        weights that live on the GPU are read back (a device sync) once, not on every call."""
-        key = (str(device),) + tuple(self._tkey(c) for c in cost)
-        if getattr(self, "_cost_key", None) != key:
-            cref = torch.as_tensor(cost[0]).to(device, torch.float32).contiguous()
-            cw = [float(v) for v in torch.as_tensor(cost[1]).detach().cpu().reshape(-1)] + \
-                 [float(v) for v in torch.as_tensor(cost[2]).detach().cpu().reshape(-1)]
-            self._cost_val, self._cost_key = (cref, cw), key
-        return self._cost_val
+        """(ref [H,6], qw [6], rw [2]) -> (device ref, 8 python floats).  Weights given as lists / numpy / CPU tensors
+        are read on every call (8 floats); only torch tensors are cached, by object identity + version, with the cache
+        holding them (weights that live on the GPU are read back -- a device sync -- once, not on every call)."""
+        c = self.__dict__.get("_cost_cache")
+        cacheable = all(isinstance(v, torch.Tensor) for v in cost)
+        if cacheable and c is not None and c[0] == device and self._same(c[1], cost):
+            return c[2]
+        cref = torch.as_tensor(cost[0]).to(device, torch.float32).contiguous()
+        cw = [float(v) for v in torch.as_tensor(cost[1]).detach().cpu().reshape(-1)] + \
+             [float(v) for v in torch.as_tensor(cost[2]).detach().cpu().reshape(-1)]
+        if len(cw) != 8:
+            raise RuntimeError(f"mpcdl: cost weights must be qw [6] and rw [2], got {len(cw)} values")
+        self.__dict__["_cost_cache"] = (device, [(v, v._version) for v in cost], (cref, cw)) if cacheable else None
+        return cref, cw
 
     @torch.no_grad()
     def rollout(self, init, U, stats=None, *, noise=None, eps=None, seed=0, traj_offset=0, cost=None,
-                return_states=True, stateful=None, carry=None, tune=(), precision=None, sample=None, shared_init=False):
+                return_states=True, stateful=None, carry=None, tune=(), precision=None, sample=None, shared_init=False,
+                out=None):
         """Closed-loop rollout of N trajectories over H steps in one kernel launch.
 
         init  s0 [N,6] (MLP) or window [N,T,8] (GRU/LSTM), raw units; U [N,H,2] controls.
@@ -108,6 +120,7 @@ class _RolloutMixin:
         sample  MPPI call: dict(n=N, sigma=(s_a, s_steer), lo=(..), hi=(..), seed=int) -> U is the NOMINAL sequence
               [H,2] and trajectory n applies clamp(U + sigma * z_n) with z_n drawn in-kernel (Philox keyed by
               seed, traj_offset + n, t); no [N,H,2] tensor exists.  shared_init: init is ONE state / window.
+        out   (states [N,H,6] | None, costs [N] | None): caller-owned result buffers to write into instead of fresh ones.
         Returns (states [N,H,6] or None, costs [N] or None[, carry if stateful])."""
         hidden, layers, window = self._desc()
         dev = U.device
@@ -130,11 +143,13 @@ class _RolloutMixin:
         if precision not in _lib.PRECISION:
             raise RuntimeError(f"mpcdl: unknown precision {precision!r} (fp32 | tf32x3 | tf32 | bf16)")
         prec = _lib.PRECISION[precision]
-        states, costs = ops.OPS[self.KIND](self._blob(dev), self._norm(stats, dev), init, U, hidden, layers, window,
+        # the blob of the precision in use only (the other one is never packed or uploaded)
+        states, costs = ops.OPS[self.KIND](self._blob(dev) if prec == 0 else None, self._norm(stats, dev), init, U, hidden, layers, window,
                                            stateful, carry if stateful else None, nblob, ncfg, eps, int(seed),
                                            int(traj_offset), cref, cw, bool(return_states), cost is not None,
                                            list(tune), prec, self._blob_tc(dev) if prec else None,
-                                           ctrl, ctrl_seed, n_samples, bool(shared_init))
+                                           ctrl, ctrl_seed, n_samples, bool(shared_init),
+                                           out[0] if out is not None else None, out[1] if out is not None else None)
         out = (states if return_states else None, costs if cost is not None else None)
         return out + (carry,) if stateful else out
 

@@ -82,21 +82,25 @@ class HostPipeline:
 
     A planner that keeps its control samples in host memory pays H2D(init, U) + kernel + D2H(result) per call;
     issued on one stream they serialise (C2: 0.42 ms per call against a 0.28 ms kernel).  The pipeline gives every
-    in-flight batch its own device input buffers and runs the three stages on three streams (copy-in, the caller's
-    current stream for the kernel, copy-out), so batch i+1 is uploaded and batch i-1 downloaded while batch i
-    computes.  Every batch still moves all of its bytes; only the waiting is overlapped.
+    in-flight batch its own device input AND result buffers and runs the three stages on three streams (copy-in, the
+    caller's current stream for the kernel, copy-out), so batch i+1 is uploaded and batch i-1 downloaded while batch
+    i computes.  Every batch still moves all of its bytes; only the waiting is overlapped.
 
-        pipe = HostPipeline(lambda init, U: model.rollout(init, U, stats)[0], depth=2)
+        pipe = HostPipeline(lambda init, U, out: model.rollout(init, U, stats, out=(out, None))[0], depth=2)
         pipe.submit((init_pinned, U_pinned), out_pinned)      # returns at once
         pipe.drain()                                          # current stream (and host, if sync=True) waits
 
-    ``fn(*device_inputs) -> Tensor`` runs on the current stream; host tensors must be pinned for real overlap."""
+    ``fn(*device_inputs, out) -> Tensor`` runs on the current stream and writes its result into ``out`` (a device
+    tensor shaped like the host result, owned by the pipeline slot: nothing is allocated per batch -- with results
+    from the caching allocator and ``record_stream`` the first batches of a run each paid a cudaMalloc, which is what
+    made the round-1 figure swing 0.29 .. 0.89 ms from box to box).  Host tensors must be pinned for real overlap."""
 
     def __init__(self, fn, depth: int = 2, device=None):
         self.fn, self.depth = fn, max(1, int(depth))
         self.dev = torch.device(device if device is not None else ("cuda", torch.cuda.current_device()))
         self.s_in, self.s_out = torch.cuda.Stream(self.dev), torch.cuda.Stream(self.dev)
-        self.slots = [dict(bufs=None, used=None, done=None) for _ in range(self.depth)]
+        self.slots = [dict(bufs=None, res=None, ready=torch.cuda.Event(), used=torch.cuda.Event(), done=torch.cuda.Event(),
+                           fresh=True) for _ in range(self.depth)]
         self.k = 0
 
     def submit(self, host_inputs, host_out):
@@ -105,27 +109,25 @@ class HostPipeline:
         cur = torch.cuda.current_stream(self.dev)
         if slot["bufs"] is None or any(b.shape != h.shape for b, h in zip(slot["bufs"], host_inputs)):
             slot["bufs"] = [torch.empty(h.shape, dtype=h.dtype, device=self.dev) for h in host_inputs]
-        if slot["used"] is not None:
-            self.s_in.wait_event(slot["used"])          # the kernel that last read these buffers has finished
-        else:
+        if slot["res"] is None or slot["res"].shape != host_out.shape:
+            slot["res"] = torch.empty(host_out.shape, dtype=host_out.dtype, device=self.dev)
+        if slot["fresh"]:
             self.s_in.wait_stream(cur)
+        else:
+            self.s_in.wait_event(slot["used"])          # the kernel that last read these input buffers has finished
+            cur.wait_event(slot["done"])                # ... and the last copy-out of this slot's result buffer
         with torch.cuda.stream(self.s_in):
             for b, h in zip(slot["bufs"], host_inputs):
                 b.copy_(h, non_blocking=True)
-            ready = torch.cuda.Event()
-            ready.record(self.s_in)
-        cur.wait_event(ready)
-        res = self.fn(*slot["bufs"])
-        slot["used"] = torch.cuda.Event()
+            slot["ready"].record(self.s_in)
+        cur.wait_event(slot["ready"])
+        res = self.fn(*slot["bufs"], slot["res"])
         slot["used"].record(cur)
-        if slot["done"] is not None:
-            self.s_out.wait_event(slot["done"])
         self.s_out.wait_event(slot["used"])
-        res.record_stream(self.s_out)
         with torch.cuda.stream(self.s_out):
             host_out.copy_(res, non_blocking=True)
-            slot["done"] = torch.cuda.Event()
             slot["done"].record(self.s_out)
+        slot["fresh"] = False
         return res
 
     def drain(self, sync: bool = False):

@@ -193,7 +193,7 @@ def test_host_pipeline_matches_synchronous_calls(gold_stats):
     rows = synth.load_rows()
     batches = [synth.make_inputs(rows, 1000, 20, window=0, seed=s) for s in range(5)]
     outs = [torch.empty(1000, 20, 6).pin_memory() for _ in batches]
-    pipe = parallel.HostPipeline(lambda a, b: m.rollout(a, b, st)[0], depth=2, device=_dev())
+    pipe = parallel.HostPipeline(lambda a, b, out: m.rollout(a, b, st, out=(out, None))[0], depth=2, device=_dev())
     for (init, U), o in zip(batches, outs):
         pipe.submit((init.pin_memory(), U.pin_memory()), o)
     pipe.drain(sync=True)

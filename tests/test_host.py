@@ -322,3 +322,33 @@ def test_pack_lstm256_bf16_layout():
                 assert np.array_equal(w16[p:p + want.size], want), (l, c, "h", s)
                 p += want.size
     assert p == w16.size
+
+
+def test_cost_and_norm_caches_follow_content():
+    """Round-1 advisor finding: the cost / statistics caches keyed on id() / data_ptr, so a helper that rebuilt
+    `qw = [w] * 6` on every call (the id is reused after the list is freed) got the FIRST call's weights forever.
+    Non-tensor inputs are no longer cached; tensor inputs are cached by object identity + version with the cache
+    holding the tensors, so a freed-and-reallocated tensor at the same address cannot alias an entry."""
+    import mpcdl
+    m = mpcdl.Basic_Model(8, 16, 6, 1, False)
+    cpu = torch.device("cpu")
+    ref = torch.zeros(3, 6)
+    for w in (1.0, 2.0, 3.0, 4.0):
+        qw, rw = [w] * 6, [w / 2] * 2                      # fresh temporaries on every call
+        assert m._cost((ref, qw, rw), cpu)[1] == [w] * 6 + [w / 2] * 2
+    for w in (1.0, 2.0, 3.0):                              # tensors that die between calls (storage may be recycled)
+        got = m._cost((ref, torch.full((6,), w), torch.full((2,), w)), cpu)[1]
+        assert got == [w] * 8
+    qw, rw = torch.ones(6), torch.ones(2)                  # in-place edits move the version counter
+    assert m._cost((ref, qw, rw), cpu)[1] == [1.0] * 8
+    qw.mul_(5.0)
+    assert m._cost((ref, qw, rw), cpu)[1] == [5.0] * 6 + [1.0] * 2
+    st = {k: torch.ones(8 if k[0] == "f" else 6) for k in ("f_mean", "f_std", "l_mean", "l_std")}
+    a = m._norm(st, cpu)
+    assert m._norm(st, cpu) is a                           # same tensors, unchanged -> cached
+    st["f_std"].add_(1.0)
+    b = m._norm(st, cpu)
+    assert b is not a and float(b[8]) == 2.0
+    for v in (1.0, 2.0):                                   # numpy statistics are converted on every call
+        stn = {k: np.full(8 if k[0] == "f" else 6, v, dtype=np.float32) for k in st}
+        assert float(m._norm(stn, cpu)[0]) == v

@@ -21,7 +21,7 @@ def t(fn, n=3000):
 print(f"rollout(states)            : {t(lambda: m.rollout(idv, Ud, st)):.1f} us per call (host)")
 print(f"rollout(states + cost)     : {t(lambda: m.rollout(idv, Ud, st, cost=cost)):.1f} us per call (host)")
 res = torch.empty(128, 2, 6).pin_memory()
-pipe = parallel.HostPipeline(lambda a, b: m.rollout(a, b, st, cost=cost)[0], depth=2, device=dev)
+pipe = parallel.HostPipeline(lambda a, b, out: m.rollout(a, b, st, cost=cost, out=(out, None))[0], depth=2, device=dev)
 print(f"HostPipeline.submit        : {t(lambda: pipe.submit((ip, Up), res)):.1f} us per call (host)")
 pipe.drain()
 e = torch.empty(1 << 10, device=dev)
