@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MPCDL_VERSION 104
+#define MPCDL_VERSION 105
 
 enum { MPCDL_MLP = 0, MPCDL_GRU = 1, MPCDL_LSTM = 2 };
 /* Arithmetic of the gate GEMMs.  FP32 = FFMA kernels (the parity path, <= 1e-5 one-step).  The tensor-core
@@ -122,6 +122,12 @@ typedef struct {
      * sequences in BF16 operand layout); borrowed for the duration of the launch, contents undefined afterwards. */
     void* scratch;
     uint64_t scratch_bytes;
+    /* Stacked models (validation sweep over several checkpoints of one architecture, model_scripts/eval_models.py:14-65
+     * run as ONE launch): n_models > 1 -> wblob holds n_models packed blobs back to back (mpcdl_blob_floats each), the
+     * N = n_models * (N / n_models) trajectories are model-major (model m owns [m*N/n_models, (m+1)*N/n_models)) and so
+     * are states / costs / eps.  share_inputs != 0 -> init and U hold ONE set of N / n_models trajectories that every
+     * model rolls out.  FP32 precision only, stateless, no MPPI sampling; 0 and 1 both mean a single model. */
+    int32_t n_models, share_inputs;
 } mpcdl_rollout_args;
 
 /* The fused closed loop.  Replaces, batched over N trajectories and H steps in ONE launch:
@@ -197,6 +203,60 @@ int mpcdl_mppi_reduce(const mpcdl_mppi_args* args, void* stream);
 /* Per-sample error metrics of eval_models.calc_error (model_scripts/eval_models.py:91-92):
  * mae[n] = mean_d |output[n,d] - labels[n,d]|, rmse[n] = sqrt(mean_d (output - labels)^2), d < 6; all device, FP32. */
 int mpcdl_error_metrics(const float* output, const float* labels, int64_t B, float* mae, float* rmse, void* stream);
+
+/* ---- Data side of the path on the device --------------------------------------------------
+ * A dataset is described by the recorded rows of all bags concatenated (FP32: the pickle's doubles rounded to nearest,
+ * as torch.tensor(list) does) and, per bag, its first row and its first sample; windows never cross a bag boundary.
+ *   window = 0 : basic_model.RobotData  (model_scripts/basic_model.py:13-26)   sample i of a bag = (row i, label row i+1);
+ *                                        n_b = len_b - 1
+ *   window = T : deep_models.RobotData  (model_scripts/deep_models.py:13-27)   sample i = (rows i..i+T-1, label row i+T);
+ *                                        n_b = len_b - T - 1 */
+typedef struct {
+    const float* rows;            /* device [R,8]                                   */
+    const int64_t* bag_row_off;   /* device [n_bags] first row of every bag         */
+    const int64_t* samp_off;      /* device [n_bags] first sample of every bag      */
+    int32_t n_bags, window;
+    int64_t n;                    /* samples in total                               */
+} mpcdl_dataset_desc;
+
+/* RobotData.norm statistics (basic_model.py:28-32, deep_models.py:29-33): mean and UNBIASED std over the samples, per
+ * window position, written in the layout of mpcdl_rollout_args.norm: f_mean[T*8] f_std[T*8] l_mean[6] l_std[6]
+ * (T = max(window,1)); device, FP32.  Two passes in double precision; <= 1e-6 relative to torch.mean / torch.std. */
+int mpcdl_dataset_stats(const mpcdl_dataset_desc* d, float* stats, void* stream);
+/* featrs [n,T,8] (window = 0: [n,8]) and labels [n,6], device.  stats = NULL -> raw values, else the z-score
+ * (x - mean) / std of RobotData.norm (basic_model.py:34-35, deep_models.py:35-36: subtract THEN divide). */
+int mpcdl_dataset_build(const mpcdl_dataset_desc* d, const float* stats, float* featrs, float* labels, void* stream);
+/* Open-loop evaluation inputs cut from the recorded rows, for samples that leave H recorded frames ahead (the caller
+ * sizes samp_off for that: n_b = len_b - H (window 0) / len_b - T - H + 1): init [n,6] or [n,T,8], the recorded controls
+ * U [n,H,2] and (optional) the recorded states target [n,H,6] the predictions are compared with. */
+int mpcdl_rollout_inputs(const mpcdl_dataset_desc* d, int32_t H, float* init, float* U, float* target, void* stream);
+/* Error curves of an open-loop validation sweep: pred [n_models,n,H,6] raw predicted states, target [n,H,6],
+ * lstat = l_mean[6] l_std[6]; mae / rmse [n_models,H] = mean over the n trajectories of eval_models.calc_error's
+ * per-sample metrics (model_scripts/eval_models.py:91-92) on label-normalised values, one value per horizon step. */
+int mpcdl_curve_metrics(const float* pred, const float* target, const float* lstat, int32_t n_models, int64_t n, int32_t H,
+                        float* mae, float* rmse, void* stream);
+
+/* DynamicsDataset resampling (utils/data_utils.py:21-37 and :52-72), float64 like numpy, bit-exact:
+ *   t_i = np.arange(t[0], t[-1], dataset_dt)[i];  x_i = np.interp(t_i, t, x) per channel;
+ *   q_out [n_q,6] = q_interp[::step]  (n_q = ceil(n_interp / step));  u_out [n_u,2] = mean of `step` consecutive
+ *   u_interp rows (n_u = n_interp / step).  t [M] ascending seconds, q [M,6], u [M,2]; all device pointers. */
+typedef struct {
+    const double* t;
+    const double* q;
+    const double* u;
+    int64_t M;
+    double dataset_dt;
+    int32_t step;
+    int64_t n_interp;
+    double* q_out;
+    double* u_out;
+} mpcdl_resample_args;
+int mpcdl_resample(const mpcdl_resample_args* args, void* stream);
+
+/* Test aid: fills the shared memory of every SM with NaN patterns (one CTA per SM, maximum dynamic shared memory), so a
+ * kernel that reads shared memory it has not written shows up as NaN / changed bits in the determinism tests
+ * (compute-sanitizer is not available on the GPU pool). */
+int mpcdl_debug_poison_smem(void* stream);
 
 /* FP32 FFMA peak micro-kernel (register-only FMA chains on every SM); used by bench.py to measure
  * the FP32 roofline denominator on the box it runs on.  out: device buffer of >= grid*256 floats.

@@ -144,6 +144,18 @@ void fill_io(IoParams& io, const mpcdl_rollout_args& a, int ntiles) {
     io.N = a.N; io.H = a.H; io.ntiles = ntiles;
     io.sample = a.sample_controls != 0; io.init_mul = a.shared_init ? 0 : 1; io.ctrl_seed = a.ctrl_seed;
     for (int i = 0; i < 2; ++i) { io.sig[i] = a.ctrl_sigma[i]; io.ulo[i] = a.ctrl_lo[i]; io.uhi[i] = a.ctrl_hi[i]; }
+    io.npm = a.N; io.tpm = ntiles > 0 ? ntiles : 1; io.share_inputs = 0;      // single model; set_stacking() overrides
+}
+
+int n_models_of(const mpcdl_rollout_args& a) { return a.n_models > 1 ? a.n_models : 1; }
+// stacked models: model-major trajectories, tiles never straddle two models
+void set_stacking(RolloutParams& p, const mpcdl_rollout_args& a, int TN, uint32_t blob_floats) {
+    const int nm = n_models_of(a);
+    p.io.npm = a.N / nm;
+    p.io.tpm = (int)((p.io.npm + TN - 1) / TN);
+    p.io.ntiles = nm * p.io.tpm;
+    p.io.share_inputs = nm > 1 && a.share_inputs;
+    p.m.blob_stride = nm > 1 ? blob_floats : 0u;
 }
 
 void fill_noise(NoiseParams& nz, const mpcdl_rollout_args& a) {
@@ -269,7 +281,7 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
     int width_max = 0, bias_max = 0;
     for (int i = 0; i < nparts; ++i) { width_max = std::max<int>(width_max, parts[i].width); bias_max = std::max<int>(bias_max, parts[i].bias_floats); }
 
-    if (!rnn && !a.noise_wblob && !a.tune_nslots && a.tune_kc >= 0 && d.hidden <= 64) {
+    if (!rnn && !a.noise_wblob && !a.tune_nslots && a.tune_kc >= 0 && d.hidden <= 64 && n_models_of(a) == 1) {
         double best2 = 1e300;
         bool found2 = false;
         for (const Mlp2Cand& c : kMlp2) {
@@ -313,7 +325,7 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
             pl.variant = 0; pl.ks = 1;
             pl.rt = rt; pl.rj = rj; pl.n_tg = n_tg; pl.TN = n_tg * rt;
             pl.nct = (n_tg * n_jg + 31) / 32 * 32;
-            pl.resident = (!a.tune_nslots && total <= 24576u) ? 1 : 0;
+            pl.resident = (!a.tune_nslots && total <= 24576u && n_models_of(a) == 1) ? 1 : 0;   // stacked models stream their own blob per tile
             int kc_rows = a.tune_kc > 0 ? a.tune_kc : std::max(1, 4096 / width_max);
             pl.slot_floats = std::max(kc_rows * width_max, bias_max);
             pl.nslots = pl.resident ? 1 : (a.tune_nslots ? a.tune_nslots : 3);
@@ -325,7 +337,7 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
             SmemLayout L = make_layout(m, nz, rnn);
             pl.smem_bytes = L.total * 4;
             if (pl.smem_bytes > SMEM_LIMIT) continue;
-            pl.ntiles = (int)((a.N + pl.TN - 1) / pl.TN);
+            pl.ntiles = n_models_of(a) * (int)((a.N / n_models_of(a) + pl.TN - 1) / pl.TN);
             pl.grid = std::min(pl.ntiles, num_sms);
             const int rounds = (pl.ntiles + num_sms - 1) / num_sms;
             const double instr = NGA * rt * rj * (rnn ? (double)G / NGA * 1.0 : 1.0) + (rt + 3) / 4 + (G * rj + 3) / 4;
@@ -394,6 +406,11 @@ int check_args(const mpcdl_rollout_args* a) {
         if (a->model.kind == MPCDL_MLP && a->noise_wblob)
             return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core MLP rollout has no residual-noise path; use MPCDL_PREC_FP32");
         if (!a->wblob_tc) return fail(MPCDL_ERR_ARG, "tensor-core precision needs wblob_tc (mpcdl_pack_rnn_tc)");
+    }
+    if (a->n_models > 1) {
+        if (a->precision != MPCDL_PREC_FP32 || a->stateful || a->sample_controls || a->shared_init)
+            return fail(MPCDL_ERR_UNSUPPORTED, "stacked models (n_models=%d): FP32 precision, stateless, explicit controls only", a->n_models);
+        if (a->N % a->n_models) return fail(MPCDL_ERR_ARG, "N=%lld is not a multiple of n_models=%d", (long long)a->N, a->n_models);
     }
     if (a->sample_controls && !(a->ctrl_lo[0] <= a->ctrl_hi[0] && a->ctrl_lo[1] <= a->ctrl_hi[1] && a->ctrl_sigma[0] >= 0.f && a->ctrl_sigma[1] >= 0.f))
         return fail(MPCDL_ERR_ARG, "sample_controls needs ctrl_sigma >= 0 and ctrl_lo <= ctrl_hi");
@@ -763,6 +780,7 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     fill_model(p.m, *a, pl, total);
     fill_noise(p.nz, *a);
     fill_io(p.io, *a, pl.ntiles);
+    if (pl.variant != 2) set_stacking(p, *a, pl.TN, total);
     cudaError_t e;
     if (pl.variant == 2) e = launch_mlp2(p, pl.rt, pl.rj, pl.ks, pl.grid, pl.smem_bytes, st);
     else if (a->model.kind == MPCDL_MLP) e = launch_mlp(p, pl.rt, pl.rj, pl.grid, pl.smem_bytes, st);
@@ -838,6 +856,85 @@ int mpcdl_error_metrics(const float* output, const float* labels, int64_t B, flo
     if (int drc = sm100_device(di)) return drc;
     cudaError_t e = launch_error_metrics(output, labels, B, mae, rmse, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "error_metrics launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+namespace {
+int check_dataset(const mpcdl_dataset_desc* d, DatasetParams& q) {
+    if (!d) return fail(MPCDL_ERR_ARG, "dataset desc is NULL");
+    if (!d->rows || !d->bag_row_off || !d->samp_off) return fail(MPCDL_ERR_ARG, "rows/bag_row_off/samp_off must be non-NULL device pointers");
+    if (d->n_bags < 1 || d->n < 1) return fail(MPCDL_ERR_ARG, "n_bags=%d n=%lld must be >= 1", d->n_bags, (long long)d->n);
+    if (d->window < 0 || d->window > MAX_WINDOW) return fail(MPCDL_ERR_UNSUPPORTED, "window=%d outside [0,%d]", d->window, MAX_WINDOW);
+    q.rows = d->rows; q.bag_row_off = reinterpret_cast<const long long*>(d->bag_row_off);
+    q.samp_off = reinterpret_cast<const long long*>(d->samp_off); q.n_bags = d->n_bags; q.window = d->window; q.n = d->n;
+    return MPCDL_OK;
+}
+}  // namespace
+
+int mpcdl_dataset_stats(const mpcdl_dataset_desc* d, float* stats, void* stream) {
+    DatasetParams q;
+    if (int rc = check_dataset(d, q)) return rc;
+    if (!stats) return fail(MPCDL_ERR_ARG, "stats is NULL");
+    if (d->n < 2) return fail(MPCDL_ERR_ARG, "the unbiased std needs at least 2 samples, got %lld", (long long)d->n);
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    cudaError_t e = launch_dataset_stats(q, stats, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "dataset_stats launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+int mpcdl_dataset_build(const mpcdl_dataset_desc* d, const float* stats, float* featrs, float* labels, void* stream) {
+    DatasetParams q;
+    if (int rc = check_dataset(d, q)) return rc;
+    if (!featrs || !labels) return fail(MPCDL_ERR_ARG, "featrs/labels must be non-NULL device pointers");
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    cudaError_t e = launch_dataset_build(q, stats, featrs, labels, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "dataset_build launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+int mpcdl_rollout_inputs(const mpcdl_dataset_desc* d, int32_t H, float* init, float* U, float* target, void* stream) {
+    DatasetParams q;
+    if (int rc = check_dataset(d, q)) return rc;
+    if (!init || !U || H < 1) return fail(MPCDL_ERR_ARG, "init/U must be non-NULL device pointers and H=%d >= 1", H);
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    cudaError_t e = launch_rollout_inputs(q, H, init, U, target, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "rollout_inputs launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+int mpcdl_curve_metrics(const float* pred, const float* target, const float* lstat, int32_t n_models, int64_t n, int32_t H,
+                        float* mae, float* rmse, void* stream) {
+    if (!pred || !target || !lstat || !mae || !rmse || n_models < 1 || n < 1 || H < 1) return fail(MPCDL_ERR_ARG, "mpcdl_curve_metrics: bad arguments");
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    cudaError_t e = launch_curve_metrics(pred, target, lstat, n_models, n, H, mae, rmse, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "curve_metrics launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+int mpcdl_resample(const mpcdl_resample_args* a, void* stream) {
+    if (!a) return fail(MPCDL_ERR_ARG, "args is NULL");
+    if (!a->t || !a->q || !a->u || !a->q_out || !a->u_out) return fail(MPCDL_ERR_ARG, "t/q/u/q_out/u_out must be non-NULL device pointers");
+    if (a->M < 1 || a->step < 1 || a->n_interp < 0 || !(a->dataset_dt > 0.0)) return fail(MPCDL_ERR_ARG, "mpcdl_resample: M=%lld step=%d n_interp=%lld dt=%g", (long long)a->M, a->step, (long long)a->n_interp, a->dataset_dt);
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    ResampleParams p;
+    p.t = a->t; p.q = a->q; p.u = a->u; p.M = a->M; p.dt = a->dataset_dt; p.step = a->step;
+    p.n_q = (a->n_interp + a->step - 1) / a->step; p.n_u = a->n_interp / a->step;
+    p.q_out = a->q_out; p.u_out = a->u_out;
+    cudaError_t e = launch_resample(p, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "resample launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+int mpcdl_debug_poison_smem(void* stream) {
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    cudaError_t e = launch_poison_smem(di->sms, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "poison_smem launch failed: %s", cudaGetErrorString(e));
     return MPCDL_OK;
 }
 

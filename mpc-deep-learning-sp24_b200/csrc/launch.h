@@ -42,6 +42,13 @@ cudaError_t launch_aux(const AuxParams& p, bool closed_loop, int grid, int smem_
 cudaError_t launch_mppi_min(const float* costs, long long N, float* workspace, float* cmin_out, cudaStream_t st);
 cudaError_t launch_mppi_reduce(const MppiParams& p, cudaStream_t st);
 cudaError_t launch_error_metrics(const float* output, const float* labels, long long B, float* mae, float* rmse, cudaStream_t st);
+cudaError_t launch_dataset_stats(const DatasetParams& d, float* stats, cudaStream_t st);
+cudaError_t launch_dataset_build(const DatasetParams& d, const float* stats, float* featrs, float* labels, cudaStream_t st);
+cudaError_t launch_rollout_inputs(const DatasetParams& d, int H, float* init, float* U, float* target, cudaStream_t st);
+cudaError_t launch_curve_metrics(const float* pred, const float* target, const float* lstat, int n_models, long long n, int H,
+                                 float* mae, float* rmse, cudaStream_t st);
+cudaError_t launch_resample(const ResampleParams& p, cudaStream_t st);
+cudaError_t launch_poison_smem(int num_sms, cudaStream_t st);
 cudaError_t launch_ffma_peak(float* out, int iters, int grid, cudaStream_t st);
 
 }  // namespace mpcdl

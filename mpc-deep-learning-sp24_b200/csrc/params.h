@@ -39,6 +39,11 @@ struct IoParams {
     int init_mul;            // 1: init is per trajectory; 0: one initial state / window shared by all trajectories
     float sig[2], ulo[2], uhi[2];
     unsigned long long ctrl_seed;
+    // stacked models (validation sweep): N = n_models * npm trajectories, model mi owns [mi*npm, (mi+1)*npm)
+    // and tiles [mi*tpm, (mi+1)*tpm); its weights are blob + mi * blob_stride.  share_inputs: every model reads the SAME
+    // npm initial states / control sequences (init [npm,..], U [npm,H,2]).  Single model: npm = N, tpm = ntiles.
+    long long npm;
+    int tpm, share_inputs;
 };
 
 struct ModelParams {
@@ -47,6 +52,7 @@ struct ModelParams {
     int nparts;
     int hid, layers, window, stateful;
     uint32_t data_off, data_floats;          // ring-streamed region of the blob
+    uint32_t blob_stride;                    // floats between the blobs of stacked models (0 = one model)
     int n_tg, TN;                            // trajectory groups / trajectories per CTA tile
     int n_cthreads;                          // consumer threads (multiple of 32); producer warp follows
     int nslots, slot_floats, resident;
@@ -88,6 +94,28 @@ struct MppiParams {
     const float* cmin;       // device [1]
     float* workspace;        // [MPPI_GRID][2H+2]
     float* sums;             // [2H+2]
+};
+
+// dataset build / statistics / evaluation inputs (dataset_kernels.cu): all bags concatenated into one row array
+struct DatasetParams {
+    const float* rows;              // [R,8]
+    const long long* bag_row_off;   // [n_bags]   first row of every bag
+    const long long* samp_off;      // [n_bags]   first sample of every bag (windows never cross a bag boundary)
+    int n_bags;
+    int window;                     // 0 = basic_model.RobotData, >= 1 = deep_models.RobotData(size)
+    long long n;                    // samples in total
+};
+// DynamicsDataset resampling (utils/data_utils.py:21-37, 52-72), float64
+struct ResampleParams {
+    const double* t;                // [M] seconds, ascending
+    const double* q;                // [M,6]
+    const double* u;                // [M,2]
+    long long M;
+    double dt;                      // DATASET_DT
+    int step;                       // int(dt // DATASET_DT)
+    long long n_q, n_u;             // outputs: q_out [n_q,6] = q_interp[::step], u_out [n_u,2] = pooled u_interp
+    double* q_out;
+    double* u_out;
 };
 
 // ------------------------------------------------------------------ shared-memory layout (float offsets)

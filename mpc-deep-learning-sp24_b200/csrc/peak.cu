@@ -36,3 +36,22 @@ cudaError_t launch_ffma_peak(float* out, int iters, int grid, cudaStream_t st) {
 }
 
 }  // namespace mpcdl
+
+// Test aid (mpcdl_debug_poison_smem): one CTA per SM claims the maximum dynamic shared memory and fills it with NaN bit
+// patterns.  Launched before a rollout in the determinism tests: a kernel that reads shared memory it has not written
+// then produces NaN / changed bits instead of silently reusing the previous launch's (usually identical) contents.
+namespace mpcdl {
+
+__global__ void __launch_bounds__(256) poison_smem_kernel() {
+    extern __shared__ volatile unsigned psm[];                  // volatile: the stores are the whole point
+    for (int i = threadIdx.x; i < SMEM_LIMIT / 4; i += blockDim.x) psm[i] = 0x7FC00000u | (unsigned)(i & 0xFFFF);
+}
+
+cudaError_t launch_poison_smem(int num_sms, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(poison_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+    if (e != cudaSuccess) return e;
+    poison_smem_kernel<<<num_sms, 256, SMEM_LIMIT, st>>>();
+    return cudaGetLastError();
+}
+
+}  // namespace mpcdl

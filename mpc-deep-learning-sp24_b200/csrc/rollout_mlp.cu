@@ -57,9 +57,11 @@ __global__ void __launch_bounds__(MLP_MAX_THREADS, 1) rollout_mlp_kernel(const _
             if (m.resident) {
                 ring_produce_resident(ring, m.data_floats);
             } else {
-                for (int it = 0; it < my_tiles; ++it)
+                for (int it = 0; it < my_tiles; ++it) {
+                    ring.blob = m.blob + (size_t)(((int)blockIdx.x + it * (int)gridDim.x) / p.io.tpm) * m.blob_stride;   // the tile's model
                     for (int t = 0; t < H; ++t)
                         for (int i = 0; i < m.nparts; ++i) ring_produce_part(ring, m.parts[i], kc_floats);
+                }
             }
         }
         return;
@@ -89,18 +91,21 @@ __global__ void __launch_bounds__(MLP_MAX_THREADS, 1) rollout_mlp_kernel(const _
 
     for (int tile = blockIdx.x; tile < p.io.ntiles; tile += gridDim.x) {
         const bool owner = tid < TN;
-        long long n = (long long)tile * TN + tid;
-        const bool valid = owner && n < p.io.N;
-        if (n >= p.io.N) n = p.io.N - 1;
+        const int mi = tile / p.io.tpm;                                  // stacked models: the tile's model (0 for one model)
+        const long long lim = (long long)(mi + 1) * p.io.npm;
+        long long n = (long long)mi * p.io.npm + (long long)(tile - mi * p.io.tpm) * TN + tid;
+        const bool valid = owner && n < lim;
+        if (n >= lim) n = lim - 1;
+        const long long n_in = p.io.share_inputs ? n - (long long)mi * p.io.npm : n;
         float s[6], cost = 0.f;
         if (owner) {
 #pragma unroll
-            for (int d = 0; d < 6; ++d) s[d] = __ldg(p.io.init + n * p.io.init_mul * 6 + d);
+            for (int d = 0; d < 6; ++d) s[d] = __ldg(p.io.init + n_in * p.io.init_mul * 6 + d);
         }
         for (int t = 0; t < H; ++t) {
             float u[2] = {0.f, 0.f};
             if (owner) {
-                float2 uu = load_control(p.io, n, t);
+                float2 uu = load_control(p.io, n_in, t);
                 u[0] = uu.x; u[1] = uu.y;
 #pragma unroll
                 for (int k = 0; k < 6; ++k) xin[k * TN + tid] = __fdiv_rn(__fsub_rn(s[k], normS[k]), normS[8 + k]);

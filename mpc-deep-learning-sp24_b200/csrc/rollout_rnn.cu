@@ -64,7 +64,8 @@ __global__ void __launch_bounds__(rnn_max_consumers(RT, RJ) + 32, 1) rollout_rnn
             if (m.resident) {
                 ring_produce_resident(ring, m.data_floats);
             } else {
-                for (int it = 0; it < my_tiles; ++it)
+                for (int it = 0; it < my_tiles; ++it) {
+                    ring.blob = m.blob + (size_t)(((int)blockIdx.x + it * (int)gridDim.x) / p.io.tpm) * m.blob_stride;   // the tile's model
                     for (int t = 0; t < H; ++t) {
                         for (int l = 0; l < NL; ++l)
                             for (int f = 0; f < T; ++f) {
@@ -73,6 +74,7 @@ __global__ void __launch_bounds__(rnn_max_consumers(RT, RJ) + 32, 1) rollout_rnn
                             }
                         ring_produce_part(ring, fc_part, kc_floats);
                     }
+                }
             }
         }
         return;
@@ -102,14 +104,17 @@ __global__ void __launch_bounds__(rnn_max_consumers(RT, RJ) + 32, 1) rollout_rnn
     const int CARRY_C = NL;                            // LSTM: c planes follow the h planes
 
     for (int tile = blockIdx.x; tile < p.io.ntiles; tile += gridDim.x) {
-        const long long tile0 = (long long)tile * TN;
+        const int mi = tile / p.io.tpm;                // stacked models: the tile's model (0 for one model)
+        const long long lim = (long long)(mi + 1) * p.io.npm;
+        const long long tile0 = (long long)mi * p.io.npm + (long long)(tile - mi * p.io.tpm) * TN;
         const bool owner = tid < TN;
         long long n = tile0 + tid;
-        const bool valid = owner && n < N;
-        if (n >= N) n = N - 1;
+        const bool valid = owner && n < lim;
+        if (n >= lim) n = lim - 1;
+        const long long n_in = p.io.share_inputs ? n - (long long)mi * p.io.npm : n;
         float cost = 0.f;
         if (owner) {                                   // initial window -> xwin[f][k][pos]
-            const float4* w4 = reinterpret_cast<const float4*>(p.io.init + n * p.io.init_mul * T * 8);
+            const float4* w4 = reinterpret_cast<const float4*>(p.io.init + n_in * p.io.init_mul * T * 8);
             for (int f = 0; f < T; ++f) {
                 float4 a = __ldg(w4 + 2 * f), b = __ldg(w4 + 2 * f + 1);
                 float* d = xwin + f * 8 * TN + tid;
@@ -128,7 +133,7 @@ __global__ void __launch_bounds__(rnn_max_consumers(RT, RJ) + 32, 1) rollout_rnn
             }
             float u[2] = {0.f, 0.f};
             if (owner) {
-                float2 uu = load_control(p.io, n, t);
+                float2 uu = load_control(p.io, n_in, t);
                 u[0] = uu.x; u[1] = uu.y;
                 if (p.nz.enabled) {                    // newest frame feeds the noise history
                     int pf = base + T - 1; if (pf >= T) pf -= T;
@@ -152,7 +157,7 @@ __global__ void __launch_bounds__(rnn_max_consumers(RT, RJ) + 32, 1) rollout_rnn
 #pragma unroll
                         for (int i = 0; i < RT; ++i) {
                             long long q = tile0 + (i / VEC) * hstride + tg * VEC + (i % VEC);
-                            if (q >= N) q = N - 1;
+                            if (q >= lim) q = lim - 1;
                             const float* ch = p.io.carry + ((long long)l * N + q) * HID + jg * RJ;
                             int pos = (i / VEC) * hstride + tg * VEC + (i % VEC);
 #pragma unroll
@@ -225,7 +230,7 @@ __global__ void __launch_bounds__(rnn_max_consumers(RT, RJ) + 32, 1) rollout_rnn
 #pragma unroll
                                 for (int i = 0; i < RT; ++i) {
                                     long long q = tile0 + (i / VEC) * hstride + tg * VEC + (i % VEC);
-                                    if (q < N) {
+                                    if (q < lim) {
                                         p.io.carry[((long long)l * N + q) * HID + j] = hnew[i];
                                         if (CELL == CELL_LSTM)
                                             p.io.carry[((long long)(CARRY_C + l) * N + q) * HID + j] = cst[i][r];

@@ -45,7 +45,7 @@ std::tuple<Tensor, Tensor> rollout(int kind, const OptTensor& wblob, const Tenso
                                    int64_t traj_offset, const OptTensor& cost_ref, at::ArrayRef<double> cost_w, bool return_states,
                                    bool return_costs, at::IntArrayRef tune, int64_t precision, const OptTensor& wblob_tc,
                                    at::ArrayRef<double> ctrl, int64_t ctrl_seed, int64_t n_samples, bool shared_init,
-                                   const OptTensor& out_states, const OptTensor& out_costs) {
+                                   const OptTensor& out_states, const OptTensor& out_costs, int64_t n_models, bool share_inputs) {
     TORCH_CHECK(U.is_cuda(), "mpcdl: U must be a CUDA tensor (no CPU fallback), got ", U.device());
     const c10::Device dev = U.device();
     const int T = kind == MPCDL_MLP ? 0 : (int)window;
@@ -59,12 +59,14 @@ std::tuple<Tensor, Tensor> rollout(int kind, const OptTensor& wblob, const Tenso
         TORCH_CHECK(U.dim() == 3 && U.size(2) == 2, "mpcdl: U must be [N,H,2], got ", U.sizes());
         N = U.size(0); H = U.size(1);
     }
+    const int64_t n_in = N;                               // trajectories the inputs hold
+    if (n_models > 1 && share_inputs) N *= n_models;      // stacked models all rolling out the same n_in trajectories
     {
         const int64_t lead = shared_init ? 0 : 1;
         const bool ok = kind == MPCDL_MLP ? (init.dim() == lead + 1 && init.size(lead) == 6)
                                           : (init.dim() == lead + 2 && init.size(lead) == T && init.size(lead + 1) == 8);
-        TORCH_CHECK(ok && (shared_init || init.size(0) == N), "mpcdl: init must be ", shared_init ? "" : "[N] + ",
-                    kind == MPCDL_MLP ? "[6]" : "[window,8]", " with N = ", N, ", got ", init.sizes());
+        TORCH_CHECK(ok && (shared_init || init.size(0) == n_in), "mpcdl: init must be ", shared_init ? "" : "[N] + ",
+                    kind == MPCDL_MLP ? "[6]" : "[window,8]", " with N = ", n_in, ", got ", init.sizes());
     }
     const int nt = T > 0 ? T : 1;
     TORCH_CHECK(norm.numel() == 2 * nt * 8 + 12, "mpcdl: norm must hold ", 2 * nt * 8 + 12, " floats (f_mean,f_std [", nt,
@@ -80,7 +82,7 @@ std::tuple<Tensor, Tensor> rollout(int kind, const OptTensor& wblob, const Tenso
                     " floats (pack_rnn(..., tensor_core=True))");
         a.wblob_tc = f32c(wblob_tc, "wblob_tc", dev);
     } else {
-        const size_t need = mpcdl_blob_floats(&a.model);
+        const size_t need = mpcdl_blob_floats(&a.model) * (size_t)(n_models > 1 ? n_models : 1);
         if (need == 0) check_status(MPCDL_ERR_UNSUPPORTED);
         TORCH_CHECK(has(wblob) && (size_t)wblob->numel() == need, "mpcdl: wblob has ", has(wblob) ? wblob->numel() : 0,
                     " floats, model needs ", need);
@@ -147,6 +149,7 @@ std::tuple<Tensor, Tensor> rollout(int kind, const OptTensor& wblob, const Tenso
         a.ctrl_seed = (uint64_t)ctrl_seed;
     }
     a.shared_init = shared_init;
+    a.n_models = (int32_t)n_models; a.share_inputs = share_inputs;
     c10::cuda::CUDAGuard guard(dev);                     // the launch goes to the tensors' device
     Tensor scratch;
     if (a.precision == MPCDL_PREC_BF16) {
@@ -167,10 +170,12 @@ std::tuple<Tensor, Tensor> rollout(int kind, const OptTensor& wblob, const Tenso
         bool stateful, const OptTensor &carry, const OptTensor &noise_wblob, at::IntArrayRef noise_cfg, const OptTensor &eps,        \
         int64_t seed, int64_t traj_offset, const OptTensor &cost_ref, at::ArrayRef<double> cost_w, bool return_states,              \
         bool return_costs, at::IntArrayRef tune, int64_t precision, const OptTensor &wblob_tc, at::ArrayRef<double> ctrl,           \
-        int64_t ctrl_seed, int64_t n_samples, bool shared_init, const OptTensor &out_states, const OptTensor &out_costs
+        int64_t ctrl_seed, int64_t n_samples, bool shared_init, const OptTensor &out_states, const OptTensor &out_costs,            \
+        int64_t n_models, bool share_inputs
 #define MPCDL_ROLLOUT_PASS                                                                                                          \
     wblob, norm, init, U, hidden, layers, window, stateful, carry, noise_wblob, noise_cfg, eps, seed, traj_offset, cost_ref, cost_w, \
-        return_states, return_costs, tune, precision, wblob_tc, ctrl, ctrl_seed, n_samples, shared_init, out_states, out_costs
+        return_states, return_costs, tune, precision, wblob_tc, ctrl, ctrl_seed, n_samples, shared_init, out_states, out_costs,      \
+        n_models, share_inputs
 
 std::tuple<Tensor, Tensor> rollout_mlp(MPCDL_ROLLOUT_ARGS) { return rollout(MPCDL_MLP, MPCDL_ROLLOUT_PASS); }
 std::tuple<Tensor, Tensor> rollout_gru(MPCDL_ROLLOUT_ARGS) { return rollout(MPCDL_GRU, MPCDL_ROLLOUT_PASS); }
@@ -289,13 +294,112 @@ Tensor mppi_reduce(const Tensor& costs, const Tensor& U, at::ArrayRef<double> ct
     return sums;
 }
 
+// ---------------------------------------------------------------------------- dataset build / statistics / evaluation inputs
+const int64_t* i64c(const Tensor& t, const char* name, const c10::Device& dev) {
+    TORCH_CHECK(t.scalar_type() == at::kLong && t.is_cuda() && t.device() == dev && t.is_contiguous(), "mpcdl: ", name,
+                " must be a contiguous int64 CUDA tensor on ", dev);
+    return static_cast<const int64_t*>(t.data_ptr());
+}
+mpcdl_dataset_desc dataset_desc(const Tensor& rows, const Tensor& bag_row_off, const Tensor& samp_off, int64_t window, int64_t n) {
+    TORCH_CHECK(rows.is_cuda(), "mpcdl: rows must be a CUDA tensor (no CPU fallback), got ", rows.device());
+    const c10::Device dev = rows.device();
+    TORCH_CHECK(rows.dim() == 2 && rows.size(1) == 8, "mpcdl: rows must be [R,8], got ", rows.sizes());
+    TORCH_CHECK(bag_row_off.dim() == 1 && bag_row_off.sizes() == samp_off.sizes() && bag_row_off.numel() >= 1,
+                "mpcdl: bag_row_off and samp_off must be [n_bags]");
+    mpcdl_dataset_desc d;
+    d.rows = f32c(rows, "rows", dev);
+    d.bag_row_off = i64c(bag_row_off, "bag_row_off", dev);
+    d.samp_off = i64c(samp_off, "samp_off", dev);
+    d.n_bags = (int32_t)bag_row_off.numel(); d.window = (int32_t)window; d.n = n;
+    return d;
+}
+
+// RobotData.norm statistics (basic_model.py:28-32, deep_models.py:29-33) in the rollout's `norm` layout
+Tensor dataset_stats(const Tensor& rows, const Tensor& bag_row_off, const Tensor& samp_off, int64_t window, int64_t n) {
+    const mpcdl_dataset_desc d = dataset_desc(rows, bag_row_off, samp_off, window, n);
+    const int64_t T = window > 0 ? window : 1;
+    Tensor stats = at::empty({2 * T * 8 + 12}, rows.options());
+    c10::cuda::CUDAGuard guard(rows.device());
+    check_status(mpcdl_dataset_stats(&d, static_cast<float*>(stats.data_ptr()), at::cuda::getCurrentCUDAStream(rows.device().index()).stream()));
+    return stats;
+}
+// RobotData.__init__ (+ norm when stats is given): featrs [n,T,8] / [n,8], labels [n,6]
+std::tuple<Tensor, Tensor> dataset_build(const Tensor& rows, const Tensor& bag_row_off, const Tensor& samp_off, int64_t window, int64_t n,
+                                         const OptTensor& stats) {
+    const mpcdl_dataset_desc d = dataset_desc(rows, bag_row_off, samp_off, window, n);
+    const c10::Device dev = rows.device();
+    const int64_t T = window > 0 ? window : 1;
+    if (has(stats)) TORCH_CHECK(stats->numel() == 2 * T * 8 + 12, "mpcdl: stats must hold ", 2 * T * 8 + 12, " floats");
+    Tensor featrs = window > 0 ? at::empty({n, T, 8}, rows.options()) : at::empty({n, 8}, rows.options());
+    Tensor labels = at::empty({n, 6}, rows.options());
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_dataset_build(&d, f32c(stats, "stats", dev), static_cast<float*>(featrs.data_ptr()), static_cast<float*>(labels.data_ptr()),
+                                     at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return {featrs, labels};
+}
+// open-loop evaluation inputs: init, recorded controls U [n,H,2], recorded states target [n,H,6]
+std::tuple<Tensor, Tensor, Tensor> rollout_inputs(const Tensor& rows, const Tensor& bag_row_off, const Tensor& samp_off, int64_t window,
+                                                  int64_t n, int64_t H) {
+    const mpcdl_dataset_desc d = dataset_desc(rows, bag_row_off, samp_off, window, n);
+    const c10::Device dev = rows.device();
+    TORCH_CHECK(H >= 1, "mpcdl: H must be >= 1");
+    Tensor init = window > 0 ? at::empty({n, window, 8}, rows.options()) : at::empty({n, 6}, rows.options());
+    Tensor U = at::empty({n, H, 2}, rows.options()), target = at::empty({n, H, 6}, rows.options());
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_rollout_inputs(&d, (int32_t)H, static_cast<float*>(init.data_ptr()), static_cast<float*>(U.data_ptr()),
+                                      static_cast<float*>(target.data_ptr()), at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return {init, U, target};
+}
+// per-step MAE / RMSE curves of stacked models: pred [M,n,H,6] (or [n,H,6]), target [n,H,6], lstat [12] -> ([M,H], [M,H])
+std::tuple<Tensor, Tensor> curve_metrics(const Tensor& pred, const Tensor& target, const Tensor& lstat) {
+    TORCH_CHECK(pred.is_cuda(), "mpcdl: pred must be a CUDA tensor (no CPU fallback), got ", pred.device());
+    const c10::Device dev = pred.device();
+    TORCH_CHECK(target.dim() == 3 && target.size(2) == 6 && (pred.dim() == 3 || pred.dim() == 4) && lstat.numel() == 12,
+                "mpcdl: curve_metrics needs pred [M,n,H,6] | [n,H,6], target [n,H,6], lstat [12]");
+    const int64_t M = pred.dim() == 4 ? pred.size(0) : 1, n = target.size(0), H = target.size(1);
+    TORCH_CHECK(pred.numel() == M * n * H * 6, "mpcdl: pred ", pred.sizes(), " does not match target ", target.sizes());
+    Tensor mae = at::empty({M, H}, pred.options()), rmse = at::empty({M, H}, pred.options());
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_curve_metrics(f32c(pred, "pred", dev), f32c(target, "target", dev), f32c(lstat, "lstat", dev), (int32_t)M, n, (int32_t)H,
+                                     static_cast<float*>(mae.data_ptr()), static_cast<float*>(rmse.data_ptr()),
+                                     at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return {mae, rmse};
+}
+// DynamicsDataset resampling (utils/data_utils.py:21-37, 52-72): float64 t [M], q [M,6], u [M,2] -> (q_ds, u_ds)
+std::tuple<Tensor, Tensor> resample(const Tensor& t, const Tensor& q, const Tensor& u, double dataset_dt, int64_t step, int64_t n_interp) {
+    TORCH_CHECK(t.is_cuda(), "mpcdl: t must be a CUDA tensor (no CPU fallback), got ", t.device());
+    const c10::Device dev = t.device();
+    for (const Tensor* x : {&t, &q, &u})
+        TORCH_CHECK(x->scalar_type() == at::kDouble && x->is_cuda() && x->device() == dev && x->is_contiguous(),
+                    "mpcdl: resample needs contiguous float64 CUDA tensors on one device");
+    const int64_t M = t.numel();
+    TORCH_CHECK(t.dim() == 1 && q.dim() == 2 && q.size(0) == M && q.size(1) == 6 && u.dim() == 2 && u.size(0) == M && u.size(1) == 2,
+                "mpcdl: resample needs t [M], q [M,6], u [M,2]");
+    TORCH_CHECK(step >= 1 && n_interp >= 0, "mpcdl: resample needs step >= 1 and n_interp >= 0");
+    mpcdl_resample_args a;
+    a.t = static_cast<const double*>(t.data_ptr()); a.q = static_cast<const double*>(q.data_ptr()); a.u = static_cast<const double*>(u.data_ptr());
+    a.M = M; a.dataset_dt = dataset_dt; a.step = (int32_t)step; a.n_interp = n_interp;
+    Tensor qo = at::empty({(n_interp + step - 1) / step, 6}, t.options()), uo = at::empty({n_interp / step, 2}, t.options());
+    a.q_out = static_cast<double*>(qo.data_ptr()); a.u_out = static_cast<double*>(uo.data_ptr());
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_resample(&a, at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return {qo, uo};
+}
+// test aid: NaN-fill the shared memory of every SM of `like`'s device (determinism tests)
+void debug_poison_smem(const Tensor& like) {
+    TORCH_CHECK(like.is_cuda(), "mpcdl: debug_poison_smem needs a CUDA tensor to name the device");
+    c10::cuda::CUDAGuard guard(like.device());
+    check_status(mpcdl_debug_poison_smem(at::cuda::getCurrentCUDAStream(like.device().index()).stream()));
+}
+
 }  // namespace
 
 #define MPCDL_ROLLOUT_SCHEMA                                                                                                          \
     "(Tensor? wblob, Tensor norm, Tensor init, Tensor U, int hidden, int layers, int window, bool stateful, Tensor(a!)? carry, "       \
     "Tensor? noise_wblob, int[] noise_cfg, Tensor? eps, int seed, int traj_offset, Tensor? cost_ref, float[] cost_w, "                \
     "bool return_states, bool return_costs, int[] tune, int precision, Tensor? wblob_tc, float[] ctrl, int ctrl_seed, "               \
-    "int n_samples, bool shared_init, Tensor(b!)? out_states, Tensor(c!)? out_costs) -> (Tensor, Tensor)"
+    "int n_samples, bool shared_init, Tensor(b!)? out_states, Tensor(c!)? out_costs, int n_models=1, bool share_inputs=False) "       \
+    "-> (Tensor, Tensor)"
 
 TORCH_LIBRARY(mpcdl, m) {
     m.def("rollout_mlp" MPCDL_ROLLOUT_SCHEMA);
@@ -307,6 +411,12 @@ TORCH_LIBRARY(mpcdl, m) {
     m.def("error_metrics(Tensor output, Tensor labels) -> (Tensor, Tensor)");
     m.def("mppi_reduce(Tensor costs, Tensor U, float[] ctrl, int ctrl_seed, int traj_offset, float lam, Tensor? cmin) -> Tensor");
     m.def("mppi_min(Tensor costs) -> Tensor");
+    m.def("dataset_stats(Tensor rows, Tensor bag_row_off, Tensor samp_off, int window, int n) -> Tensor");
+    m.def("dataset_build(Tensor rows, Tensor bag_row_off, Tensor samp_off, int window, int n, Tensor? stats) -> (Tensor, Tensor)");
+    m.def("rollout_inputs(Tensor rows, Tensor bag_row_off, Tensor samp_off, int window, int n, int H) -> (Tensor, Tensor, Tensor)");
+    m.def("curve_metrics(Tensor pred, Tensor target, Tensor lstat) -> (Tensor, Tensor)");
+    m.def("resample(Tensor t, Tensor q, Tensor u, float dataset_dt, int step, int n_interp) -> (Tensor, Tensor)");
+    m.def("debug_poison_smem(Tensor like) -> ()");
 }
 
 TORCH_LIBRARY_IMPL(mpcdl, CUDA, m) {
@@ -318,4 +428,10 @@ TORCH_LIBRARY_IMPL(mpcdl, CUDA, m) {
     m.impl("error_metrics", &error_metrics);
     m.impl("mppi_reduce", &mppi_reduce);
     m.impl("mppi_min", &mppi_min);
+    m.impl("dataset_stats", &dataset_stats);
+    m.impl("dataset_build", &dataset_build);
+    m.impl("rollout_inputs", &rollout_inputs);
+    m.impl("curve_metrics", &curve_metrics);
+    m.impl("resample", &resample);
+    m.impl("debug_poison_smem", &debug_poison_smem);
 }

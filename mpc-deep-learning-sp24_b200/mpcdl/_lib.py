@@ -58,7 +58,19 @@ class RolloutArgs(C.Structure):
         ("ctrl_seed", C.c_uint64),
         ("scratch", C.c_void_p),
         ("scratch_bytes", C.c_uint64),
+        ("n_models", C.c_int32),
+        ("share_inputs", C.c_int32),
     ]
+
+
+class DatasetDesc(C.Structure):
+    _fields_ = [("rows", C.c_void_p), ("bag_row_off", C.c_void_p), ("samp_off", C.c_void_p),
+                ("n_bags", C.c_int32), ("window", C.c_int32), ("n", C.c_int64)]
+
+
+class ResampleArgs(C.Structure):
+    _fields_ = [("t", C.c_void_p), ("q", C.c_void_p), ("u", C.c_void_p), ("M", C.c_int64), ("dataset_dt", C.c_double),
+                ("step", C.c_int32), ("n_interp", C.c_int64), ("q_out", C.c_void_p), ("u_out", C.c_void_p)]
 
 
 class MppiArgs(C.Structure):
@@ -103,7 +115,9 @@ class Plan(C.Structure):
 
 
 EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_pack_mlp_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
-           "mpcdl_rollout", "mpcdl_rollout_scratch_bytes", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version")
+           "mpcdl_rollout", "mpcdl_rollout_scratch_bytes", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version",
+           "mpcdl_dataset_stats", "mpcdl_dataset_build", "mpcdl_rollout_inputs", "mpcdl_curve_metrics", "mpcdl_resample",
+           "mpcdl_debug_poison_smem")
 
 
 def _load():
@@ -147,6 +161,18 @@ def _load():
     lib.mpcdl_error_metrics.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.mpcdl_ffma_peak.restype = C.c_int
     lib.mpcdl_ffma_peak.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.mpcdl_dataset_stats.restype = C.c_int
+    lib.mpcdl_dataset_stats.argtypes = [C.POINTER(DatasetDesc), C.c_void_p, C.c_void_p]
+    lib.mpcdl_dataset_build.restype = C.c_int
+    lib.mpcdl_dataset_build.argtypes = [C.POINTER(DatasetDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.mpcdl_rollout_inputs.restype = C.c_int
+    lib.mpcdl_rollout_inputs.argtypes = [C.POINTER(DatasetDesc), C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.mpcdl_curve_metrics.restype = C.c_int
+    lib.mpcdl_curve_metrics.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.mpcdl_resample.restype = C.c_int
+    lib.mpcdl_resample.argtypes = [C.POINTER(ResampleArgs), C.c_void_p]
+    lib.mpcdl_debug_poison_smem.restype = C.c_int
+    lib.mpcdl_debug_poison_smem.argtypes = [C.c_void_p]
     lib.mpcdl_last_error.restype = C.c_char_p
     lib.mpcdl_version.restype = C.c_int
     return lib

@@ -115,6 +115,92 @@ def calc_error(dataset, model, file, state_f=False):
     return diff / epochs, rm / epochs
 
 
+# ------------------------------------------------------------------------------------------------ validation sweep (f2)
+def _sweep_checkpoints(model_dirs):
+    """{name: state_dict} of every checkpoint under the given directories (default: the reference's two, :18 / :41)."""
+    out = {}
+    for d in model_dirs:
+        d2, files = _files(d, os.path.basename(d))
+        for f in files:
+            out[f.rsplit(".", 1)[0]] = _load_state(os.path.join(d2, f))
+    return out
+
+
+def _pad_mlp_state(sd, hidden, layers, to_layers):
+    """Basic_Model state_dict with `layers` hidden layers -> an equivalent one with `to_layers`: the extra layers are
+    identity matrices with zero bias placed before the output layer.  Their inputs are ReLU outputs (>= 0), so
+    relu(I x + 0) = x exactly (every added FMA term is x*1 or x*0 onto 0): the padded model computes the same bits."""
+    if layers == to_layers:
+        return {k: torch.as_tensor(v) for k, v in sd.items()}
+    out = {f"layers.{i}.{p}": torch.as_tensor(sd[f"layers.{i}.{p}"]) for i in range(layers + 1) for p in ("weight", "bias")}
+    for i in range(layers + 1, to_layers + 1):
+        out[f"layers.{i}.weight"], out[f"layers.{i}.bias"] = torch.eye(hidden), torch.zeros(hidden)
+    out[f"layers.{to_layers + 1}.weight"] = torch.as_tensor(sd[f"layers.{layers + 1}.weight"])
+    out[f"layers.{to_layers + 1}.bias"] = torch.as_tensor(sd[f"layers.{layers + 1}.bias"])
+    return out
+
+
+def sweep(checkpoints=None, pickles=("mpc", "pid"), horizons=(1, 10, 50), device=None, model_dirs=(FWD_DIR, RNN_DIR)):
+    """The whole validation sweep as ONE call: every checkpoint x every validation pickle x every
+    horizon.  The reference runs ``calc_error`` per checkpoint at batch 1 and only one step deep
+    (model_scripts/eval_models.py:14-96); here, per pickle and per model family (MLP hidden 16, MLP hidden 64, GRU, LSTM)
+    the checkpoints' packed weights are STACKED and one fused-rollout launch evaluates all of them on all samples:
+
+      H = 1   teacher forced: the model's prediction on every dataset sample against its label (``calc_error`` with
+              SAMPLE = False) -> (mae, rmse) in the pickle's own z-score units
+      H > 1   open loop from every stretch of the bag that leaves H recorded frames ahead, fed with the recorded
+              controls -> per-step curves (mae [H], rmse [H]) of the predicted against the recorded states, same metric
+
+    checkpoints: {name: state_dict} (names follow the file-name schema, eval_models.py:19-25 / 43-52) or None = every
+    file under `model_dirs`.  pickles: names resolved like ``basic_model.DATA`` ("mpc" -> mpc_data_clean) or a
+    {label: bags} dict.  GRU / LSTM checkpoints are evaluated stateless, as ``calc_error`` does (init_hidden before
+    every sample, :81-82).  Dataset build, statistics, evaluation inputs, rollout and metrics all run on the GPU.
+    Returns {pickle: {name: {H: (mae, rmse)}}} with numpy values."""
+    from . import _lib, data, ops, pack, synth
+    dev = torch.device(device if device is not None else "cuda")
+    ckpts = checkpoints if checkpoints is not None else _sweep_checkpoints(model_dirs)
+    if not isinstance(pickles, dict):
+        pickles = {p: synth.load_bags(f"{p}_data_clean") for p in pickles}
+    groups = {}                                                        # (kind, hidden, window) -> [(name, layers, sd)]
+    for name, sd in ckpts.items():
+        p = name.split("_")
+        kind = {"Basic": _lib.MLP, "GRU": _lib.GRU, "LSTM": _lib.LSTM}[p[0]]
+        groups.setdefault((kind, int(p[1]), 0 if kind == _lib.MLP else int(p[3])), []).append((name, int(p[2]), sd))
+    out = {}
+    for label, bags in pickles.items():
+        db = data.DeviceBags(bags, dev)
+        res = out.setdefault(label, {})
+        for (kind, hidden, window), members in groups.items():
+            lay = max(m[1] for m in members) if kind == _lib.MLP else members[0][1]
+            if kind != _lib.MLP and any(m[1] != lay for m in members):
+                raise RuntimeError("mpcdl: stacked GRU / LSTM checkpoints must share the layer count")
+            blobs = [pack.pack_mlp(_pad_mlp_state(sd, hidden, L, lay), hidden, lay) if kind == _lib.MLP
+                     else pack.pack_rnn({k: torch.as_tensor(v) for k, v in sd.items()}, kind, hidden, lay, window) for _, L, sd in members]
+            wblob = torch.cat(blobs).to(dev)
+            M = len(members)
+            featrs, labels, svec = data.device_dataset(db, window or None, dev)
+            ident = pack.identity_norm(window).to(dev)
+
+            def launch(norm, init, U):
+                return ops.OPS[kind](wblob, norm, init, U, hidden, lay, window, False, None, None, [], None, 0, 0, None, [],
+                                     True, False, [], 0, None, [], 0, 0, False, None, None, M, True)[0]
+            for H in horizons:
+                if H == 1:
+                    if kind == _lib.MLP:
+                        init, U = featrs[:, :6].contiguous(), featrs[:, None, 6:8].contiguous()
+                    else:
+                        init, U = featrs, torch.zeros(featrs.shape[0], 1, 2, device=dev)
+                    pred, target, lstat, norm = launch(ident, init, U), labels[:, None, :].contiguous(), ident[-12:], None
+                else:
+                    init, U, target = data.open_loop_inputs(db, H, window or None, dev)
+                    pred, lstat = launch(svec, init, U), svec[-12:]
+                mae, rmse = torch.ops.mpcdl.curve_metrics(pred.view(M, -1, H, 6), target, lstat.contiguous())
+                mae, rmse = mae.cpu().numpy(), rmse.cpu().numpy()
+                for i, (name, _, _) in enumerate(members):
+                    res.setdefault(name, {})[H] = (float(mae[i, 0]), float(rmse[i, 0])) if H == 1 else (mae[i], rmse[i])
+    return out
+
+
 params = {"x_pos": [], "y_pos": [], "v_long": [], "v_tran": []}
 result = {"x_pos": [], "y_pos": [], "v_long": [], "v_tran": []}
 

@@ -469,3 +469,23 @@ def from_checkpoint_name(name, sd=None, device=None):
     if device is not None:
         m.to(device)
     return m, meta
+
+
+def load_model(path, device=None):
+    """Checkpoint file -> (module, meta): the file name is the config (eval_models.py:19-25, 43-52), the state_dict loads
+    unchanged (``.pt`` via torch.load as eval_models.py:28 does, or the ``.npz`` export), and the z-score statistics
+    persisted beside it by ``mpcdl.data.save_stats(mpcdl.data.stats_path(path), stats)`` -- the reference computes them
+    at import and throws them away -- are attached as ``module.stats`` (None if there is no such file)."""
+    import os
+
+    import numpy as np
+
+    from . import data
+    if path.endswith(".npz"):
+        sd = {k: torch.from_numpy(v) for k, v in np.load(path).items()}
+    else:
+        sd = torch.load(path, map_location="cpu")
+    m, meta = from_checkpoint_name(os.path.basename(path), sd, device)
+    sp = data.stats_path(path)
+    m.stats = data.load_stats(sp) if os.path.exists(sp) else None
+    return m, meta

@@ -367,6 +367,111 @@ to, co, _ = R.rollout_rnn(g, rst, win0, Uw, noise=my_noise, eps=eps, cost=cost)
 gold["GRU_64_4_4_16_False_noise"], gold["GRU_64_4_4_16_False_noise_cost"] = to.numpy(), co.numpy()
 np.savez_compressed(f"{GOLD}/rollouts.npz", **gold)
 
+# ---------------------------------------------------------------------------- 5. DynamicsDataset (f3)
+from collections import OrderedDict  # noqa: E402
+
+from oracle import dataset_ref as D  # noqa: E402
+
+rows_np = np.asarray(bags[0], dtype=np.float64)
+rng = np.random.default_rng(0)
+Md = 900
+ts_ns = (1_700_000_000_000_000_000 + np.cumsum(rng.integers(15_000_000, 26_000_000, Md))).astype(np.int64)   # 15..26 ms apart
+raw = OrderedDict()
+for k in range(Md):
+    r = rows_np[k]
+    ua, us_ = float(r[6]), float(r[7])
+    if k % 97 == 5:
+        ua, us_ = 1.0, 0.0          # "manual control" marker, dropped by from_dict (data_utils.py:53-54)
+    if k % 101 == 7:
+        ua, us_ = 0.0, 0.0          # idle, dropped
+    raw[int(ts_ns[k])] = {"v": {"v_long": float(r[4]), "v_tran": float(r[5])}, "w": {"w_psi": float(r[3])},
+                          "x": {"x": float(r[0]), "y": float(r[1])}, "e": {"psi": float(r[2])},
+                          "u": {"u_a": ua, "u_steer": us_}}
+import utils.data_utils as du  # noqa: E402
+dyn_gold = {}
+td, qd_, ud_ = D.arrays_from_dict(raw)
+dyn_gold["t"], dyn_gold["q"], dyn_gold["u"] = td, qd_, ud_
+for dt_ in (0.1, 0.04, 0.02):
+    ref_dd = du.DynamicsDataset.from_dict(raw, dt_, history=3)
+    q_ds, u_ds = D.resample_ref(td, qd_, ud_, dt_)
+    ok = np.array_equal(ref_dd.q, q_ds) and np.array_equal(ref_dd.u, u_ds)
+    it_r, it_m = ref_dd[4], D.get_item(q_ds, u_ds, 4, 3)
+    ok = ok and all(np.array_equal(a, b) for a, b in zip(it_r, it_m)) and len(ref_dd) == q_ds.shape[0] - 3
+    check(f"f3 DynamicsDataset.from_dict dt={dt_}: oracle == reference (bit), {q_ds.shape[0]} q / {u_ds.shape[0]} u rows", ok)
+    dyn_gold[f"q_ds_{dt_}"], dyn_gold[f"u_ds_{dt_}"] = ref_dd.q, ref_dd.u
+_, qi_, ui_ = D.interp_grid(td, qd_, ud_)
+ref_dd = du.DynamicsDataset(qi_, ui_, 0.08, history=2)
+q_ds, u_ds, _ = D.subsample(qi_, ui_, 0.08)
+check("f3 DynamicsDataset.__init__ dt=0.08 on gridded arrays: oracle == reference (bit)",
+      np.array_equal(ref_dd.q, q_ds) and np.array_equal(ref_dd.u, u_ds))
+dyn_gold["q_grid"], dyn_gold["u_grid"], dyn_gold["q_ds_init_0.08"], dyn_gold["u_ds_init_0.08"] = qi_, ui_, ref_dd.q, ref_dd.u
+np.savez_compressed(f"{GOLD}/dynamics.npz", **dyn_gold)
+
+# ---------------------------------------------------------------------------- 6. second validation pickle + the sweep (f2)
+pid_bags = synth.load_bags("pid_data_clean")
+pid = {}
+ref_pds, ref_prds = fwd.RobotData(pid_bags), rnn.RobotData(pid_bags, 4)
+pf, pl_ = R.mlp_dataset(pid_bags)
+pst = R.zscore_stats(pf, pl_)
+pfn, pln = R.apply_zscore(pf, pl_, pst)
+check("a1 pid pickle: MLP dataset+zscore bit-identical", bit_equal(pfn, ref_pds.featrs.cpu()) and bit_equal(pln, ref_pds.labels.cpu()))
+prf, prl = R.rnn_dataset(pid_bags, 4)
+prst = R.zscore_stats(prf, prl)
+prfn, prln = R.apply_zscore(prf, prl, prst)
+check("a3 pid pickle: RNN dataset+zscore bit-identical (T=4)", bit_equal(prfn, ref_prds.featrs.cpu()) and bit_equal(prln, ref_prds.labels.cpu()))
+for k, v in pst.items():
+    pid[f"mlp_{k}"] = v.numpy()
+for k, v in prst.items():
+    pid[f"rnn4_{k}"] = v.numpy()
+
+
+def ref_module(name):
+    p = name.split("_")
+    if p[0] == "Basic":
+        m = fwd.Basic_Model(8, int(p[1]), 6, int(p[2]), False).cpu()
+        m.load_state_dict(torch.load(f"{REF}/model_data/fwd_models/{name}.pt", map_location="cpu"))
+    else:
+        m = (rnn.GRU_Model if p[0] == "GRU" else rnn.LSTM_Model)(8, int(p[1]), 6, int(p[2]), False).cpu()   # evaluated stateless (eval_models.py:81-82)
+        m.load_state_dict(torch.load(f"{REF}/model_data/rnn_models/{name}.pt", map_location="cpu"))
+    return m.eval()
+
+
+sweep = {}
+HS = (1, 10, 50)
+for pk, pbags, (sm_, sr_), (fm_, lm_), (fr_, lr_) in (("mpc", bags, (mst, rst), (mfn, mln), (rfn, rln)),
+                                                     ("pid", pid_bags, (pst, prst), (pfn, pln), (prfn, prln))):
+    rows32_p = torch.as_tensor(pbags[0], dtype=torch.float64).to(torch.float32)
+    for name in names_fwd + names_rnn:
+        mlp = name.startswith("Basic")
+        ref_m = ref_module(name)
+        mine, meta = R.build_from_name(name, ckpt(name))
+        st_ = sm_ if mlp else sr_
+        got = R.sweep_model(mine, meta, pbags, HS)
+        ok = True
+        with torch.no_grad():
+            if mlp:
+                y1 = ref_m(fm_)
+                lab = lm_
+            else:
+                ref_m.h_state = None
+                y1 = ref_m(fr_)
+                lab = lr_
+            if pk == "pid":
+                pid[name] = y1.numpy()
+            e1 = R.calc_error(y1, lab)
+            ok = ok and e1 == got[1]
+            sweep[f"{pk}/{name}/H1"] = np.asarray(e1)
+            for H_ in HS[1:]:
+                init_, U_, tgt_ = R.open_loop_inputs(rows32_p, H_, 0 if mlp else 4)
+                tr = ref_loop_mlp(ref_m, st_, init_, U_) if mlp else ref_loop_rnn(ref_m, st_, init_, U_)
+                mae_c, rmse_c = R.error_curves(tr, tgt_, st_)
+                ok = ok and torch.equal(mae_c, got[H_][0]) and torch.equal(rmse_c, got[H_][1])
+                sweep[f"{pk}/{name}/H{H_}_mae"], sweep[f"{pk}/{name}/H{H_}_rmse"] = mae_c.numpy(), rmse_c.numpy()
+        check(f"f2 sweep {pk} {name}: oracle curves == reference modules in the python loop (bit), H1 mae {e1[0]:.4f}, "
+              f"H50 mae[-1] {float(sweep[f'{pk}/{name}/H50_mae'][-1]):.3f}", ok)
+np.savez_compressed(f"{GOLD}/pid.npz", **pid)
+np.savez_compressed(f"{GOLD}/sweep.npz", **sweep)
+
 bad = [n for n, ok in checks if not ok]
 print(f"{len(checks) - len(bad)}/{len(checks)} checks passed")
 print("PINNED" if not bad else "NOT PINNED: " + "; ".join(bad))

@@ -297,6 +297,55 @@ def calc_error_sampled(outputs, labels, epochs, rng):
 
 
 # --------------------------------------------------------------------------------------
+# f2  validation sweep: teacher-forced one-step + open-loop error curves    eval_models.py:14-96
+# --------------------------------------------------------------------------------------
+def open_loop_inputs(rows32, H, window):
+    """Start states / windows, recorded controls and recorded states of every stretch of ONE bag that leaves H
+    recorded frames ahead (DESIGN.md "Rollout semantics"):
+      MLP (window 0): s0 = row i [:6], U[i,t] = row i+t [6:8], target[i,t] = row i+t+1 [:6]          n = len - H
+      RNN (window T): win0 = rows i..i+T-1, U[i,t] = row i+T+t [6:8], target[i,t] = row i+T+t [:6]    n = len - T - H + 1"""
+    L = rows32.shape[0]
+    if window == 0:
+        n = L - H
+        i = torch.arange(n)[:, None] + torch.arange(H)[None, :]
+        return rows32[:n, :6].contiguous(), rows32[i][:, :, 6:8].contiguous(), rows32[i + 1][:, :, :6].contiguous()
+    n = L - window - H + 1
+    w = torch.arange(n)[:, None] + torch.arange(window)[None, :]
+    i = torch.arange(n)[:, None] + window + torch.arange(H)[None, :]
+    return rows32[w].contiguous(), rows32[i][:, :, 6:8].contiguous(), rows32[i][:, :, :6].contiguous()
+
+
+@torch.no_grad()
+def error_curves(pred, target, st):
+    """calc_error's per-sample metrics (eval_models.py:91-92) on label-normalised values, per horizon step, averaged
+    over the trajectories: pred / target [n,H,6] raw states -> (mae [H], rmse [H])."""
+    d = (pred - st["l_mean"]) / st["l_std"] - (target - st["l_mean"]) / st["l_std"]
+    return d.abs().mean(dim=-1).double().mean(dim=0), d.pow(2).mean(dim=-1).sqrt().double().mean(dim=0)
+
+
+@torch.no_grad()
+def sweep_model(model, meta, bags, horizons=(1, 10, 50)):
+    """One checkpoint over one validation pickle: the statistics are the pickle's own (RobotData.norm); H = 1 is the
+    teacher-forced calc_error over EVERY dataset sample (eval_models.py SAMPLE=False), H > 1 the open-loop curves.
+    -> {1: (mae, rmse), H: (mae [H], rmse [H])}"""
+    mlp = meta["kind"] == "mlp"
+    f, l = mlp_dataset(bags) if mlp else rnn_dataset(bags, meta["ft"])
+    st = zscore_stats(f, l)
+    fn, ln = apply_zscore(f, l, st)
+    out = {}
+    for H in horizons:
+        if H == 1:
+            y = model(fn) if mlp else model(fn, model.zero_state(len(fn)))[0]
+            out[1] = calc_error(y, ln)
+            continue
+        rows32 = torch.as_tensor(bags[0], dtype=torch.float64).to(torch.float32)
+        init, U, target = open_loop_inputs(rows32, H, 0 if mlp else meta["ft"])
+        pred = rollout_mlp(model, st, init, U)[0] if mlp else rollout_rnn(model, st, init, U, stateful=False)[0]
+        out[H] = error_curves(pred, target, st)
+    return out
+
+
+# --------------------------------------------------------------------------------------
 # a7 / a8  DynamicsNN closed loop            noise_model.py:113-125, scripts/test_model.py:67-87
 # --------------------------------------------------------------------------------------
 @torch.no_grad()

@@ -169,7 +169,8 @@ def test_ctypes_mirror_matches_the_compiled_header(tmp_path):
         pytest.skip("gcc not available")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     structs = {"mpcdl_rollout_args": _lib.RolloutArgs, "mpcdl_noise_args": _lib.NoiseArgs, "mpcdl_mppi_args": _lib.MppiArgs,
-               "mpcdl_plan": _lib.Plan, "mpcdl_model_desc": _lib.ModelDesc}
+               "mpcdl_plan": _lib.Plan, "mpcdl_model_desc": _lib.ModelDesc, "mpcdl_dataset_desc": _lib.DatasetDesc,
+               "mpcdl_resample_args": _lib.ResampleArgs}
     cfield = {"lam": "lambda"}                       # `lambda` is a Python keyword: the mirror calls it lam
     lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "mpcdl.h"', 'int main(void) {']
     for cname, cls in structs.items():

@@ -161,3 +161,88 @@ def test_philox_known_answers_and_mppi_update():
     assert cmin == costs.astype(np.float64).min() and wsum >= 1.0
     assert (np.abs(Un) <= np.abs(u).max(0) + 1e-7).all()
     assert (Un ** 2).sum() < np.median(costs)                         # pulled towards the cheap samples
+
+
+# ------------------------------------------------------------------------------ f2 / f3 goldens (round 2)
+def _npz(name):
+    import os
+    from conftest import GOLD
+    return np.load(os.path.join(GOLD, name))
+
+
+def test_dynamics_dataset_oracle_matches_reference_golden():
+    """oracle/dataset_ref.py against tests/golden/dynamics.npz (made by the reference's DynamicsDataset): bit-exact."""
+    from oracle import dataset_ref as D
+    g = _npz("dynamics.npz")
+    for dt in (0.1, 0.04, 0.02):
+        q, u = D.resample_ref(g["t"], g["q"], g["u"], dt)
+        assert np.array_equal(q, g[f"q_ds_{dt}"]) and np.array_equal(u, g[f"u_ds_{dt}"])
+    q, u, step = D.subsample(g["q_grid"], g["u_grid"], 0.08)
+    assert step == 4 and np.array_equal(q, g["q_ds_init_0.08"]) and np.array_equal(u, g["u_ds_init_0.08"])
+    with pytest.raises(AssertionError):          # 0.06 // 0.02 == 2.0 in floating point: the reference rejects this dt
+        D.subsample(g["q_grid"], g["u_grid"], 0.06)
+
+
+def test_dynamics_dataset_host_logic():
+    """The host side of mpcdl.data_utils.DynamicsDataset: the step rule (incl. the reference's 0.06 quirk) and the grid
+    length handed to the kernel equal numpy's."""
+    import math
+    from mpcdl import data_utils as du
+    assert du._step_of(0.1, 0.02) == 5 and du._step_of(0.08, 0.02) == 4
+    with pytest.raises(AssertionError):
+        du._step_of(0.06, 0.02)
+    rng = np.random.default_rng(1)
+    for _ in range(300):
+        t0 = float(rng.uniform(0, 2e9))
+        span = float(rng.uniform(0.01, 50))
+        n = len(np.arange(t0, t0 + span, 0.02))
+        assert n == max(int(math.ceil((t0 + span - t0) / 0.02)), 0)
+    with pytest.raises(RuntimeError):            # no CPU path for the arithmetic
+        du.DynamicsDataset(np.zeros((10, 6)), np.zeros((10, 2)), 0.1, device="cpu")
+
+
+@pytest.mark.parametrize("name", ["Basic_16_1_32", "Basic_64_4_32", "GRU_64_4_4_16_False"])
+def test_sweep_oracle_matches_golden(name):
+    """oracle sweep (teacher-forced H = 1 + open-loop curves) against tests/golden/sweep.npz, whose curves were computed
+    from the REFERENCE modules driven in the python loop (oracle/pin_reference.py section 6): bit-exact."""
+    from conftest import load_ckpt
+    from mpcdl import synth
+    g = _npz("sweep.npz")
+    m, meta = R.build_from_name(name, load_ckpt(name))
+    hs = (1, 10, 50) if name.startswith("Basic") else (1, 10)
+    for pk in ("mpc", "pid"):
+        got = R.sweep_model(m, meta, synth.load_bags(f"{pk}_data_clean"), hs)
+        assert np.array_equal(np.asarray(got[1]), g[f"{pk}/{name}/H1"])
+        for H in hs[1:]:
+            assert np.array_equal(got[H][0].numpy(), g[f"{pk}/{name}/H{H}_mae"])
+            assert np.array_equal(got[H][1].numpy(), g[f"{pk}/{name}/H{H}_rmse"])
+
+
+def test_pid_pickle_onestep_golden():
+    """second validation pickle (pid_data_clean): statistics and one-step outputs of the reference modules"""
+    from conftest import load_ckpt
+    from mpcdl import synth
+    g = _npz("pid.npz")
+    bags = synth.load_bags("pid_data_clean")
+    f, l = R.mlp_dataset(bags)
+    st = R.zscore_stats(f, l)
+    assert all(np.array_equal(st[k].numpy(), g[f"mlp_{k}"]) for k in st)
+    fn, _ = R.apply_zscore(f, l, st)
+    for name in ("Basic_16_2_16", "Basic_64_2_64"):
+        m, _ = R.build_from_name(name, load_ckpt(name))
+        with torch.no_grad():
+            assert np.array_equal(m(fn).numpy(), g[name])
+
+
+def test_identity_padding_of_shallow_mlps_is_exact():
+    """sweep() stacks MLP checkpoints of different depth by appending identity layers: relu(I x + 0) == x bit for bit."""
+    from conftest import load_ckpt
+    from mpcdl.eval_models import _pad_mlp_state
+    x = torch.randn(500, 8, generator=torch.Generator().manual_seed(0)) * 2
+    for name, hid, lay in (("Basic_16_1_32", 16, 1), ("Basic_64_2_32", 64, 2)):
+        sd = load_ckpt(name)
+        a, _ = R.build_from_name(name, sd)
+        b = R.RefBasic(8, hid, 6, 4)
+        b.load_state_dict(_pad_mlp_state(sd, hid, lay, 4))
+        with torch.no_grad():
+            assert torch.equal(a(x), b.eval()(x))
