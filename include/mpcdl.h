@@ -221,7 +221,7 @@ typedef struct {
 
 /* RobotData.norm statistics (basic_model.py:28-32, deep_models.py:29-33): mean and UNBIASED std over the samples, per
  * window position, written in the layout of mpcdl_rollout_args.norm: f_mean[T*8] f_std[T*8] l_mean[6] l_std[6]
- * (T = max(window,1)); device, FP32.  Two passes in double precision; <= 1e-6 relative to torch.mean / torch.std. */
+ * (T = max(window,1)); device, FP32.  Two passes in double precision; within one FP32 rounding of the FP64 statistics (std <= 1e-6 relative to torch.std, mean <= 1e-6 of max(|mean|, std) against torch.mean). */
 int mpcdl_dataset_stats(const mpcdl_dataset_desc* d, float* stats, void* stream);
 /* featrs [n,T,8] (window = 0: [n,8]) and labels [n,6], device.  stats = NULL -> raw values, else the z-score
  * (x - mean) / std of RobotData.norm (basic_model.py:34-35, deep_models.py:35-36: subtract THEN divide). */

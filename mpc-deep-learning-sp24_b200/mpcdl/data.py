@@ -84,8 +84,8 @@ def stats_from_vector(vec, size):
 
 def device_dataset(bags, size=None, device="cuda", normalise=True, stats_vec=None):
     """RobotData.__init__ + norm on the GPU: -> (featrs, labels, stats_vec).  Two launches: the statistics (unless
-    given) and the gather + z-score.  Statistics agree with torch.mean / torch.std to <= 1e-6 relative (two-pass double
-    accumulation here, float32 cascade sum there); given the same statistics the z-scored values are bit-identical."""
+    given) and the gather + z-score.  Statistics are within one FP32 rounding of the FP64 ones (two-pass double accumulation;
+    against torch's float32 cascade sum: std <= 1e-6 relative, mean <= 1e-6 of max(|mean|, std)); given the same statistics the z-scored values are bit-identical."""
     db = bags if isinstance(bags, DeviceBags) else DeviceBags(bags, device)
     w = int(size) if size else 0
     row_off, samp_off, n = db.offsets((lambda ln: ln - 1) if w == 0 else (lambda ln: ln - w - 1))   # basic_model.py:19 / deep_models.py:18
