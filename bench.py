@@ -379,8 +379,9 @@ def roofline_of(pb, k_ms, fp32_peak, peaks):
     ach = units * w["flop_exec"] / (k_ms * 1e-3) / 1e12
     if prec == "fp32":
         bound, peak = "fp32", fp32_peak
-        src = ("FP32 FFMA peak measured live by mpcdl_ffma_peak (MEASURED_PEAKS.json has no FP32 figure; "
-               "nominal 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)")
+        src = ("FP32 FMA peak measured live: the better of the scalar-FFMA and the packed-FFMA2 register micro-kernels "
+               "(mpcdl_ffma_peak / mpcdl_ffma2_peak; MEASURED_PEAKS.json has no FP32 figure; nominal 148 SM x 128 lanes x 2 x "
+               "1.965 GHz = 74.4)")
     elif prec == "bf16":
         bound, peak = "tensor", peaks.get("bf16_tflops", 1590.0)
         src = "dense BF16 peak: MEASURED_PEAKS.json bf16_tflops (burst)" if peaks else "fallback 1590 (B200_PROFILING.md)"
@@ -452,7 +453,8 @@ def run_native(args, key):
     for _ in range(warm):
         pb.step(pb.init_d, pb.U_d, pb.res_d)
     torch.cuda.synchronize(dev)
-    fp32_peak = ops.ffma_peak_tflops(dev)
+    fp32_peaks = ops.ffma_peak_tflops(dev, both=True)
+    fp32_peak = max(fp32_peaks)
 
     # ---- timed region 1: inputs resident in HBM, per-step device time (step = kernel [+ all-gather of costs])
     sampler = ClockSampler(local)
@@ -522,6 +524,7 @@ def run_native(args, key):
         peaks = load_peaks()
         roofline = roofline_of(pb, k_ms, fp32_peak, peaks)
         roofline["fp32_ffma_peak"] = fp32_peak
+        roofline["fp32_peaks_measured"] = {"ffma": fp32_peaks[0], "ffma2": fp32_peaks[1]}
         lps = pb.launches_per_step
         line = {"metric": METRIC, "value": units / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": w["scaling"],

@@ -262,6 +262,8 @@ int mpcdl_debug_poison_smem(void* stream);
  * the FP32 roofline denominator on the box it runs on.  out: device buffer of >= grid*256 floats.
  * FLOPs per launch = 2 * grid * 256 * iters * 64. */
 int mpcdl_ffma_peak(float* out_device, int iters, int grid, void* stream);
+/* The same tile issued as packed FFMA2 (fma.rn.f32x2, the form the rollout kernels use); same FLOP count. */
+int mpcdl_ffma2_peak(float* out_device, int iters, int grid, void* stream);
 
 const char* mpcdl_last_error(void);
 int mpcdl_version(void);

@@ -940,8 +940,15 @@ int mpcdl_debug_poison_smem(void* stream) {
 
 int mpcdl_ffma_peak(float* out_device, int iters, int grid, void* stream) {
     if (!out_device || iters < 1 || grid < 1) return fail(MPCDL_ERR_ARG, "mpcdl_ffma_peak: bad arguments");
-    cudaError_t e = launch_ffma_peak(out_device, iters, grid, static_cast<cudaStream_t>(stream));
+    cudaError_t e = launch_ffma_peak(out_device, iters, grid, false, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "ffma_peak launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
+int mpcdl_ffma2_peak(float* out_device, int iters, int grid, void* stream) {
+    if (!out_device || iters < 1 || grid < 1) return fail(MPCDL_ERR_ARG, "mpcdl_ffma2_peak: bad arguments");
+    cudaError_t e = launch_ffma_peak(out_device, iters, grid, true, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "ffma2_peak launch failed: %s", cudaGetErrorString(e));
     return MPCDL_OK;
 }
 

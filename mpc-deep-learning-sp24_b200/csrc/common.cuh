@@ -55,6 +55,22 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+// ------------------------------------------------------------------ packed FP32 FMA (Blackwell FFMA2)
+// fma.rn.f32x2 does two IEEE FP32 fused multiply-adds per lane in ONE issue slot (SASS FFMA2): each half is the same
+// round-to-nearest fmaf the scalar instruction computes, so results are bit-identical; what changes is that the FMA pipe,
+// not the issue slot, bounds a register-tile GEMM (ncu r02: rollout_mlp2 issued 78 % of the cycles with 67 % FMA).
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void ffma2(uint64_t& acc, uint64_t a, uint64_t b) {      // acc = a * b + acc, per half
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+
 // ------------------------------------------------------------------ activations
 // sigmoid(x) = 1/(1+2^(-x*log2e)); MUFU.EX2 (2 ulp) + MUFU.RCP (1 ulp): |err| < 1.5e-7 absolute.
 __device__ __forceinline__ float ex2_approx(float x) {

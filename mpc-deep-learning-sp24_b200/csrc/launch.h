@@ -49,6 +49,6 @@ cudaError_t launch_curve_metrics(const float* pred, const float* target, const f
                                  float* mae, float* rmse, cudaStream_t st);
 cudaError_t launch_resample(const ResampleParams& p, cudaStream_t st);
 cudaError_t launch_poison_smem(int num_sms, cudaStream_t st);
-cudaError_t launch_ffma_peak(float* out, int iters, int grid, cudaStream_t st);
+cudaError_t launch_ffma_peak(float* out, int iters, int grid, bool packed, cudaStream_t st);
 
 }  // namespace mpcdl

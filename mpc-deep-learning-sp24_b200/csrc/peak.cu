@@ -30,8 +30,40 @@ __global__ void __launch_bounds__(256) ffma_peak_kernel(float* out, int iters, f
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
-cudaError_t launch_ffma_peak(float* out, int iters, int grid, cudaStream_t st) {
-    ffma_peak_kernel<<<grid, 256, 0, st>>>(out, iters, 1.0f);
+// the same 8 x 8 accumulator tile issued as packed FFMA2 (fma.rn.f32x2: two FMAs per lane and issue slot)
+__global__ void __launch_bounds__(256) ffma2_peak_kernel(float* out, int iters, float seed) {
+    float a[8], w[8];
+    uint64_t acc[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        a[i] = seed + threadIdx.x * 1e-6f + i * 1e-3f;
+        w[i] = seed * 0.5f + i * 1e-3f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = pack2(0.f, 0.f);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ffma2(acc[i][j], pack2(a[i], a[i]), pack2(w[2 * j], w[2 * j + 1]));
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float lo, hi;
+            unpack2(acc[i][j], lo, hi);
+            s += lo + hi;
+        }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+cudaError_t launch_ffma_peak(float* out, int iters, int grid, bool packed, cudaStream_t st) {
+    if (packed) ffma2_peak_kernel<<<grid, 256, 0, st>>>(out, iters, 1.0f);
+    else ffma_peak_kernel<<<grid, 256, 0, st>>>(out, iters, 1.0f);
     return cudaGetLastError();
 }
 

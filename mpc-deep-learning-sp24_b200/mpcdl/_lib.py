@@ -115,7 +115,7 @@ class Plan(C.Structure):
 
 
 EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_pack_mlp_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
-           "mpcdl_rollout", "mpcdl_rollout_scratch_bytes", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_last_error", "mpcdl_version",
+           "mpcdl_rollout", "mpcdl_rollout_scratch_bytes", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_ffma2_peak", "mpcdl_last_error", "mpcdl_version",
            "mpcdl_dataset_stats", "mpcdl_dataset_build", "mpcdl_rollout_inputs", "mpcdl_curve_metrics", "mpcdl_resample",
            "mpcdl_debug_poison_smem")
 
@@ -161,6 +161,8 @@ def _load():
     lib.mpcdl_error_metrics.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.mpcdl_ffma_peak.restype = C.c_int
     lib.mpcdl_ffma_peak.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.mpcdl_ffma2_peak.restype = C.c_int
+    lib.mpcdl_ffma2_peak.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.mpcdl_dataset_stats.restype = C.c_int
     lib.mpcdl_dataset_stats.argtypes = [C.POINTER(DatasetDesc), C.c_void_p, C.c_void_p]
     lib.mpcdl_dataset_build.restype = C.c_int

@@ -52,20 +52,24 @@ def plan(kind, hidden, layers, window, N, H, stateful=False, noise_cfg=None, tun
     return p.as_dict()
 
 
-def ffma_peak_tflops(device=None, iters=20000, reps=5) -> float:
-    """Measured FP32 FFMA peak of the current GPU (TFLOP/s), CUDA events, best of `reps`."""
+def ffma_peak_tflops(device=None, iters=20000, reps=5, both=False):
+    """Measured FP32 FMA peak of the current GPU (TFLOP/s), CUDA events, best of `reps`: the better of the scalar FFMA and
+    the packed FFMA2 micro-kernel (the rollout kernels issue FFMA2).  both=True -> (ffma, ffma2)."""
     dev = torch.device(device or "cuda")
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
     grid = sms * 2
     out = torch.empty(grid * 256, device=dev, dtype=torch.float32)
     st = torch.cuda.current_stream(dev).cuda_stream
-    best = float("inf")
-    for r in range(reps + 1):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        _lib.check(_lib.lib.mpcdl_ffma_peak(C.c_void_p(out.data_ptr()), iters, grid, C.c_void_p(st)))
-        e1.record()
-        e1.synchronize()
-        if r:
-            best = min(best, e0.elapsed_time(e1))
-    return 2.0 * grid * 256 * iters * 64 / (best * 1e-3) / 1e12
+    res = []
+    for fn in (_lib.lib.mpcdl_ffma_peak, _lib.lib.mpcdl_ffma2_peak):
+        best = float("inf")
+        for r in range(reps + 1):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _lib.check(fn(C.c_void_p(out.data_ptr()), iters, grid, C.c_void_p(st)))
+            e1.record()
+            e1.synchronize()
+            if r:
+                best = min(best, e0.elapsed_time(e1))
+        res.append(2.0 * grid * 256 * iters * 64 / (best * 1e-3) / 1e12)
+    return tuple(res) if both else max(res)

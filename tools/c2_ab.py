@@ -22,8 +22,9 @@ def main():
     st = {k[4:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("mlp_")}
     rows = synth.load_rows()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    peak = ops.ffma_peak_tflops(dev)
-    print(f"ffma peak {peak:.1f} TFLOP/s")
+    pk = ops.ffma_peak_tflops(dev, both=True)
+    peak = max(pk)
+    print(f"fp32 peak: ffma {pk[0]:.1f}  ffma2 {pk[1]:.1f} TFLOP/s")
     for name in ("Basic_64_4_32", "Basic_64_2_64"):
         m, meta = mpcdl.from_checkpoint_name(name, load_ckpt(name), dev)
         flop = 2 * (8 * 64 + meta["layers"] * 64 * 64 + 6 * 64)
