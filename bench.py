@@ -443,7 +443,8 @@ def run_native(args, key):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))   # a protocol bug fails in minutes, not hours
     prec = args.precision
     pb = Problem(key, prec, dev, rank, world)
     w, N, H = pb.w, pb.N, pb.H
@@ -465,7 +466,10 @@ def run_native(args, key):
 
     # ---- timed region 2: end to end with host buffers (H2D inputs, D2H result every step)
     init_p, U_p, res_p = pb.host_buffers()
-    est_ms = max(dev_ms / args.steps, 0.05)
+    est_t = torch.tensor([dev_ms / args.steps], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(est_t, op=dist.ReduceOp.MAX)      # every rank must run the SAME number of steps (each step ends in a collective)
+    est_ms = max(float(est_t.item()), 0.05)
     e2e_steps = int(max(args.steps, min(math.ceil(500.0 / est_ms), 5000)))
     if e2e_steps * est_ms > 4000.0:                       # keep the five repeats of a slow workload within ~20 s
         e2e_steps = max(3, int(4000.0 / est_ms))

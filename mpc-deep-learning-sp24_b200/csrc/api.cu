@@ -70,17 +70,21 @@ uint32_t build_parts(const mpcdl_model_desc& d, PartDesc* parts, int& nparts) {
 struct Plan {
     int rt, rj, n_tg, TN, nct, grid, smem_bytes, resident, nslots, slot_floats, ntiles;
     int variant, ks;      // variant 0 = generic ring kernel, 2 = weight-resident MLP kernel (rollout_mlp2.cu)
+    int ng;               // weight-resident MLP kernel: independent thread groups per CTA (each owns a tile of TN trajectories)
 };
 
 // weight-resident MLP kernel: candidate tiles and their measured cost (cycles per dependent 64x64 layer,
 // profiles/r01a/mb_layer.log); must match MPCDL_MLP2_CONFIGS in launch.h
-struct Mlp2Cand { int hid, rt, rj, ks, tn_lo, tn_hi, tn_step; };
+struct Mlp2Cand { int hid, rt, rj, ks, tn_lo, tn_hi, tn_step, ng; };
 const Mlp2Cand kMlp2[] = {
-    {64, 4, 4, 2, 32, 32, 32}, {64, 8, 8, 2, 64, 64, 32}, {64, 8, 8, 1, 128, 256, 32},
-    {32, 4, 4, 2, 32, 64, 32}, {32, 8, 4, 1, 128, 256, 32},
-    {16, 4, 4, 2, 32, 64, 32}, {16, 8, 2, 1, 128, 512, 32},
+    {64, 4, 4, 2, 32, 32, 32, 1}, {64, 8, 8, 2, 64, 64, 32, 1}, {64, 8, 8, 1, 128, 256, 32, 1}, {64, 8, 8, 1, 128, 128, 32, 2},
+    {32, 4, 4, 2, 32, 64, 32, 1}, {32, 8, 4, 1, 128, 256, 32, 1},
+    {16, 4, 4, 2, 32, 64, 32, 1}, {16, 8, 2, 1, 128, 512, 32, 1},
 };
+constexpr double kMlp2TwoGroupCycles = 10300.0;  // per pass of 2 x 128 trajectories (1 M x 50: 32.8 ms against 35.7 ms for one group of 256,
+                                                 // 65 536 x 50: 2.35 against 2.53 ms; profiles/r02/twogroup/ab.log)
 double mlp2_cycles(const Mlp2Cand& c, int TN) {
+    if (c.ng == 2) return kMlp2TwoGroupCycles;
     if (c.ks == 2 && c.rt == 4) return 2009.0 * TN / 32;     // TN 28 on 147 SMs (7 warps) measured SLOWER than TN 32 on 128 (r01c)
     if (c.ks == 2) return 4029.0 * TN / 64;
     return 6596.0 + (TN - 128) * 39.3;
@@ -288,18 +292,20 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
             if (c.hid != d.hidden || (a.tune_rt && a.tune_rt != c.rt)) continue;
             for (int TN = c.tn_lo; TN <= c.tn_hi; TN += c.tn_step) {
                 if (a.tune_ntg && a.tune_ntg * c.rt != TN) continue;
-                if (a.tune_kc && a.tune_kc != c.ks) continue;
+                // tune_kc: 1 | 2 = K split of the one-group kernel, 4 = the two-group form (K split 1)
+                if (a.tune_kc && a.tune_kc != (c.ng == 2 ? 4 : c.ks)) continue;
                 Plan pl;
                 memset(&pl, 0, sizeof(pl));
-                pl.variant = 2; pl.ks = c.ks; pl.rt = c.rt; pl.rj = c.rj; pl.TN = TN; pl.n_tg = TN / c.rt;
-                pl.nct = pl.n_tg * (d.hidden / c.rj) * c.ks;
-                if (pl.nct % 32 || pl.nct > ((d.hidden == 16 && c.rt == 8) ? 512 : 256) || pl.nct < TN) continue;
+                pl.variant = 2; pl.ks = c.ks; pl.ng = c.ng; pl.rt = c.rt; pl.rj = c.rj; pl.TN = TN; pl.n_tg = TN / c.rt;
+                const int per_group = pl.n_tg * (d.hidden / c.rj) * c.ks;
+                pl.nct = per_group * c.ng;
+                if (per_group % 32 || pl.nct > ((d.hidden == 16 && c.rt == 8) ? 512 : 256) || per_group < TN) continue;
                 pl.resident = 1; pl.nslots = 1; pl.slot_floats = 0;
-                pl.smem_bytes = mlp2_smem_bytes((int)total, d.hidden, TN, c.ks, c.rt, c.rj);
+                pl.smem_bytes = mlp2_smem_bytes((int)total, d.hidden, TN, c.ks, c.rt, c.rj, c.ng);
                 if (pl.smem_bytes > SMEM_LIMIT) continue;
                 pl.ntiles = (int)((a.N + TN - 1) / TN);
-                pl.grid = std::min(pl.ntiles, num_sms);
-                const double cost = (double)((pl.ntiles + num_sms - 1) / num_sms) * mlp2_cycles(c, TN);
+                pl.grid = std::min((pl.ntiles + c.ng - 1) / c.ng, num_sms);
+                const double cost = (double)((pl.ntiles + num_sms * c.ng - 1) / (num_sms * c.ng)) * mlp2_cycles(c, TN);
                 if (cost < best2) { best2 = cost; best = pl; found2 = true; }
             }
         }
@@ -322,7 +328,7 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
         for (int n_tg = ntg_max; n_tg >= 1; --n_tg) {
             if (a.tune_ntg && n_tg != a.tune_ntg) continue;
             Plan pl;
-            pl.variant = 0; pl.ks = 1;
+            pl.variant = 0; pl.ks = 1; pl.ng = 1;
             pl.rt = rt; pl.rj = rj; pl.n_tg = n_tg; pl.TN = n_tg * rt;
             pl.nct = (n_tg * n_jg + 31) / 32 * 32;
             pl.resident = (!a.tune_nslots && total <= 24576u && n_models_of(a) == 1) ? 1 : 0;   // stacked models stream their own blob per tile
@@ -393,7 +399,13 @@ int check_args(const mpcdl_rollout_args* a) {
         if (!lt_supported(a->model))
             return fail(MPCDL_ERR_UNSUPPORTED, "MPCDL_PREC_BF16 is the LSTM hidden=%d kernel; got kind=%d hidden=%d window=%d",
                         LT_HID, a->model.kind, a->model.hidden, a->model.window);
-        if (a->stateful || a->noise_wblob) return fail(MPCDL_ERR_UNSUPPORTED, "MPCDL_PREC_BF16: stateless models without the residual-noise net only; use MPCDL_PREC_FP32");
+        if (a->noise_wblob) {
+            NoiseParams nz;
+            fill_noise(nz, *a);
+            if (lt_noise_layout(nz).total * 4 > LT_A_BYTES)
+                return fail(MPCDL_ERR_UNSUPPORTED, "MPCDL_PREC_BF16: the residual-noise net's buffers (%d B) exceed the %d B the kernel can lend them; use MPCDL_PREC_FP32",
+                            lt_noise_layout(nz).total * 4, LT_A_BYTES);
+        }
         if (!a->wblob_tc) return fail(MPCDL_ERR_ARG, "MPCDL_PREC_BF16 needs wblob_tc (mpcdl_pack_rnn_tc)");
         const size_t need = mpcdl_rollout_scratch_bytes(a);
         if (!a->scratch || a->scratch_bytes < need)
@@ -671,7 +683,7 @@ size_t mpcdl_rollout_scratch_bytes(const mpcdl_rollout_args* a) {
     if (!a || a->precision != MPCDL_PREC_BF16 || !lt_supported(a->model) || a->N < 1) return 0;
     LtPlan lp;
     make_lt_plan(*a, lp, planning_sms());
-    return (size_t)lp.grid * lt_scratch_bytes_per_cta(a->model.window);
+    return (size_t)lp.grid * lt_scratch_bytes_per_cta(a->model.window, a->noise_wblob ? 8 * a->noise_history : 0);
 }
 
 int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
@@ -731,6 +743,8 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
         memset(&q, 0, sizeof(q));
         build_lt_offsets(a->model, q.m);
         q.m.blob = a->wblob_tc;
+        q.m.stateful = a->stateful != 0;
+        fill_noise(q.nz, *a);
         q.scratch = static_cast<unsigned char*>(a->scratch);
 #ifdef MPCDL_LT_DEBUG      // development builds only (make DEFS=-DMPCDL_LT_DEBUG, tools/lt_dbg.py): host-mapped progress words
         if (const char* e = getenv("MPCDL_LT_DBG")) q.dbg = reinterpret_cast<unsigned int*>(strtoull(e, nullptr, 0));
@@ -782,7 +796,7 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     fill_io(p.io, *a, pl.ntiles);
     if (pl.variant != 2) set_stacking(p, *a, pl.TN, total);
     cudaError_t e;
-    if (pl.variant == 2) e = launch_mlp2(p, pl.rt, pl.rj, pl.ks, pl.grid, pl.smem_bytes, st);
+    if (pl.variant == 2) e = launch_mlp2(p, pl.rt, pl.rj, pl.ks, pl.ng, pl.grid, pl.smem_bytes, st);
     else if (a->model.kind == MPCDL_MLP) e = launch_mlp(p, pl.rt, pl.rj, pl.grid, pl.smem_bytes, st);
     else e = launch_rnn(p, a->model.kind == MPCDL_GRU ? 0 : 1, pl.rt, pl.rj, pl.grid, pl.smem_bytes, st);
     if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "kernel launch failed: %s (rt=%d n_tg=%d smem=%d)", cudaGetErrorString(e), pl.rt, pl.n_tg, pl.smem_bytes);

@@ -30,8 +30,8 @@ inline int mlp_rj(int hid) { return hid <= 16 ? 2 : hid <= 128 ? 4 : 8; }
 inline int rnn_rj(int) { return 4; }
 
 cudaError_t launch_mlp(const RolloutParams& p, int rt, int rj, int grid, int smem_bytes, cudaStream_t st);
-cudaError_t launch_mlp2(const RolloutParams& p, int rt, int rj, int ks, int grid, int smem_bytes, cudaStream_t st);
-int mlp2_smem_bytes(int blob_floats, int hid, int TN, int ks, int rt, int rj);
+cudaError_t launch_mlp2(const RolloutParams& p, int rt, int rj, int ks, int ng, int grid, int smem_bytes, cudaStream_t st);   // ng = thread groups per CTA
+int mlp2_smem_bytes(int blob_floats, int hid, int TN, int ks, int rt, int rj, int ng);
 cudaError_t launch_rnn(const RolloutParams& p, int cell, int rt, int rj, int grid, int smem_bytes, cudaStream_t st);
 cudaError_t launch_rnn_tc(const TcRolloutParams& p, int grid, int smem_bytes, cudaStream_t st);
 cudaError_t launch_lstm_tc(const LtRolloutParams& p, int grid, int smem_bytes, cudaStream_t st);

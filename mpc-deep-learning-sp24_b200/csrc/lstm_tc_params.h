@@ -33,6 +33,7 @@ struct LtModel {
     const float* blob;
     uint32_t bias_off, fc_off, w_off;      // float offsets
     int layers, window;
+    int stateful;                          // (h, c) of every layer carried from step to step / call to call (deep_models.py:88-91)
 };
 __host__ __device__ inline uint32_t lt_x0_slot_bytes() { return 128 * 16 * 2; }      // per CTA
 __host__ __device__ inline uint32_t lt_layer_bytes(int l) {
@@ -45,14 +46,29 @@ __host__ __device__ inline uint32_t lt_chunk_bytes(int l) { return lt_layer_byte
 
 struct LtRolloutParams {
     LtModel m;
-    NoiseParams nz;             // always disabled (owner_finish reads nz.enabled)
+    NoiseParams nz;             // residual-noise net (noise_model.py:34-40), evaluated on the CUDA cores at the end of every step
     IoParams io;
     unsigned int* dbg;          // development aid (MPCDL_LT_DEBUG builds): host-mapped words, else unused
     unsigned char* scratch;     // per CTA: [T frames] A tiles of 64 KB: the current layer's output sequence, written IN PLACE
                                 // over the previous layer's (cell (l, f) overwrites slot f after loading it as its x operand)
 };
-__host__ __device__ inline size_t lt_scratch_bytes_per_cta(int window) {      // + the raw window frames [T][8][128] FP32 (row-private)
-    return (size_t)window * LT_A_BYTES + (size_t)window * 8 * LT_TN * 4;
+// + the raw window frames [T][8][128] FP32 and the noise net's history [nin_dim][128] FP32 (both row-private)
+__host__ __device__ inline size_t lt_scratch_bytes_per_cta(int window, int nin_dim) {
+    return (size_t)window * LT_A_BYTES + (size_t)window * 8 * LT_TN * 4 + (size_t)nin_dim * LT_TN * 4;
+}
+// noise-net buffers inside the (idle at the end of a step) A_h region: [blob][nin][nact0][nact1][nzb][ybuf], float offsets
+struct LtNoiseSmem { int blob, nin, nact0, nact1, nzb, ybuf, total; };
+__host__ __device__ inline LtNoiseSmem lt_noise_layout(const NoiseParams& nz) {
+    LtNoiseSmem L;
+    int o = 0;
+    L.blob = o;  o += align_up(nz.blob_floats, 32);
+    L.nin = o;   o += nz.in_dim * LT_TN;
+    L.nact0 = o; o += nz.size * LT_TN;
+    L.nact1 = o; o += nz.size * LT_TN;
+    L.nzb = o;   o += 12 * LT_TN;
+    L.ybuf = o;  o += 8 * LT_TN;
+    L.total = o;
+    return L;
 }
 
 struct LtSmem {        // byte offsets

@@ -14,7 +14,9 @@
 //     operand and the next layer's input, re-loaded by TMA -- layer-major order keeps on-chip state to one layer;
 //   * layer 0 (K = 8 features) uses K = 16: [x_hi | x_lo] against [W | W], i.e. the inputs keep 16 mantissa bits;
 //   * activations on MUFU.TANH (5 per unit); full_c head, de-normalisation, cost and feedback stay FP32.
-// Stateless models, no residual-noise path (config 4 has neither); anything else is refused by the planner.
+// Stateful models: (h, c) of every layer come from / go to the carry planes [2L][N][256] (FP32); the carried h is rounded to
+// BF16 when it is staged as frame 0's recurrent operand, like every other h.  Residual-noise net: evaluated by the epilogue
+// warps on the CUDA cores at the end of a step, its buffers in the A_h region (idle then), its history in the scratch.
 #include "owner.cuh"
 #include "umma.cuh"
 #include "lstm_tc_params.h"
@@ -160,7 +162,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(LT_THREADS, 1) rollo
     unsigned char* const ring = smb + L.ring;
     // raw window frames [T][8][128] FP32: row-private (only the owner thread of a trajectory touches its column), kept in
     // the per-CTA scratch (L1/L2) so that shared memory holds a fifth ring slot
-    float* const xwin = reinterpret_cast<float*>(p.scratch + (size_t)blockIdx.x * lt_scratch_bytes_per_cta(T) + (size_t)T * LT_A_BYTES);
+    const int nin_dim = p.nz.enabled ? p.nz.in_dim : 0;
+    const bool stateful = m.stateful != 0;
+    float* const xwin = reinterpret_cast<float*>(p.scratch + (size_t)blockIdx.x * lt_scratch_bytes_per_cta(T, nin_dim) + (size_t)T * LT_A_BYTES);
     float* const biasS = reinterpret_cast<float*>(smb + L.bias);
     const float* const fcG = m.blob + m.fc_off;                         // full_c head [256][8] + bias[8]: read through L1 (once per step)
     float* const normS = reinterpret_cast<float*>(smb + L.norm);
@@ -208,7 +212,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(LT_THREADS, 1) rollo
                                 const unsigned char* src = wbase + lt_layer_off_bytes(l) + (uint32_t)c * lt_chunk_bytes(l);
                                 if (l == 0) { produce(src, lt_x0_slot_bytes()); src += 2 * lt_x0_slot_bytes(); }
                                 else { for (int s = 0; s < LT_SPC; ++s) produce(src + s * 2 * LT_SLOT_BYTES, LT_SLOT_BYTES); src += LT_SPC * 2 * LT_SLOT_BYTES; }
-                                if (f > 0) for (int s = 0; s < LT_SPC; ++s) produce(src + s * 2 * LT_SLOT_BYTES, LT_SLOT_BYTES);
+                                if (f > 0 || stateful) for (int s = 0; s < LT_SPC; ++s) produce(src + s * 2 * LT_SLOT_BYTES, LT_SLOT_BYTES);
                             }
         }
       } else if (warp == LT_EPI_WARPS + 1) {
@@ -266,9 +270,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(LT_THREADS, 1) rollo
                             if (c == 0) { await(&bars->ax_full, axp, 3, dq); axp ^= 1u; umma::fence_after_sync(); }
                             if (l == 0) slot_mmas(ax_u, 0u, 1, dcol, acc);
                             else for (uint32_t s = 0; s < (uint32_t)LT_SPC; ++s) slot_mmas(ax_u, 8u * s, 4, dcol, acc);
-                            if (f > 0) {
+                            if (f > 0 || stateful) {
                                 for (uint32_t s = 0; s < (uint32_t)LT_SPC; ++s) {
-                                    // h_{f-1} arrives in two pieces: units 0..191 while the previous cell's last chunk is still in
+                                    // h_{f-1} (frame 0 of a stateful model: the carried h) arrives in two pieces: units 0..191 while the previous cell's last chunk is still in
                                     // its epilogue, units 192..255 (that chunk's output) right after it
                                     if (c == 0 && s == 0) { await(&bars->ah_full[0], ahp, 4, dq); umma::fence_after_sync(); }
                                     if (c == 0 && s == LT_SPC - 1) { await(&bars->ah_full[1], ahp, 4, dq); ahp ^= 1u; umma::fence_after_sync(); }

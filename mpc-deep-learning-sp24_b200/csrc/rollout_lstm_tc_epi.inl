@@ -5,7 +5,11 @@
         const bool owner = g == 0;                            // tid < 128: keeps the trajectory's state, cost, window
         const uint32_t tlane = tbase + (static_cast<uint32_t>(q * 32) << 16);
         const uint32_t rowoff = (row >> 3) * 128 + (row & 7) * 16;          // byte offset of this row inside a 16-B k-chunk column
-        unsigned char* const scratch = p.scratch + (size_t)blockIdx.x * lt_scratch_bytes_per_cta(T);
+        unsigned char* const scratch = p.scratch + (size_t)blockIdx.x * lt_scratch_bytes_per_cta(T, nin_dim);
+        float* const nhist = xwin + T * 8 * LT_TN;             // noise history [in_dim][128], row-private like xwin
+        const LtNoiseSmem NZ = lt_noise_layout(p.nz);
+        float* const nzS = reinterpret_cast<float*>(ah);       // noise-net buffers: A_h is idle between the last cell of a step and the next step
+        const long long Ntot = p.io.N;
         const float* const norm_l = normS + 2 * T * 8;
         constexpr int NEPI = LT_EPI_WARPS * 32;
         uint32_t dq = 0;
@@ -40,6 +44,24 @@
                     if (tid == 0) mbar_arrive(&bars->ax_full);
                 }
             };
+            // stateful: frame 0's recurrent operand of layer l = the carried h (FP32 plane l), rounded to BF16 like every h.
+            // Every thread stages the 64 units it owns (the ones it wrote at the end of the previous step / the caller's
+            // initial carry).  A_h must be free: called where every MMA of the previous cell is complete.
+            auto stage_h0 = [&](int l) {
+                const float* hc = p.io.carry + ((long long)l * Ntot + n) * LT_HID;
+#pragma unroll
+                for (int c = 0; c < LT_NCH; ++c)
+#pragma unroll
+                    for (int half = 0; half < 2; ++half) {
+                        const int u0 = c * LT_CH + 16 * g + 8 * half;
+                        const float4 a = *reinterpret_cast<const float4*>(hc + u0), b = *reinterpret_cast<const float4*>(hc + u0 + 4);
+                        *reinterpret_cast<uint4*>(ah + (size_t)(c * 8 + g * 2 + half) * LT_A_LBO + rowoff) =
+                            make_uint4(lt_pack(a.x, a.y), lt_pack(a.z, a.w), lt_pack(b.x, b.y), lt_pack(b.z, b.w));
+                    }
+                umma::fence_proxy_async_smem();
+                named_bar_sync(1, NEPI);
+                if (tid == 0) { mbar_arrive(&bars->ah_full[0]); mbar_arrive(&bars->ah_full[1]); }
+            };
             for (int t = 0; t < H; ++t) {
                 float u[2] = {0.f, 0.f};
                 if (owner) { const float2 uu = load_control(p.io, n, t); u[0] = uu.x; u[1] = uu.y; }
@@ -51,8 +73,18 @@
                     float cst[LT_NCH * 16];
 #pragma unroll
                     for (int i = 0; i < LT_NCH * 16; ++i) cst[i] = 0.f;        // stateless: (h, c) = 0 at every call (deep_models.py:82-83)
+                    if (stateful) {                                             // carried cell state: plane L + l
+                        const float* cc = p.io.carry + ((long long)(NL + l) * Ntot + n) * LT_HID;
+#pragma unroll
+                        for (int c = 0; c < LT_NCH; ++c)
+#pragma unroll
+                            for (int hq = 0; hq < 4; ++hq) {
+                                const float4 v = *reinterpret_cast<const float4*>(cc + c * LT_CH + 16 * g + 4 * hq);
+                                cst[c * 16 + 4 * hq] = v.x; cst[c * 16 + 4 * hq + 1] = v.y; cst[c * 16 + 4 * hq + 2] = v.z; cst[c * 16 + 4 * hq + 3] = v.w;
+                            }
+                    }
                     for (int f = 0; f < T; ++f) {
-                        if (l == 0 && f == 0) stage_l0(0);
+                        if (l == 0 && f == 0) { stage_l0(0); if (stateful) stage_h0(0); }
                         int l2 = l, f2 = f + 1;                                  // the next cell
                         if (f2 == T) { l2 = l + 1; f2 = 0; }
                         const bool last = l == NL - 1 && f == T - 1;
@@ -72,6 +104,7 @@
                                     bulk_g2s(ax, src, LT_A_BYTES / 2, &bars->ax_full);
                                     bulk_g2s(ax + LT_A_BYTES / 2, src + LT_A_BYTES / 2, LT_A_BYTES / 2, &bars->ax_full);
                                 }
+                                if (f2 == 0 && stateful) stage_h0(l2);        // the next layer starts from ITS carried h
                                 if (f2 > 0 && tid == 0) {        // units 0..191 of h_f (chunks 0..2: fenced + barrier below)
                                     mbar_expect_tx(&bars->ah_full[0], 3 * LT_A_BYTES / 4);
                                     bulk_g2s(ah, hout, LT_A_BYTES / 2, &bars->ah_full[0]);
@@ -100,6 +133,15 @@
                                 }
                                 *reinterpret_cast<uint4*>(hout + (size_t)(c * 8 + g * 2 + half) * LT_A_LBO + rowoff) =
                                     make_uint4(lt_pack(hv[0], hv[1]), lt_pack(hv[2], hv[3]), lt_pack(hv[4], hv[5]), lt_pack(hv[6], hv[7]));
+                                if (stateful && f == T - 1 && valid) {             // (h, c) after the window's last frame -> carry (FP32)
+                                    float* ch = p.io.carry + ((long long)l * Ntot + n) * LT_HID + c * LT_CH + u0;
+                                    float* cc = p.io.carry + ((long long)(NL + l) * Ntot + n) * LT_HID + c * LT_CH + u0;
+                                    *reinterpret_cast<float4*>(ch) = make_float4(hv[0], hv[1], hv[2], hv[3]);
+                                    *reinterpret_cast<float4*>(ch + 4) = make_float4(hv[4], hv[5], hv[6], hv[7]);
+                                    const float* cs = &cst[c * 16 + half * 8];
+                                    *reinterpret_cast<float4*>(cc) = make_float4(cs[0], cs[1], cs[2], cs[3]);
+                                    *reinterpret_cast<float4*>(cc + 4) = make_float4(cs[4], cs[5], cs[6], cs[7]);
+                                }
                                 if (last) {                                        // full_c head on the FP32 h of the last layer's last frame
                                     const float* wf = fcG + (c * 64 + u0) * 8;
 #pragma unroll
@@ -142,14 +184,47 @@
 #pragma unroll
                     for (int d = 0; d < 6; ++d) ypart[((g - 1) * 6 + d) * LT_TN + row] = y[d];
                 }
+                if (p.nz.enabled) {
+                    // residual-noise net (noise_model.py:34-40) on the CUDA cores: weights + history -> the idle A_h region
+                    for (int i = tid; i < p.nz.blob_floats; i += NEPI) nzS[NZ.blob + i] = __ldg(p.nz.blob + i);
+                    if (owner) {                               // (q, u) of the window's newest frame joins the history (noise_model.py:95-99)
+                        int pf = base + T - 1; if (pf >= T) pf -= T;
+                        float s6[6], uf[2];
+#pragma unroll
+                        for (int d = 0; d < 6; ++d) s6[d] = xwin[(pf * 8 + d) * LT_TN + row];
+                        uf[0] = xwin[(pf * 8 + 6) * LT_TN + row]; uf[1] = xwin[(pf * 8 + 7) * LT_TN + row];
+                        noise_push(nhist, LT_TN, row, p.nz.hist, t == 0, s6, uf);
+                        for (int k = 0; k < p.nz.in_dim; ++k) nzS[NZ.nin + k * LT_TN + row] = nhist[k * LT_TN + row];
+                    }
+                }
                 named_bar_sync(1, NEPI);
+                if (p.nz.enabled) {
+                    const float* W = nzS + NZ.blob;
+                    int K = p.nz.in_dim;
+                    for (int ph = 0; ph <= p.nz.nlayers; ++ph) {
+                        const bool lastp = ph == p.nz.nlayers;
+                        const int outw = lastp ? 12 : p.nz.size;
+                        const float* in = ph == 0 ? nzS + NZ.nin : nzS + (((ph - 1) & 1) ? NZ.nact1 : NZ.nact0);
+                        float* out = lastp ? nzS + NZ.nzb : nzS + ((ph & 1) ? NZ.nact1 : NZ.nact0);
+                        dense_resident<4, 4>(in, K, W, outw, outw, lastp ? ACT_IDENTITY : p.nz.act, out, LT_TN, tid, NEPI);
+                        W += (K + 1) * outw; K = p.nz.size;
+                        named_bar_sync(1, NEPI);
+                    }
+                }
                 if (owner) {
 #pragma unroll
                     for (int d = 0; d < 6; ++d)
                         y[d] = y[d] + ypart[(0 * 6 + d) * LT_TN + row] + ypart[(1 * 6 + d) * LT_TN + row] + ypart[(2 * 6 + d) * LT_TN + row] +
                                __ldg(fcG + LT_HID * 8 + d);
                     float nxt[6];
-                    owner_finish(p, norm_l, y, nullptr, 1, 0, n, valid, t, u, nxt, cost);
+                    if (p.nz.enabled) {                        // owner_finish reads y and the noise output with one column stride
+                        float* yb = nzS + NZ.ybuf;
+#pragma unroll
+                        for (int d = 0; d < 6; ++d) yb[d * LT_TN + row] = y[d];
+                        owner_finish(p, norm_l, yb, nzS + NZ.nzb, LT_TN, row, n, valid, t, u, nxt, cost);
+                    } else {
+                        owner_finish(p, norm_l, y, nullptr, 1, 0, n, valid, t, u, nxt, cost);
+                    }
                     // window shift: the oldest physical slot takes the new frame [s_{t+1}, u_t]
 #pragma unroll
                     for (int d = 0; d < 6; ++d) xwin[(base * 8 + d) * LT_TN + row] = nxt[d];

@@ -19,21 +19,23 @@
 
 namespace mpcdl {
 
-struct Mlp2Smem {     // float offsets
-    int bars, blob, norm, xin, act0, act1, red, ybuf, total;
+struct Mlp2Smem {     // float offsets; xin .. ybuf are group 0's, group g's follow at + g * gstride
+    int bars, blob, norm, xin, act0, act1, red, ybuf, gstride, total;
 };
-__host__ __device__ inline Mlp2Smem mlp2_layout(int blob_floats, int hid, int TN, int ks, int kq) {
+__host__ __device__ inline Mlp2Smem mlp2_layout(int blob_floats, int hid, int TN, int ks, int kq, int ng) {
     Mlp2Smem L;
     int o = 0;
     L.bars = o;  o += 32;
     L.blob = o;  o += align_up(blob_floats, 32);
     L.norm = o;  o += 32;
+    const int g0 = o;
     L.xin = o;   o += 8 * TN;
     L.act0 = o;  o += hid * TN;
     L.act1 = o;  o += hid * TN;
     L.red = o;   o += (ks - 1) * hid * TN;
     L.ybuf = o;  o += kq * 8 * TN;
-    L.total = o;
+    L.gstride = align_up(o - g0, 32);
+    L.total = g0 + ng * L.gstride;
     return L;
 }
 
@@ -102,32 +104,42 @@ struct Mlp2Cfg {
     static_assert(KQ >= 1 && HID % KQ == 0 && HID % KS == 0 && RT % 4 == 0, "unsupported MLP tile configuration");
 };
 
-template <int HID, int RT, int RJ, int KS>
+// NG = 2: the CTA is two independent groups of threads, each rolling out its own tile of TN trajectories with its own
+// activation buffers and a named barrier of its own, sharing the weights.  The two groups drift apart, so the per-layer
+// epilogue of one (bias, ReLU, transposed stores, barrier: ~940 of ~5700 clocks, tools/mb_layer2) runs under the k-loop of
+// the other on every scheduler instead of idling the FMA pipe.
+template <int HID, int RT, int RJ, int KS, int NG>
 __global__ void __launch_bounds__((Mlp2Cfg<HID, RT, RJ, KS>::MAX_THREADS), 1) rollout_mlp2_kernel(const __grid_constant__ RolloutParams p) {
     using C = Mlp2Cfg<HID, RT, RJ, KS>;
     extern __shared__ __align__(128) float sm[];
     const ModelParams& m = p.m;
     const int TN = m.TN, n_tg = m.n_tg, NL = m.layers, H = p.io.H;
-    const Mlp2Smem L = mlp2_layout((int)m.data_floats, HID, TN, KS, C::KQ);
-    const int tid = threadIdx.x;
+    const Mlp2Smem L = mlp2_layout((int)m.data_floats, HID, TN, KS, C::KQ, NG);
+    const int GT = (int)blockDim.x / NG;                       // threads per group
+    const int grp = NG == 1 ? 0 : (int)threadIdx.x / GT;
+    const int tid = (int)threadIdx.x - grp * GT;               // thread index INSIDE the group: every mapping below uses it
     uint64_t* full = reinterpret_cast<uint64_t*>(sm + L.bars);
     float* const blob = sm + L.blob;
     float* const normS = sm + L.norm;
-    float* const xin = sm + L.xin;
-    float* const act0 = sm + L.act0;
+    float* const xin = sm + L.xin + grp * L.gstride;
+    float* const act0 = sm + L.act0 + grp * L.gstride;
     const int act_flip = L.act1 - L.act0;
-    float* const red = sm + L.red;
-    float* const ybuf = sm + L.ybuf;
+    float* const red = sm + L.red + grp * L.gstride;
+    float* const ybuf = sm + L.ybuf + grp * L.gstride;
+    auto group_sync = [&]() {
+        if (NG == 1) __syncthreads();
+        else named_bar_sync(1 + grp, GT);
+    };
 
     // ---- one-time: weights -> shared memory (TMA bulk copies on one mbarrier), statistics
-    if (tid == 0) {
+    if (threadIdx.x == 0) {
         mbar_init(full, 1);
         mbar_fence_init();
         mbar_expect_tx(full, m.data_floats * 4u);
         for (uint32_t o = 0; o < m.data_floats; o += 8192u)
             bulk_g2s(blob + o, m.blob + o, min(8192u, m.data_floats - o) * 4u, full);
     }
-    for (int i = tid; i < 28; i += blockDim.x) normS[i] = p.io.norm[i];       // f_mean8 f_std8 l_mean6 l_std6
+    for (int i = threadIdx.x; i < 28; i += blockDim.x) normS[i] = p.io.norm[i];       // f_mean8 f_std8 l_mean6 l_std6
     __syncthreads();
     mbar_wait(full, 0);
 
@@ -140,7 +152,7 @@ __global__ void __launch_bounds__((Mlp2Cfg<HID, RT, RJ, KS>::MAX_THREADS), 1) ro
     const PartDesc& pin = m.parts[0];
     const PartDesc& pout = m.parts[NL + 1];
 
-    for (int tile = blockIdx.x; tile < p.io.ntiles; tile += gridDim.x) {
+    for (int tile = blockIdx.x * NG + grp; tile < p.io.ntiles; tile += gridDim.x * NG) {
         long long n = (long long)tile * TN + tid;
         const bool valid = owner && n < p.io.N;
         if (n >= p.io.N) n = p.io.N - 1;
@@ -160,7 +172,7 @@ __global__ void __launch_bounds__((Mlp2Cfg<HID, RT, RJ, KS>::MAX_THREADS), 1) ro
 #pragma unroll
                 for (int k = 0; k < 2; ++k) xin[(6 + k) * TN + tid] = __fdiv_rn(__fsub_rn(u[k], normS[6 + k]), normS[14 + k]);
             }
-            __syncthreads();
+            group_sync();
             // ---- input layer 8 -> HID (K = 8: not worth splitting)
             if (ks == 0) {
                 float acc[RT][RJ], b[RJ];
@@ -172,7 +184,7 @@ __global__ void __launch_bounds__((Mlp2Cfg<HID, RT, RJ, KS>::MAX_THREADS), 1) ro
                 tile_gemm<RT, RJ, 8, HID>(acc, xin + tg * 4, TN, hs, blob + pin.off + pin.bias_floats + jg * RJ);
                 store_relu<RT, RJ>(act0 + (jg * RJ) * TN + tg * 4, TN, hs, acc);
             }
-            __syncthreads();
+            group_sync();
             // ---- hidden layers HID -> HID
             for (int l = 1; l <= NL; ++l) {
                 const float* in = act0 + ((l - 1) & 1) * act_flip;
@@ -204,7 +216,7 @@ __global__ void __launch_bounds__((Mlp2Cfg<HID, RT, RJ, KS>::MAX_THREADS), 1) ro
                                 *reinterpret_cast<float4*>(d + r * TN + c * hs) =
                                     make_float4(acc[4 * c][r], acc[4 * c + 1][r], acc[4 * c + 2][r], acc[4 * c + 3][r]);
                     }
-                    __syncthreads();
+                    group_sync();
                     if (ks == 0) {
 #pragma unroll
                         for (int q = 0; q < KS - 1; ++q)
@@ -218,7 +230,7 @@ __global__ void __launch_bounds__((Mlp2Cfg<HID, RT, RJ, KS>::MAX_THREADS), 1) ro
                     }
                 }
                 if (ks == 0) store_relu<RT, RJ>(out + (jg * RJ) * TN + tg * 4, TN, hs, acc);
-                __syncthreads();
+                group_sync();
             }
             // ---- output layer HID -> 6 (blob width 8): K quarters per trajectory, owner sums them
             {
@@ -240,7 +252,7 @@ __global__ void __launch_bounds__((Mlp2Cfg<HID, RT, RJ, KS>::MAX_THREADS), 1) ro
 #pragma unroll
                 for (int d = 0; d < 6; ++d) ybuf[(okq * 8 + d) * TN + otraj] = y[d];
             }
-            __syncthreads();
+            group_sync();
             if (owner) {
 #pragma unroll
                 for (int d = 0; d < 6; ++d) {
@@ -256,27 +268,29 @@ __global__ void __launch_bounds__((Mlp2Cfg<HID, RT, RJ, KS>::MAX_THREADS), 1) ro
             }
         }
         if (valid && p.io.costs) p.io.costs[n] = cost;
-        __syncthreads();     // ybuf / xin of this tile are dead before the next tile's owners write
+        group_sync();     // ybuf / xin of this tile are dead before the next tile's owners write
     }
 }
 
 // ------------------------------------------------------------------ launcher
-template <int HID, int RT, int RJ, int KS>
+template <int HID, int RT, int RJ, int KS, int NG>
 static cudaError_t launch_mlp2_t(const RolloutParams& p, int grid, int smem_bytes, cudaStream_t st) {
-    auto k = rollout_mlp2_kernel<HID, RT, RJ, KS>;
+    auto k = rollout_mlp2_kernel<HID, RT, RJ, KS, NG>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     if (e != cudaSuccess) return e;
-    k<<<grid, p.m.n_cthreads, smem_bytes, st>>>(p);
+    k<<<grid, p.m.n_cthreads, smem_bytes, st>>>(p);      // n_cthreads = threads of ALL groups
     return cudaGetLastError();
 }
 
-int mlp2_smem_bytes(int blob_floats, int hid, int TN, int ks, int rt, int rj) {
-    return mlp2_layout(blob_floats, hid, TN, ks, hid * ks / (rt * rj)).total * 4;
+int mlp2_smem_bytes(int blob_floats, int hid, int TN, int ks, int rt, int rj, int ng) {
+    return mlp2_layout(blob_floats, hid, TN, ks, hid * ks / (rt * rj), ng).total * 4;
 }
 
-cudaError_t launch_mlp2(const RolloutParams& p, int rt, int rj, int ks, int grid, int smem_bytes, cudaStream_t st) {
+cudaError_t launch_mlp2(const RolloutParams& p, int rt, int rj, int ks, int ng, int grid, int smem_bytes, cudaStream_t st) {
+    if (ng == 2 && p.m.hid == 64 && rt == 8 && rj == 8 && ks == 1) return launch_mlp2_t<64, 8, 8, 1, 2>(p, grid, smem_bytes, st);
+    if (ng != 1) return cudaErrorInvalidConfiguration;
 #define MPCDL_CASE(H_, RT_, RJ_, KS_) \
-    if (p.m.hid == H_ && rt == RT_ && rj == RJ_ && ks == KS_) return launch_mlp2_t<H_, RT_, RJ_, KS_>(p, grid, smem_bytes, st);
+    if (p.m.hid == H_ && rt == RT_ && rj == RJ_ && ks == KS_) return launch_mlp2_t<H_, RT_, RJ_, KS_, 1>(p, grid, smem_bytes, st);
     MPCDL_MLP2_CONFIGS(MPCDL_CASE)
 #undef MPCDL_CASE
     return cudaErrorInvalidConfiguration;

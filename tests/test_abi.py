@@ -87,6 +87,12 @@ def test_plans_fit_the_machine():
                 assert p["smem_bytes"] <= 232448 and p["threads"] <= 512 and p["threads"] % 32 == 0
                 assert 1 <= p["grid"] <= 148 and p["ntiles"] * p["tile_traj"] >= n
                 assert p["tile_traj"] == p["rt"] * p["n_tg"]
+    # 1 M trajectories of the hidden-64 MLP: two independent 128-trajectory groups per CTA; few tiles: one group, more SMs
+    p = ops.plan(0, 64, 4, 0, 1 << 20, 50)
+    assert p["variant"] == 2 and p["tile_traj"] == 128 and p["threads"] == 256 and p["ntiles"] == 8192 and p["grid"] == 148
+    p = ops.plan(0, 64, 4, 0, 16384, 50)
+    assert p["variant"] == 2 and p["tile_traj"] == 128 and p["threads"] == 128 and p["grid"] == 128
+    assert ops.plan(0, 64, 4, 0, 4096, 50)["tile_traj"] == 32
 
 
 def test_tensor_core_plans_and_errors():
@@ -129,8 +135,14 @@ def test_tensor_core_plans_and_errors():
     assert _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a)) == 8 * (4 * 128 * 256 * 2 + 4 * 8 * 128 * 4)
     a.precision = 0
     assert _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a)) == 0
-    for args, kw in [((2, 64, 4, 4), {}), ((1, 256, 4, 4), {}), ((2, 256, 4, 4), dict(stateful=True)),
-                     ((2, 256, 4, 4), dict(noise_cfg=[3, 32, 2, 2]))]:
+    # with the residual-noise net the scratch also holds its history [8 * history][128] FP32 per CTA
+    a.precision, a.noise_wblob, a.noise_history, a.noise_size, a.noise_layers, a.noise_act = 3, 16, 3, 32, 2, 2
+    assert _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a)) == 8 * (4 * 128 * 256 * 2 + 4 * 8 * 128 * 4 + 24 * 128 * 4)
+    # stateful models and the default noise net run on the BF16 kernel (round 2); other families / sizes and a noise net
+    # whose buffers exceed the 64 KB the kernel can lend it are refused
+    assert ops.plan(2, 256, 4, 4, 100, 5, precision="bf16", stateful=True)["variant"] == 6
+    assert ops.plan(2, 256, 4, 4, 100, 5, precision="bf16", noise_cfg=[3, 32, 2, 2])["variant"] == 6
+    for args, kw in [((2, 64, 4, 4), {}), ((1, 256, 4, 4), {}), ((2, 256, 4, 4), dict(noise_cfg=[8, 64, 2, 2]))]:
         with pytest.raises(RuntimeError):
             ops.plan(*args, 100, 5, precision="bf16", **kw)
 

@@ -122,3 +122,103 @@ def test_c5_full_size_properties(gold_stats):
     k = perm[:2048].cpu()
     want = R.rollout_mlp(ref, st, s0[k], U[k], cost=cost)[1]
     assert ((c[k.to(_dev())].cpu() - want).abs() / want.abs()).max().item() <= 1e-3
+
+
+def test_c3_stateful_full_size_properties(gold_stats):
+    """C3 with the stateful checkpoint (GRU_64_4_4_64_True: h_state carried from step to step, deep_models.py:61-65)
+    + residual-noise net, 65 536 x 100: permutation invariance of states AND of the carried hidden state bit for bit,
+    the two half batches (traj_offset) against the full launch, and 96 trajectories against the oracle."""
+    import mpcdl
+    from oracle import rollout_ref as R
+    from mpcdl import synth
+    N, H = 65536, 100
+    m, ref, win, U, _ = _setup("GRU_64_4_4_64_True", N, H)
+    st = gold_stats[1]
+    noise = mpcdl.FeedforwardNoiseModel(6, 2, 3, n_layers=2, size=32, activation="tanh", output_activation="identity")
+    noise.model.load_state_dict(load_ckpt("noise_seed0_h3_s32_l2"))
+    noise.to(_dev())
+    win, U = win.to(_dev()), U.to(_dev())
+    s, _, carry = m.rollout(win, U, st, noise=noise, seed=1, stateful=True)
+    assert torch.isfinite(s).all() and carry.shape == (4, N, 64)
+    h = N // 2
+    s_hi, _, c_hi = m.rollout(win[h:].contiguous(), U[h:].contiguous(), st, noise=noise, seed=1, traj_offset=h, stateful=True)
+    assert torch.equal(s_hi, s[h:]) and torch.equal(c_hi, carry[:, h:])
+    del s_hi, c_hi
+    eps = synth.make_eps(N, H, seed=1).to(_dev())
+    s, _, carry = m.rollout(win, U, st, noise=noise, eps=eps, stateful=True)
+    perm = torch.randperm(N, generator=torch.Generator().manual_seed(5)).to(_dev())
+    sp, _, cp = m.rollout(win[perm].contiguous(), U[perm].contiguous(), st, noise=noise, eps=eps[perm].contiguous(), stateful=True)
+    assert torch.equal(sp, s[perm]) and torch.equal(cp, carry[:, perm])
+    del sp, cp
+    k = perm[:96]
+    rn = R.RefNoise(6, 2, 3, 2, 32, "tanh", "identity")
+    rn.model.load_state_dict(load_ckpt("noise_seed0_h3_s32_l2"))
+    rn.eval()
+    want, _, hfin = R.rollout_rnn(ref, st, win[k].cpu(), U[k].cpu(), stateful=True, noise=rn, eps=eps[k].cpu())
+    err = R.rel_err(s[k].cpu(), want)
+    assert err[:, 0].max().item() <= 1e-5 and _p90(err) <= 1e-5
+    # the carried state after 100 chaotic steps: quantile bound like T2 (one saturating gate moves a unit by 1e-3)
+    cerr = (carry[:, k].cpu() - hfin).abs().flatten().double()
+    assert torch.quantile(cerr, 0.9).item() <= 1e-4
+
+
+@pytest.mark.parametrize("prec,one_step,p90_bound", [("fp32", 1e-5, 1e-5), ("tf32x3", 2e-5, 2e-4), ("tf32", 5e-3, 2e-2)])
+def test_c5_gru_full_size_properties(prec, one_step, p90_bound, gold_stats):
+    """C5 with the GRU: 1 048 576 x 100, cost-only, FP32 and both tensor-core precisions.  Bit-for-bit permutation and shard
+    invariance of the costs; the states of a 64-trajectory sample (rolled out again with states on) against the oracle at
+    the precision's stated bound (T1/T2 for fp32, T3 of DESIGN.md 5 for tf32x3 / tf32)."""
+    from oracle import rollout_ref as R
+    N, H = 1 << 20, 100
+    m, ref, win, U, cost = _setup("GRU_64_4_4_16_False", N, H)
+    st = gold_stats[1]
+    wd, Ud = win.to(_dev()), U.to(_dev())
+    cost_d = tuple(c.to(_dev()) for c in cost)
+    kw = dict(cost=cost_d, return_states=False, precision=prec)
+    c = m.rollout(wd, Ud, st, **kw)[1]
+    assert c.shape == (N,) and torch.isfinite(c).all()
+    h = N // 2
+    c_hi = m.rollout(wd[h:].contiguous(), Ud[h:].contiguous(), st, traj_offset=h, **kw)[1]
+    assert torch.equal(c_hi, c[h:])
+    perm = torch.randperm(N, generator=torch.Generator().manual_seed(6)).to(_dev())
+    if prec == "fp32":                       # one more 2 s launch only for the parity path
+        cp = m.rollout(wd[perm].contiguous(), Ud[perm].contiguous(), st, **kw)[1]
+        assert torch.equal(cp, c[perm])
+    k = perm[:64]
+    s, ck = m.rollout(wd[k].contiguous(), Ud[k].contiguous(), st, cost=cost_d, precision=prec)
+    assert torch.equal(ck, c[k])             # the cost of a trajectory does not depend on the batch it was launched in
+    want, cwant, _ = R.rollout_rnn(ref, st, win[k.cpu()], U[k.cpu()], stateful=False, cost=cost)
+    err = R.rel_err(s.cpu(), want)
+    print(f"measured {prec}: one-step {err[:, 0].max().item():.3e}  p90 over the horizon {_p90(err):.3e}")
+    assert err[:, 0].max().item() <= one_step and _p90(err) <= p90_bound, (err[:, 0].max().item(), _p90(err))
+
+
+@pytest.mark.parametrize("prec,one_step,p90_bound", [("tf32x3", 2e-5, 2e-4), ("tf32", 5e-3, 2e-2)])
+def test_c3_tensor_core_full_size_properties(prec, one_step, p90_bound, gold_stats):
+    """C3 (GRU + residual-noise net, 65 536 x 100) on the tcgen05 kernel: repeat launches bit-identical, shard invariance with
+    in-kernel Philox noise, a 96-trajectory sample against the oracle with supplied eps at the precision's T3 bound."""
+    import mpcdl
+    from oracle import rollout_ref as R
+    from mpcdl import synth
+    N, H = 65536, 100
+    m, ref, win, U, _ = _setup("GRU_64_4_4_16_False", N, H)
+    st = gold_stats[1]
+    noise = mpcdl.FeedforwardNoiseModel(6, 2, 3, n_layers=2, size=32, activation="tanh", output_activation="identity")
+    noise.model.load_state_dict(load_ckpt("noise_seed0_h3_s32_l2"))
+    noise.to(_dev())
+    win, U = win.to(_dev()), U.to(_dev())
+    s = m.rollout(win, U, st, noise=noise, seed=1, precision=prec)[0]
+    assert torch.isfinite(s).all()
+    assert torch.equal(m.rollout(win, U, st, noise=noise, seed=1, precision=prec)[0], s)
+    h = N // 2
+    assert torch.equal(m.rollout(win[h:].contiguous(), U[h:].contiguous(), st, noise=noise, seed=1, traj_offset=h, precision=prec)[0], s[h:])
+    del s
+    k = torch.randperm(N, generator=torch.Generator().manual_seed(7))[:96]
+    eps = synth.make_eps(96, H, seed=1)
+    got = m.rollout(win[k.to(_dev())].contiguous(), U[k.to(_dev())].contiguous(), st, noise=noise, eps=eps.to(_dev()), precision=prec)[0]
+    rn = R.RefNoise(6, 2, 3, 2, 32, "tanh", "identity")
+    rn.model.load_state_dict(load_ckpt("noise_seed0_h3_s32_l2"))
+    rn.eval()
+    want = R.rollout_rnn(ref, st, win[k.to(_dev())].cpu(), U[k.to(_dev())].cpu(), stateful=False, noise=rn, eps=eps)[0]
+    err = R.rel_err(got.cpu(), want)
+    print(f"measured {prec}: one-step {err[:, 0].max().item():.3e}  p90 over the horizon {_p90(err):.3e}")
+    assert err[:, 0].max().item() <= one_step and _p90(err) <= p90_bound, (err[:, 0].max().item(), _p90(err))

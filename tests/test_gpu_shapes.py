@@ -119,6 +119,27 @@ def test_resident_mlp_kernel_instances(hidden, rt, ks, gold_stats):
     _check("mlp", hidden, 2, 0, n, 4, tune, False, False, do_drop=True, gold_stats=gold_stats, seed=3 * hidden + rt + ks)
 
 
+@pytest.mark.parametrize("n,h", [(1, 1), (127, 3), (128, 2), (129, 5), (1000, 7), (40000, 3)])
+def test_two_group_mlp_kernel_bitwise_equal(n, h, gold_stats):
+    """rollout_mlp2_kernel<64,8,8,1,2> (two independent 128-trajectory groups per CTA, tune kc = 4) == the one-group kernel
+    (kc = 1) == the generic kernel, bit for bit: states, costs, cost-only launch."""
+    import mpcdl
+    from conftest import load_ckpt
+    from mpcdl import _lib, ops, synth
+    m, _ = mpcdl.from_checkpoint_name("Basic_64_4_32", load_ckpt("Basic_64_4_32"), torch.device(DEV))
+    rows = synth.load_rows()
+    init, U = synth.make_inputs(rows, n, h, window=0, seed=31)
+    cost = tuple(c.to(DEV) for c in synth.make_cost(rows, h))
+    init, U, st = init.to(DEV), U.to(DEV), gold_stats[0]
+    p = ops.plan(_lib.MLP, 64, 4, 0, n, h, tune=(8, 0, 0, 4))
+    assert p["variant"] == 2 and p["threads"] == 256 and p["tile_traj"] == 128 and p["grid"] == min((p["ntiles"] + 1) // 2, 148)
+    s2, c2 = m.rollout(init, U, st, cost=cost, tune=(8, 0, 0, 4))
+    s1, c1 = m.rollout(init, U, st, cost=cost, tune=(8, 0, 0, 1))
+    sg, cg = m.rollout(init, U, st, cost=cost, tune=(0, 0, 0, -1))
+    assert torch.isfinite(s2).all() and torch.equal(s2, s1) and torch.equal(c2, c1) and torch.equal(s2, sg) and torch.equal(c2, cg)
+    assert torch.equal(m.rollout(init, U, st, cost=cost, return_states=False, tune=(8, 0, 0, 4))[1], c2)
+
+
 @pytest.mark.parametrize("kind", ["gru", "lstm"])
 @pytest.mark.parametrize("hidden,rt", RNN_TILES)
 def test_rnn_kernel_instances(kind, hidden, rt, gold_stats):

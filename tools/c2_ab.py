@@ -36,7 +36,7 @@ def main():
             idx = torch.arange(n) % init.shape[0]
             init, U = init[idx].contiguous().to(dev), U[idx].contiguous().to(dev)
             cost = tuple(c.to(dev) for c in synth.make_cost(rows, h))
-            for tune in ((), (4, 8, 0, 2), (8, 0, 0, 2), (8, 0, 0, 1)):
+            for tune in ((), (4, 8, 0, 2), (8, 0, 0, 2), (8, 0, 0, 1), (8, 0, 0, 4)):
                 try:
                     p = ops.plan(_lib.MLP, 64, meta["layers"], 0, n, h, tune=tune)
                     fn = lambda: m.rollout(init, U, st, cost=cost, return_states=states, tune=tune)   # noqa: E731

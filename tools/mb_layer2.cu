@@ -9,6 +9,7 @@
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %d\n", cudaGetErrorString(e), __LINE__); exit(1); } } while (0)
 constexpr int HID = 64;
+__constant__ float Wc[HID * HID + HID];      // CONSTW variants: the layer's weights as constant-bank operands
 
 __device__ __forceinline__ uint64_t pack2(float lo, float hi) { uint64_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
 __device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
@@ -23,7 +24,8 @@ template <int RT> __device__ __forceinline__ void lda(float (&d)[RT], const floa
     for (int c = 0; c < RT / 4; ++c) { float4 v = *reinterpret_cast<const float4*>(p + c * hs); d[4 * c] = v.x; d[4 * c + 1] = v.y; d[4 * c + 2] = v.z; d[4 * c + 3] = v.w; }
 }
 
-// PACKED = 1: FFMA2 over column pairs, 0: scalar FFMA.  INPLACE: one activation buffer.
+// PACKED = 1: FFMA2 over column pairs, 0: scalar FFMA, 2: scalar FFMA with the weights read from the constant bank at a
+// warp-uniform index (no shared-memory -> register fill for the weight operand).  INPLACE: one activation buffer.
 template <int RT, int RJ, int UNR, int PACKED, int INPLACE>
 __global__ void __launch_bounds__(256) k_layer(float* out, int iters, int TN, long long* cyc) {
     extern __shared__ __align__(16) float sm[];
@@ -52,7 +54,18 @@ __global__ void __launch_bounds__(256) k_layer(float* out, int iters, int TN, lo
         }
         const float* ap = in + tg * 4;
         const float* wp = W + jg * RJ;
-        if (PACKED) {
+        if (PACKED == 2) {
+            const int jgu = __shfl_sync(0xffffffffu, jg, 0) * RJ;         // warp-uniform (n_tg is a multiple of 32)
+#pragma unroll UNR
+            for (int k = 0; k < HID; ++k) {
+                float a[RT];
+                lda<RT>(a, ap + k * TN, hs);
+#pragma unroll
+                for (int i = 0; i < RT; ++i)
+#pragma unroll
+                    for (int r = 0; r < RJ; ++r) acc[i][r] = fmaf(a[i], Wc[k * HID + jgu + r], acc[i][r]);
+            }
+        } else if (PACKED) {
             uint64_t pa[RT][RP];
 #pragma unroll
             for (int i = 0; i < RT; ++i)
@@ -120,13 +133,15 @@ template <int RT, int RJ, int UNR, int PACKED, int INPLACE> static void run(int 
     long long m = 0; for (int i = 0; i < n_sm; ++i) if (h[i] > m) m = h[i];
     double cpl = (double)m / iters;
     printf("TN %3d tile %2dx%-2d unr %2d %s %s thr %3d regs %3d : %8.1f cyc/layer  %6.1f FMA/clk/SM  (%.3f of 128)\n", TN, RT, RJ, UNR,
-           PACKED ? "FFMA2" : "FFMA ", INPLACE ? "inplace" : "pingpong", threads, fa.numRegs, cpl, (double)TN * HID * HID / cpl,
+           PACKED == 2 ? "CONSTW" : PACKED ? "FFMA2" : "FFMA ", INPLACE ? "inplace" : "pingpong", threads, fa.numRegs, cpl, (double)TN * HID * HID / cpl,
            (double)TN * HID * HID / cpl / 128.0);
 }
 
 int main() {
     cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, 0)); n_sm = p.multiProcessorCount;
     CK(cudaMalloc(&d_out, 16 << 20)); CK(cudaMalloc(&d_cyc, 1024 * sizeof(long long)));
+    { static float h[HID * HID + HID]; for (int i = 0; i < HID * HID + HID; ++i) h[i] = ((i * 37) % 101 - 50) * 2e-3f; CK(cudaMemcpyToSymbol(Wc, h, sizeof(h))); }
+    run<8, 8, 8, 2, 0>(256);  run<8, 8, 16, 2, 0>(256); run<8, 8, 8, 2, 0>(128); run<16, 8, 8, 2, 0>(256);
     run<8, 8, 8, 0, 0>(256);  run<8, 8, 8, 1, 0>(256);  run<8, 8, 4, 1, 0>(256);  run<8, 8, 16, 1, 0>(256);
     run<16, 8, 4, 1, 0>(256); run<16, 8, 8, 1, 0>(256); run<8, 16, 4, 1, 0>(256); run<8, 16, 8, 1, 0>(256);
     run<16, 8, 4, 0, 0>(256); run<8, 16, 4, 0, 0>(256);
