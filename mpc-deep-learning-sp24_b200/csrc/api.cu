@@ -304,7 +304,7 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
                 pl.smem_bytes = mlp2_smem_bytes((int)total, d.hidden, TN, c.ks, c.rt, c.rj, c.ng);
                 if (pl.smem_bytes > SMEM_LIMIT) continue;
                 pl.ntiles = (int)((a.N + TN - 1) / TN);
-                pl.grid = std::min((pl.ntiles + c.ng - 1) / c.ng, num_sms);
+                pl.grid = std::min(pl.ntiles, num_sms);                 // tiles go out group-major: a partial pass spreads over all SMs
                 const double cost = (double)((pl.ntiles + num_sms * c.ng - 1) / (num_sms * c.ng)) * mlp2_cycles(c, TN);
                 if (cost < best2) { best2 = cost; best = pl; found2 = true; }
             }

@@ -152,7 +152,9 @@ __global__ void __launch_bounds__((Mlp2Cfg<HID, RT, RJ, KS>::MAX_THREADS), 1) ro
     const PartDesc& pin = m.parts[0];
     const PartDesc& pout = m.parts[NL + 1];
 
-    for (int tile = blockIdx.x * NG + grp; tile < p.io.ntiles; tile += gridDim.x * NG) {
+    // pass k hands tiles [k NG G, (k+1) NG G) out GROUP-major (G = gridDim.x): a last, partial pass first fills group 0 of every
+    // CTA, and a CTA running one group finishes its tile in 0.6 of the two-group time (131 072 x 50: 4.70 -> 4.26 ms)
+    for (int tile = blockIdx.x + grp * gridDim.x; tile < p.io.ntiles; tile += gridDim.x * NG) {
         long long n = (long long)tile * TN + tid;
         const bool valid = owner && n < p.io.N;
         if (n >= p.io.N) n = p.io.N - 1;

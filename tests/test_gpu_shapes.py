@@ -132,7 +132,7 @@ def test_two_group_mlp_kernel_bitwise_equal(n, h, gold_stats):
     cost = tuple(c.to(DEV) for c in synth.make_cost(rows, h))
     init, U, st = init.to(DEV), U.to(DEV), gold_stats[0]
     p = ops.plan(_lib.MLP, 64, 4, 0, n, h, tune=(8, 0, 0, 4))
-    assert p["variant"] == 2 and p["threads"] == 256 and p["tile_traj"] == 128 and p["grid"] == min((p["ntiles"] + 1) // 2, 148)
+    assert p["variant"] == 2 and p["threads"] == 256 and p["tile_traj"] == 128 and p["grid"] == min(p["ntiles"], 148)
     s2, c2 = m.rollout(init, U, st, cost=cost, tune=(8, 0, 0, 4))
     s1, c1 = m.rollout(init, U, st, cost=cost, tune=(8, 0, 0, 1))
     sg, cg = m.rollout(init, U, st, cost=cost, tune=(0, 0, 0, -1))
