@@ -276,6 +276,8 @@ int make_mc_plan(const mpcdl_rollout_args& a, McPlan& pl, int num_sms) {
     return MPCDL_OK;
 }
 
+static inline bool resident_ring(const Plan& pl) { return pl.resident != 0; }
+
 int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
     const mpcdl_model_desc& d = a.model;
     const bool rnn = d.kind != MPCDL_MLP;
@@ -325,16 +327,27 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
         if (rt > n_jg) continue;                                   // owner threads: TN <= consumer threads
         const int maxc = rnn ? rnn_max_consumers(rt, rj) : mlp_max_consumers();
         const int ntg_max = maxc / n_jg;
-        for (int n_tg = ntg_max; n_tg >= 1; --n_tg) {
+        for (int n_tg = ntg_max; n_tg >= 1; --n_tg)
+        for (int nslots_try = 3; nslots_try >= 2; --nslots_try)          // a 2-slot ring where the third slot would cost tile rows
+        for (int slot_kb = 24; slot_kb >= 16; slot_kb -= 8) {            // 24 KB or 16 KB of weight rows per ring slot
             if (a.tune_ntg && n_tg != a.tune_ntg) continue;
             Plan pl;
             pl.variant = 0; pl.ks = 1; pl.ng = 1;
             pl.rt = rt; pl.rj = rj; pl.n_tg = n_tg; pl.TN = n_tg * rt;
             pl.nct = (n_tg * n_jg + 31) / 32 * 32;
             pl.resident = (!a.tune_nslots && total <= 24576u && n_models_of(a) == 1) ? 1 : 0;   // stacked models stream their own blob per tile
-            int kc_rows = a.tune_kc > 0 ? a.tune_kc : std::max(1, 4096 / width_max);
+            if ((pl.resident || a.tune_nslots) && nslots_try != 3) continue;
+            if ((pl.resident || a.tune_kc > 0 || !rnn) && slot_kb != 16) continue;
+            // rows of K per ring slot, the hidden-deep matrices split into EQUAL chunks: 64 rows as 21 + 21 + 21 + 1 cost a whole
+            // ring hand-off (~700 clocks: wait, release, refill latency) for one row (profiles/r02/c3_sweep.log)
+            int kc_rows = std::max(1, slot_kb * 256 / width_max);
+            if (d.hidden > kc_rows) {
+                const int nch = (d.hidden + kc_rows - 1) / kc_rows;
+                kc_rows = (d.hidden + nch - 1) / nch;
+            }
+            if (a.tune_kc > 0) kc_rows = a.tune_kc;
             pl.slot_floats = std::max(kc_rows * width_max, bias_max);
-            pl.nslots = pl.resident ? 1 : (a.tune_nslots ? a.tune_nslots : 3);
+            pl.nslots = pl.resident ? 1 : (a.tune_nslots ? a.tune_nslots : nslots_try);
             ModelParams m;
             memset(&m, 0, sizeof(m));
             fill_model(m, a, pl, total);
@@ -346,8 +359,24 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
             pl.ntiles = n_models_of(a) * (int)((a.N / n_models_of(a) + pl.TN - 1) / pl.TN);
             pl.grid = std::min(pl.ntiles, num_sms);
             const int rounds = (pl.ntiles + num_sms - 1) / num_sms;
-            const double instr = NGA * rt * rj * (rnn ? (double)G / NGA * 1.0 : 1.0) + (rt + 3) / 4 + (G * rj + 3) / 4;
-            const double cost = rounds * instr * std::max(pl.nct / 128.0, 2.0) * (1.0 + 0.01 * (8 - rt));
+            double cost;
+            if (rnn) {
+                // time of one tile-step in microseconds, fitted to the C3 sweep (GRU 64 x 4, window 4, + noise net, 65 536 x 20 on a
+                // B200): ring hand-offs 0.35 us each, 2.1 us per cell of barriers / activations / head share, and the FMA work at
+                // 0.36 TFLOP/s per SM for 4-row tiles (8-row tiles: 7 consumer warps, 7 % slower per trajectory; 2-row: 1.6 x)
+                const int T = d.window, Lc = d.layers, h = d.hidden;
+                auto chunks = [&](int rows) { return (rows + kc_rows - 1) / kc_rows; };
+                const int recur_frames = a.stateful ? T : T - 1;
+                const double handoffs = Lc * T * 1.0 + T * chunks(8) + (Lc - 1) * T * chunks(h) + Lc * recur_frames * chunks(h) + 1 + chunks(h);
+                const double flop = 2.0 * (T * G * h * 8.0 + (Lc - 1) * T * G * h * (double)h + Lc * recur_frames * G * h * (double)h + 6.0 * h);
+                const double rate = 0.363e6 / (rt == 4 ? 1.0 : rt == 8 ? 1.07 : 1.6);          // FLOP per microsecond per SM
+                const double per_step = (resident_ring(pl) ? 0.0 : handoffs * 0.35) + Lc * T * 2.1 + pl.TN * flop / rate;
+                // two slots expose the refill latency, more so with short chunks (sweep: 112 x 16 KB x 2 slots 26.0 ms, 96 x 24 KB x 2 24.9 ms)
+                cost = rounds * per_step * (nslots_try == 3 ? 1.0 : slot_kb == 24 ? 1.02 : 1.08);
+            } else {
+                const double instr = NGA * rt * rj + (rt + 3) / 4 + (G * rj + 3) / 4;
+                cost = rounds * instr * std::max(pl.nct / 128.0, 2.0) * (1.0 + 0.01 * (8 - rt));
+            }
             if (cost < best_cost) { best_cost = cost; best = pl; found = true; }
         }
     }
