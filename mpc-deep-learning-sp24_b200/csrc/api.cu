@@ -329,7 +329,7 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
         const int ntg_max = maxc / n_jg;
         for (int n_tg = ntg_max; n_tg >= 1; --n_tg)
         for (int nslots_try = 3; nslots_try >= 2; --nslots_try)          // a 2-slot ring where the third slot would cost tile rows
-        for (int slot_kb = 24; slot_kb >= 16; slot_kb -= 8) {            // 24 KB or 16 KB of weight rows per ring slot
+        for (int slot_kb = 32; slot_kb >= 16; slot_kb -= 8) {            // 32, 24 or 16 KB of weight rows per ring slot
             if (a.tune_ntg && n_tg != a.tune_ntg) continue;
             Plan pl;
             pl.variant = 0; pl.ks = 1; pl.ng = 1;
@@ -369,10 +369,16 @@ int make_plan(const mpcdl_rollout_args& a, Plan& best, int num_sms) {
                 const int recur_frames = a.stateful ? T : T - 1;
                 const double handoffs = Lc * T * 1.0 + T * chunks(8) + (Lc - 1) * T * chunks(h) + Lc * recur_frames * chunks(h) + 1 + chunks(h);
                 const double flop = 2.0 * (T * G * h * 8.0 + (Lc - 1) * T * G * h * (double)h + Lc * recur_frames * G * h * (double)h + 6.0 * h);
-                const double rate = 0.363e6 / (rt == 4 ? 1.0 : rt == 8 ? 1.07 : 1.6);          // FLOP per microsecond per SM
+                // 8-row tiles run 1..5 % faster per trajectory than 4-row tiles in the same configuration (LSTM 30.4 / 31.9 ms,
+                // GRU 23.2 / 23.8 ms); an odd number of trajectory groups leaves half a warp idle and misaligns the warps with the
+                // unit groups (stateful C3: 76-trajectory tiles 35.4 ms, 64-trajectory tiles 31.0 ms)
+                // ... but only with all 7 consumer warps the 255-register tile allows: 6 warps 8 %, 4 warps 18 % slower (C3 sweep)
+                const int cw = pl.nct / 32;
+                const double f8 = cw >= 7 ? 0.99 : cw == 6 ? 1.08 : 1.18;       // 0.965 at 65 536, but 1 M x 100 prefers 120-trajectory 4-row tiles (1812 / 1860 ms)
+                const double rate = 0.363e6 / (rt == 4 ? 1.0 : rt == 8 ? f8 : 1.6) / ((n_tg & 1) && n_tg > 1 ? 1.08 : 1.0);          // FLOP per microsecond per SM
                 const double per_step = (resident_ring(pl) ? 0.0 : handoffs * 0.35) + Lc * T * 2.1 + pl.TN * flop / rate;
                 // two slots expose the refill latency, more so with short chunks (sweep: 112 x 16 KB x 2 slots 26.0 ms, 96 x 24 KB x 2 24.9 ms)
-                cost = rounds * per_step * (nslots_try == 3 ? 1.0 : slot_kb == 24 ? 1.02 : 1.08);
+                cost = rounds * per_step * (nslots_try == 3 ? 1.0 : slot_kb >= 24 ? 1.02 : 1.08);
             } else {
                 const double instr = NGA * rt * rj + (rt + 3) / 4 + (G * rj + 3) / 4;
                 cost = rounds * instr * std::max(pl.nct / 128.0, 2.0) * (1.0 + 0.01 * (8 - rt));
