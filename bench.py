@@ -23,7 +23,7 @@ prints one JSON line.
             8..32 B vs 1e3..1e7 FLOP per trajectory-step).  `frac_survey_flop` uses SURVEY 8d's
             figure, which also counts the recurrent GEMM of window frame 0 that a stateless model never runs (h0 = 0)
   workloads (N = 1, default workload only) the same device-timed measurement for every other BASELINE configuration:
-            c2, c3 (fp32 / tf32x3 / tf32), c3s, c4 (bf16, fp32), c5g -- bounded to about a minute
+            c2, c3 (fp32 / tf32x3 / tf32), c3s, c4 (bf16, fp32), c5 on the tcgen05 kernel (tf32x3 / tf32), c5g -- about a minute
   cpu_baseline   oracle port (reference nn.Modules in the python loop, oracle/rollout_ref.py) on the host cores,
             rank 0, N = 1 only, bounded sample
 --impl reference times that same oracle port as the reference arm (the reference is pure Python and /root/reference
@@ -104,7 +104,7 @@ WORKLOADS = {
 }
 # the other BASELINE configurations, measured beside the default one at N = 1: (workload, precision, max timed steps)
 TABLE = [("c2", "fp32", 200), ("c3", "fp32", 5), ("c3", "tf32x3", 10), ("c3", "tf32", 10), ("c3s", "fp32", 5),
-         ("c4", "bf16", 8), ("c4", "fp32", 2), ("c5g", "fp32", 2), ("c5g", "tf32x3", 3)]
+         ("c4", "bf16", 8), ("c4", "fp32", 2), ("c5", "tf32x3", 10), ("c5", "tf32", 10), ("c5g", "fp32", 2), ("c5g", "tf32x3", 3)]
 DTYPE = {"fp32": "f32", "tf32x3": "tf32x3 (3-pass TF32 operands, FP32 accumulate/state)", "tf32": "tf32 (FP32 accumulate/state)",
          "bf16": "bf16 (BF16 gate-GEMM operands, FP32 accumulate / cell state / head / feedback)"}
 

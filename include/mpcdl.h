@@ -253,6 +253,29 @@ typedef struct {
 } mpcdl_resample_args;
 int mpcdl_resample(const mpcdl_resample_args* args, void* stream);
 
+/* ---- Training step of the forward-dynamics MLP ---------------------------------------------------
+ * One launch = one EPOCH of train_model (model_scripts/basic_model.py:100-110) for n_models models at once (one CTA per
+ * model): for every batch of `batch` samples in the order `perm` gives (DataLoader(shuffle=True), the last batch may be
+ * short): forward, nn.L1Loss, backward, torch.optim.Adam step (single-tensor formulas, FP32).  Parameters and both Adam
+ * moments are updated in place; `losses` receives the per-batch loss values.  hidden in {16, 32, 64}, layers 1..8. */
+typedef struct {
+    float* theta;              /* device [n_models, n_params]: Basic_Model.parameters() flattened in torch order          */
+    float* adam_m;             /* device [n_models, n_params] exp_avg                                                    */
+    float* adam_v;             /* device [n_models, n_params] exp_avg_sq                                                 */
+    const float* featrs;       /* device [n_rows, 8] z-scored features (RobotData.featrs), shared by the models          */
+    const float* labels;       /* device [n_rows, 6]                                                                     */
+    const int32_t* perm;       /* device [n_models, n_samples] row of every training sample of this epoch, in order      */
+    float* losses;             /* device [n_models, ceil(n_samples / batch)] or NULL                                     */
+    int64_t n_rows;
+    int32_t n_models, n_samples, batch, hidden, layers;
+    int64_t step0;             /* optimizer steps already taken (Adam's bias correction uses step0 + batch index + 1)    */
+    double lr, beta1, beta2, eps;
+} mpcdl_train_args;
+int64_t mpcdl_train_param_count(int32_t hidden, int32_t layers);
+int mpcdl_train_mlp_epoch(const mpcdl_train_args* args, void* stream);
+/* Validation loss of basic_model.py:112-122: losses[i] = L1 loss of batch i of `batch` consecutive rows of output / labels [n,6]. */
+int mpcdl_l1_batches(const float* output, const float* labels, int64_t n, int32_t batch, float* losses, void* stream);
+
 /* Test aid: fills the shared memory of every SM with NaN patterns (one CTA per SM, maximum dynamic shared memory), so a
  * kernel that reads shared memory it has not written shows up as NaN / changed bits in the determinism tests
  * (compute-sanitizer is not available on the GPU pool). */

@@ -987,6 +987,45 @@ int mpcdl_debug_poison_smem(void* stream) {
     return MPCDL_OK;
 }
 
+int64_t mpcdl_train_param_count(int32_t hidden, int32_t layers) {
+    if (hidden < 1 || layers < 0) return 0;
+    return (int64_t)hidden * 8 + hidden + (int64_t)layers * ((int64_t)hidden * hidden + hidden) + 6 * (int64_t)hidden + 6;
+}
+
+int mpcdl_train_mlp_epoch(const mpcdl_train_args* a, void* stream) {
+    if (!a) return fail(MPCDL_ERR_ARG, "args is NULL");
+    if (!a->theta || !a->adam_m || !a->adam_v || !a->featrs || !a->labels || !a->perm)
+        return fail(MPCDL_ERR_ARG, "theta/adam_m/adam_v/featrs/labels/perm must be non-NULL device pointers");
+    if (a->n_models < 1 || a->n_samples < 1 || a->batch < 1 || a->n_rows < 1 || a->step0 < 0)
+        return fail(MPCDL_ERR_ARG, "n_models=%d n_samples=%d batch=%d n_rows=%lld step0=%lld must be positive", a->n_models, a->n_samples, a->batch,
+                    (long long)a->n_rows, (long long)a->step0);
+    if ((a->hidden != 16 && a->hidden != 32 && a->hidden != 64) || a->layers < 1 || a->layers > MAX_LAYERS)
+        return fail(MPCDL_ERR_UNSUPPORTED, "training kernel: hidden=%d (16, 32, 64) layers=%d (1..%d)", a->hidden, a->layers, MAX_LAYERS);
+    if (!(a->lr > 0.0) || !(a->beta1 >= 0.0 && a->beta1 < 1.0) || !(a->beta2 >= 0.0 && a->beta2 < 1.0) || !(a->eps >= 0.0))
+        return fail(MPCDL_ERR_ARG, "Adam hyper-parameters out of range (lr=%g beta1=%g beta2=%g eps=%g)", a->lr, a->beta1, a->beta2, a->eps);
+    const int smem = train_smem_bytes(a->hidden, a->layers);
+    if (smem > SMEM_LIMIT) return fail(MPCDL_ERR_UNSUPPORTED, "training kernel: hidden=%d layers=%d need %d bytes of shared memory", a->hidden, a->layers, smem);
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    TrainParams p;
+    memset(&p, 0, sizeof(p));
+    p.theta = a->theta; p.adam_m = a->adam_m; p.adam_v = a->adam_v; p.featrs = a->featrs; p.labels = a->labels; p.perm = a->perm;
+    p.losses = a->losses; p.n_samples = a->n_samples; p.batch = a->batch; p.hidden = a->hidden; p.layers = a->layers;
+    p.step0 = a->step0; p.lr = a->lr; p.beta1 = a->beta1; p.beta2 = a->beta2; p.eps = a->eps;
+    cudaError_t e = launch_train_mlp(p, a->n_models, smem, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "training kernel launch failed: %s (smem=%d)", cudaGetErrorString(e), smem);
+    return MPCDL_OK;
+}
+
+int mpcdl_l1_batches(const float* output, const float* labels, int64_t n, int32_t batch, float* losses, void* stream) {
+    if (!output || !labels || !losses || n < 1 || batch < 1) return fail(MPCDL_ERR_ARG, "mpcdl_l1_batches: bad arguments");
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    cudaError_t e = launch_l1_batches(output, labels, n, batch, losses, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "l1_batches launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
 int mpcdl_ffma_peak(float* out_device, int iters, int grid, void* stream) {
     if (!out_device || iters < 1 || grid < 1) return fail(MPCDL_ERR_ARG, "mpcdl_ffma_peak: bad arguments");
     cudaError_t e = launch_ffma_peak(out_device, iters, grid, false, static_cast<cudaStream_t>(stream));

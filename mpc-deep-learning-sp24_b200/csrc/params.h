@@ -64,6 +64,20 @@ struct RolloutParams {
     NoiseParams nz;
 };
 
+// fused training epoch of the forward-dynamics MLP (train_kernels.cu; basic_model.py:100-110): one CTA per model
+struct TrainParams {
+    float* theta;            // [n_models][n_params] parameters in torch order (per Linear: weight out x in, bias), in/out
+    float* adam_m;           // [n_models][n_params] exp_avg, in/out
+    float* adam_v;           // [n_models][n_params] exp_avg_sq, in/out
+    const float* featrs;     // [n_rows, 8]  (shared by all models)
+    const float* labels;     // [n_rows, 6]
+    const int* perm;         // [n_models][n_samples] row index of every sample of this epoch, in training order
+    float* losses;           // [n_models][ceil(n_samples / batch)] per-batch L1 loss, or null
+    int n_samples, batch, hidden, layers;
+    long long step0;         // optimizer steps taken before this launch
+    double lr, beta1, beta2, eps;
+};
+
 // standalone noise-net entry points (aux_kernels.cu): forward (H = 1, explicit history) and DynamicsNN closed loop
 struct AuxParams {
     NoiseParams nz;

@@ -385,6 +385,45 @@ std::tuple<Tensor, Tensor> resample(const Tensor& t, const Tensor& q, const Tens
     check_status(mpcdl_resample(&a, at::cuda::getCurrentCUDAStream(dev.index()).stream()));
     return {qo, uo};
 }
+// one epoch of train_model (model_scripts/basic_model.py:100-110) for n_models models in one launch: theta / adam_m / adam_v
+// [n_models, n_params] are updated in place; perm [n_models, n_samples] int32 row order; -> per-batch losses [n_models, n_batches]
+Tensor train_mlp_epoch(Tensor theta, Tensor adam_m, Tensor adam_v, const Tensor& featrs, const Tensor& labels, const Tensor& perm,
+                       int64_t hidden, int64_t layers, int64_t batch, int64_t step0, double lr, double beta1, double beta2, double eps) {
+    TORCH_CHECK(theta.is_cuda(), "mpcdl: theta must be a CUDA tensor (no CPU fallback), got ", theta.device());
+    const c10::Device dev = theta.device();
+    const int64_t np = mpcdl_train_param_count((int32_t)hidden, (int32_t)layers);
+    TORCH_CHECK(theta.dim() == 2 && theta.size(1) == np, "mpcdl: theta must be [n_models, ", np, "] for hidden=", hidden, " layers=", layers, ", got ", theta.sizes());
+    TORCH_CHECK(adam_m.sizes() == theta.sizes() && adam_v.sizes() == theta.sizes(), "mpcdl: adam_m / adam_v must have theta's shape");
+    TORCH_CHECK(featrs.dim() == 2 && featrs.size(1) == 8 && labels.dim() == 2 && labels.size(1) == 6 && labels.size(0) == featrs.size(0),
+                "mpcdl: featrs [n,8] and labels [n,6] expected, got ", featrs.sizes(), " ", labels.sizes());
+    TORCH_CHECK(perm.scalar_type() == at::kInt && perm.is_cuda() && perm.device() == dev && perm.is_contiguous() && perm.dim() == 2 &&
+                perm.size(0) == theta.size(0) && perm.size(1) >= 1, "mpcdl: perm must be a contiguous int32 CUDA tensor [n_models, n_samples]");
+    TORCH_CHECK(batch >= 1 && step0 >= 0, "mpcdl: batch >= 1 and step0 >= 0 expected");
+    mpcdl_train_args a;
+    memset(&a, 0, sizeof(a));
+    a.theta = f32c(theta, "theta", dev); a.adam_m = f32c(adam_m, "adam_m", dev); a.adam_v = f32c(adam_v, "adam_v", dev);
+    a.featrs = f32c(featrs, "featrs", dev); a.labels = f32c(labels, "labels", dev);
+    a.perm = static_cast<const int32_t*>(perm.data_ptr());
+    a.n_rows = featrs.size(0); a.n_models = (int32_t)theta.size(0); a.n_samples = (int32_t)perm.size(1); a.batch = (int32_t)batch;
+    a.hidden = (int32_t)hidden; a.layers = (int32_t)layers; a.step0 = step0; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
+    Tensor losses = at::empty({theta.size(0), (perm.size(1) + batch - 1) / batch}, theta.options());
+    a.losses = static_cast<float*>(losses.data_ptr());
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_train_mlp_epoch(&a, at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return losses;
+}
+// per-batch L1 loss of consecutive batches (the validation loop of basic_model.py:112-122): output / labels [n,6] -> [ceil(n / batch)]
+Tensor l1_batches(const Tensor& output, const Tensor& labels, int64_t batch) {
+    TORCH_CHECK(output.is_cuda(), "mpcdl: output must be a CUDA tensor (no CPU fallback), got ", output.device());
+    const c10::Device dev = output.device();
+    TORCH_CHECK(output.dim() == 2 && output.size(1) == 6 && labels.sizes() == output.sizes() && batch >= 1 && output.size(0) >= 1,
+                "mpcdl: l1_batches needs output and labels [n,6] and batch >= 1");
+    Tensor losses = at::empty({(output.size(0) + batch - 1) / batch}, output.options());
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_l1_batches(f32c(output, "output", dev), f32c(labels, "labels", dev), output.size(0), (int32_t)batch,
+                                  static_cast<float*>(losses.data_ptr()), at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return losses;
+}
 // test aid: NaN-fill the shared memory of every SM of `like`'s device (determinism tests)
 void debug_poison_smem(const Tensor& like) {
     TORCH_CHECK(like.is_cuda(), "mpcdl: debug_poison_smem needs a CUDA tensor to name the device");
@@ -416,6 +455,9 @@ TORCH_LIBRARY(mpcdl, m) {
     m.def("rollout_inputs(Tensor rows, Tensor bag_row_off, Tensor samp_off, int window, int n, int H) -> (Tensor, Tensor, Tensor)");
     m.def("curve_metrics(Tensor pred, Tensor target, Tensor lstat) -> (Tensor, Tensor)");
     m.def("resample(Tensor t, Tensor q, Tensor u, float dataset_dt, int step, int n_interp) -> (Tensor, Tensor)");
+    m.def("train_mlp_epoch(Tensor(a!) theta, Tensor(b!) adam_m, Tensor(c!) adam_v, Tensor featrs, Tensor labels, Tensor perm, int hidden, int layers, "
+          "int batch, int step0, float lr, float beta1, float beta2, float eps) -> Tensor");
+    m.def("l1_batches(Tensor output, Tensor labels, int batch) -> Tensor");
     m.def("debug_poison_smem(Tensor like) -> ()");
 }
 
@@ -433,5 +475,7 @@ TORCH_LIBRARY_IMPL(mpcdl, CUDA, m) {
     m.impl("rollout_inputs", &rollout_inputs);
     m.impl("curve_metrics", &curve_metrics);
     m.impl("resample", &resample);
+    m.impl("train_mlp_epoch", &train_mlp_epoch);
+    m.impl("l1_batches", &l1_batches);
     m.impl("debug_poison_smem", &debug_poison_smem);
 }

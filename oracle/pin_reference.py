@@ -17,6 +17,8 @@ What it does
      (a7), calc_error (a9);
   4. drives the REFERENCE modules in a python loop (closed loop of DESIGN.md) and stores the
      trajectories as golden vectors; checks oracle.rollout_* reproduces them bit-for-bit.
+  5.-7. DynamicsDataset resampling, the second validation pickle + the validation sweep, and the training step
+     (reference Basic_Model + nn.L1Loss + optim.Adam over explicit batches == oracle/train_ref.py, golden train.npz).
 Exit code 0 and "PINNED" on the last line when everything holds.
 """
 from __future__ import annotations
@@ -471,6 +473,50 @@ for pk, pbags, (sm_, sr_), (fm_, lm_), (fr_, lr_) in (("mpc", bags, (mst, rst), 
               f"H50 mae[-1] {float(sweep[f'{pk}/{name}/H50_mae'][-1]):.3f}", ok)
 np.savez_compressed(f"{GOLD}/pid.npz", **pid)
 np.savez_compressed(f"{GOLD}/sweep.npz", **sweep)
+
+# ---------------------------------------------------------------------------- 7. training step (f4)
+# The reference's own Basic_Model class, nn.L1Loss and optim.Adam (basic_model.py:87-110) stepped over explicit batches ==
+# oracle/train_ref.py on the restated module, bit for bit; the per-batch losses and the parameters after 25 steps of 16 are
+# stored as a golden (tests/golden/train.npz) for the GPU kernel's test.
+from oracle import train_ref as TR  # noqa: E402
+
+train_gold = {}
+for hidden_, layers_, batch_ in ((16, 4, 16), (64, 2, 32)):
+    torch.manual_seed(100 + hidden_)
+    ref_t = fwd.Basic_Model(8, hidden_, 6, layers_, False).cpu()
+    mine_t = R.RefBasic(8, hidden_, 6, layers_)
+    mine_t.load_state_dict(ref_t.state_dict())
+    init_flat = torch.cat([p_.detach().reshape(-1) for p_ in ref_t.parameters()]).clone()
+    order_ = torch.randperm(mfn.shape[0], generator=torch.Generator().manual_seed(5))[:25 * batch_ - 3]      # last batch short
+    opt_ref = torch.optim.Adam(ref_t.parameters(), lr=fwd.LEARN_R)
+    crit_ref = torch.nn.L1Loss()
+    ref_t.train()
+    ref_losses = []
+    for b0_ in range(0, len(order_), batch_):                       # the body of basic_model.py:102-110 on explicit batches
+        idx_ = order_[b0_:b0_ + batch_]
+        opt_ref.zero_grad()
+        loss_ = crit_ref(ref_t(ref_ds.featrs.cpu()[idx_]), ref_ds.labels.cpu()[idx_])
+        loss_.backward()
+        opt_ref.step()
+        ref_losses.append(loss_.item())
+    my_losses, _ = TR.train_steps(mine_t, mfn, mln, order_, batch_, fwd.LEARN_R)
+    flat_ref = torch.cat([p_.detach().reshape(-1) for p_ in ref_t.parameters()])
+    flat_mine = torch.cat([p_.detach().reshape(-1) for p_ in mine_t.parameters()])
+    check(f"f4 training: {len(ref_losses)} Adam steps of Basic_{hidden_}_{layers_} (batch {batch_}): oracle == reference class + optimizer (bit), "
+          f"loss {ref_losses[0]:.4f} -> {ref_losses[-1]:.4f}", torch.equal(flat_ref, flat_mine) and torch.equal(torch.tensor(ref_losses), my_losses))
+    tag = f"Basic_{hidden_}_{layers_}_{batch_}"
+    train_gold[f"{tag}/init"], train_gold[f"{tag}/order"] = init_flat.numpy(), order_.numpy()
+    train_gold[f"{tag}/losses"], train_gold[f"{tag}/final"] = np.asarray(ref_losses, dtype=np.float32), flat_ref.numpy()
+vl_ref = 0.0
+with torch.no_grad():
+    ref_t.eval()
+    nb_ = 0
+    for b0_ in range(0, 800, 32):                                   # basic_model.py:112-122 on the first 800 samples
+        vl_ref += crit_ref(ref_t(ref_ds.featrs.cpu()[b0_:b0_ + 32]), ref_ds.labels.cpu()[b0_:b0_ + 32]).item()
+        nb_ += 1
+check("f4 validation loss: oracle == reference loop (bit)", vl_ref / nb_ == TR.validation_loss(mine_t, mfn[:800], mln[:800], 32))
+train_gold["Basic_64_2_32/valid800"] = np.asarray(vl_ref / nb_)
+np.savez_compressed(f"{GOLD}/train.npz", **train_gold)
 
 bad = [n for n, ok in checks if not ok]
 print(f"{len(checks) - len(bad)}/{len(checks)} checks passed")

@@ -147,6 +147,24 @@ def test_tensor_core_plans_and_errors():
             ops.plan(*args, 100, 5, precision="bf16", **kw)
 
 
+def test_training_entry_points_without_device():
+    """mpcdl_train_mlp_epoch / mpcdl_l1_batches: argument checks come before any device work"""
+    from mpcdl import _lib
+    lib = _lib.lib
+    assert lib.mpcdl_train_param_count(64, 4) == 17606 and lib.mpcdl_train_param_count(16, 1) == 518      # SURVEY.md App. B
+    assert lib.mpcdl_train_mlp_epoch(None, None) == -1
+    a = _lib.TrainArgs()
+    assert lib.mpcdl_train_mlp_epoch(C.byref(a), None) == -1 and b"non-NULL" in lib.mpcdl_last_error()
+    for f in ("theta", "adam_m", "adam_v", "featrs", "labels", "perm"):
+        setattr(a, f, 16)
+    a.n_models, a.n_samples, a.batch, a.n_rows, a.hidden, a.layers = 1, 100, 16, 100, 48, 2
+    a.lr, a.beta1, a.beta2, a.eps = 1e-3, 0.9, 0.999, 1e-8
+    assert lib.mpcdl_train_mlp_epoch(C.byref(a), None) == -2 and b"hidden=48" in lib.mpcdl_last_error()   # MPCDL_ERR_UNSUPPORTED
+    a.hidden, a.lr = 64, 0.0
+    assert lib.mpcdl_train_mlp_epoch(C.byref(a), None) == -1 and b"Adam" in lib.mpcdl_last_error()
+    assert lib.mpcdl_l1_batches(None, None, 10, 16, None, None) == -1
+
+
 def test_mppi_entry_points_without_device():
     from mpcdl import _lib
     lib = _lib.lib
@@ -182,7 +200,7 @@ def test_ctypes_mirror_matches_the_compiled_header(tmp_path):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     structs = {"mpcdl_rollout_args": _lib.RolloutArgs, "mpcdl_noise_args": _lib.NoiseArgs, "mpcdl_mppi_args": _lib.MppiArgs,
                "mpcdl_plan": _lib.Plan, "mpcdl_model_desc": _lib.ModelDesc, "mpcdl_dataset_desc": _lib.DatasetDesc,
-               "mpcdl_resample_args": _lib.ResampleArgs}
+               "mpcdl_resample_args": _lib.ResampleArgs, "mpcdl_train_args": _lib.TrainArgs}
     cfield = {"lam": "lambda"}                       # `lambda` is a Python keyword: the mirror calls it lam
     lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "mpcdl.h"', 'int main(void) {']
     for cname, cls in structs.items():

@@ -246,3 +246,29 @@ def test_identity_padding_of_shallow_mlps_is_exact():
         b.load_state_dict(_pad_mlp_state(sd, hid, lay, 4))
         with torch.no_grad():
             assert torch.equal(a(x), b.eval()(x))
+
+
+@pytest.mark.parametrize("tag", ["Basic_16_4_16", "Basic_64_2_32"])
+def test_training_oracle_reproduces_the_reference_made_golden(tag):
+    """oracle/train_ref.py (the reference's loop: L1Loss + Adam over explicit batches) against tests/golden/train.npz, which
+    oracle/pin_reference.py section 7 made with the reference's own Basic_Model class and optimizer: bit for bit."""
+    import os
+    import numpy as np
+    import torch
+    from conftest import GOLD
+    from oracle import rollout_ref as R, train_ref as T
+    g = np.load(os.path.join(GOLD, "train.npz"))
+    hidden, layers, batch = (int(x) for x in tag.split("_")[1:])
+    z = np.load(os.path.join(GOLD, "stats.npz"))
+    from mpcdl import synth
+    f, l = R.mlp_dataset(synth.load_bags())
+    st = {k[4:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("mlp_")}
+    fn, ln = R.apply_zscore(f, l, st)
+    m = R.RefBasic(8, hidden, 6, layers)
+    torch.nn.utils.vector_to_parameters(torch.from_numpy(g[f"{tag}/init"]).clone(), m.parameters())
+    torch.set_num_threads(1)
+    losses, _ = T.train_steps(m, fn, ln, torch.from_numpy(g[f"{tag}/order"]), batch, 1e-3)
+    final = torch.cat([p.detach().reshape(-1) for p in m.parameters()])
+    assert torch.equal(losses, torch.from_numpy(g[f"{tag}/losses"])) and torch.equal(final, torch.from_numpy(g[f"{tag}/final"]))
+    if tag == "Basic_64_2_32":
+        assert T.validation_loss(m, fn[:800], ln[:800], 32) == float(g[f"{tag}/valid800"])
