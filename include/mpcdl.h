@@ -276,6 +276,14 @@ int mpcdl_train_mlp_epoch(const mpcdl_train_args* args, void* stream);
 /* Validation loss of basic_model.py:112-122: losses[i] = L1 loss of batch i of `batch` consecutive rows of output / labels [n,6]. */
 int mpcdl_l1_batches(const float* output, const float* labels, int64_t n, int32_t batch, float* losses, void* stream);
 
+/* ---- rosbag2 CDR decode ----------------------------------------------------------------------------
+ * The `messages.data` blobs of one topic of a rosbag2 sqlite3 file (data/rosbags.py:100-124 fetches them; the reference
+ * hands them to rclpy's deserialize_message with mpclab_msgs/msg/VehicleStateMsg) decoded on the device: blob = the
+ * messages back to back (each with its 4-byte CDR encapsulation header), offsets [n + 1] their byte offsets.
+ * out [n, 9] float64 = [t, x.x, x.y, e.psi, w.w_psi, v.v_long, v.v_tran, u.u_a, u.u_steer] (the fields
+ * scripts/setup_data.py:70-80 keeps, + the sort key t); status [n] int32: 0 ok, 1 truncated / not little-endian CDR. */
+int mpcdl_cdr_decode(const uint8_t* blob, const int64_t* offsets, int64_t n, double* out, int32_t* status, void* stream);
+
 /* Test aid: fills the shared memory of every SM with NaN patterns (one CTA per SM, maximum dynamic shared memory), so a
  * kernel that reads shared memory it has not written shows up as NaN / changed bits in the determinism tests
  * (compute-sanitizer is not available on the GPU pool). */

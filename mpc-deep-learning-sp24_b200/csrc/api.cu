@@ -987,6 +987,15 @@ int mpcdl_debug_poison_smem(void* stream) {
     return MPCDL_OK;
 }
 
+int mpcdl_cdr_decode(const uint8_t* blob, const int64_t* offsets, int64_t n, double* out, int32_t* status, void* stream) {
+    if (!blob || !offsets || !out || !status || n < 1) return fail(MPCDL_ERR_ARG, "mpcdl_cdr_decode: blob/offsets/out/status must be non-NULL device pointers and n >= 1");
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    cudaError_t e = launch_cdr_decode(blob, reinterpret_cast<const long long*>(offsets), n, out, status, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "cdr_decode launch failed: %s", cudaGetErrorString(e));
+    return MPCDL_OK;
+}
+
 int64_t mpcdl_train_param_count(int32_t hidden, int32_t layers) {
     if (hidden < 1 || layers < 0) return 0;
     return (int64_t)hidden * 8 + hidden + (int64_t)layers * ((int64_t)hidden * hidden + hidden) + 6 * (int64_t)hidden + 6;

@@ -48,6 +48,7 @@ cudaError_t launch_rollout_inputs(const DatasetParams& d, int H, float* init, fl
 cudaError_t launch_curve_metrics(const float* pred, const float* target, const float* lstat, int n_models, long long n, int H,
                                  float* mae, float* rmse, cudaStream_t st);
 cudaError_t launch_resample(const ResampleParams& p, cudaStream_t st);
+cudaError_t launch_cdr_decode(const unsigned char* blob, const long long* offsets, long long n, double* out, int* status, cudaStream_t st);
 int train_smem_bytes(int hidden, int layers);
 cudaError_t launch_train_mlp(const TrainParams& p, int n_models, int smem_bytes, cudaStream_t st);
 cudaError_t launch_l1_batches(const float* output, const float* labels, long long n, int batch, float* losses, cudaStream_t st);

@@ -424,6 +424,22 @@ Tensor l1_batches(const Tensor& output, const Tensor& labels, int64_t batch) {
                                   static_cast<float*>(losses.data_ptr()), at::cuda::getCurrentCUDAStream(dev.index()).stream()));
     return losses;
 }
+// rosbag2 CDR decode: blob uint8 [bytes], offsets int64 [n + 1] -> (rows float64 [n, 9] = [t, x, y, psi, w_psi, v_long, v_tran, u_a, u_steer],
+// status int32 [n])
+std::tuple<Tensor, Tensor> cdr_decode(const Tensor& blob, const Tensor& offsets) {
+    TORCH_CHECK(blob.is_cuda(), "mpcdl: blob must be a CUDA tensor (no CPU fallback), got ", blob.device());
+    const c10::Device dev = blob.device();
+    TORCH_CHECK(blob.scalar_type() == at::kByte && blob.is_contiguous() && blob.dim() == 1, "mpcdl: blob must be a contiguous uint8 vector");
+    TORCH_CHECK(offsets.scalar_type() == at::kLong && offsets.is_cuda() && offsets.device() == dev && offsets.is_contiguous() && offsets.dim() == 1 &&
+                offsets.numel() >= 2, "mpcdl: offsets must be a contiguous int64 CUDA vector [n + 1] on the blob's device");
+    const int64_t n = offsets.numel() - 1;
+    Tensor rows = at::empty({n, 9}, blob.options().dtype(at::kDouble)), status = at::empty({n}, blob.options().dtype(at::kInt));
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_cdr_decode(static_cast<const uint8_t*>(blob.data_ptr()), static_cast<const int64_t*>(offsets.data_ptr()), n,
+                                  static_cast<double*>(rows.data_ptr()), static_cast<int32_t*>(status.data_ptr()),
+                                  at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return {rows, status};
+}
 // test aid: NaN-fill the shared memory of every SM of `like`'s device (determinism tests)
 void debug_poison_smem(const Tensor& like) {
     TORCH_CHECK(like.is_cuda(), "mpcdl: debug_poison_smem needs a CUDA tensor to name the device");
@@ -458,6 +474,7 @@ TORCH_LIBRARY(mpcdl, m) {
     m.def("train_mlp_epoch(Tensor(a!) theta, Tensor(b!) adam_m, Tensor(c!) adam_v, Tensor featrs, Tensor labels, Tensor perm, int hidden, int layers, "
           "int batch, int step0, float lr, float beta1, float beta2, float eps) -> Tensor");
     m.def("l1_batches(Tensor output, Tensor labels, int batch) -> Tensor");
+    m.def("cdr_decode(Tensor blob, Tensor offsets) -> (Tensor, Tensor)");
     m.def("debug_poison_smem(Tensor like) -> ()");
 }
 
@@ -477,5 +494,6 @@ TORCH_LIBRARY_IMPL(mpcdl, CUDA, m) {
     m.impl("resample", &resample);
     m.impl("train_mlp_epoch", &train_mlp_epoch);
     m.impl("l1_batches", &l1_batches);
+    m.impl("cdr_decode", &cdr_decode);
     m.impl("debug_poison_smem", &debug_poison_smem);
 }

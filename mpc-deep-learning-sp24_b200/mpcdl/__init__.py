@@ -3,7 +3,7 @@
 Importing the package loads libmpcdl.so (ctypes) and registers torch.ops.mpcdl.*; it raises if the
 library has not been built (no fallback).
 """
-from . import _lib, ops, pack, data, data_utils, synth, parallel, train  # noqa: F401
+from . import _lib, ops, pack, data, data_utils, synth, parallel, train, rosbags  # noqa: F401
 from .models import (Basic_Model, GRU_Model, LSTM_Model, FeedforwardNoiseModel, build_mlp,   # noqa: F401
                      CasadiDynamicCLBicycleNoise, DynamicsNN, from_checkpoint_name, load_model)
 from .data import RobotData, zscore_stats              # noqa: F401

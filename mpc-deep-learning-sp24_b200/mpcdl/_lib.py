@@ -124,7 +124,7 @@ class Plan(C.Structure):
 EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_pack_mlp_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
            "mpcdl_rollout", "mpcdl_rollout_scratch_bytes", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_ffma2_peak", "mpcdl_last_error", "mpcdl_version",
            "mpcdl_dataset_stats", "mpcdl_dataset_build", "mpcdl_rollout_inputs", "mpcdl_curve_metrics", "mpcdl_resample",
-           "mpcdl_train_param_count", "mpcdl_train_mlp_epoch", "mpcdl_l1_batches",
+           "mpcdl_train_param_count", "mpcdl_train_mlp_epoch", "mpcdl_l1_batches", "mpcdl_cdr_decode",
            "mpcdl_debug_poison_smem")
 
 
@@ -175,6 +175,8 @@ def _load():
     lib.mpcdl_train_mlp_epoch.argtypes = [C.POINTER(TrainArgs), C.c_void_p]
     lib.mpcdl_l1_batches.restype = C.c_int
     lib.mpcdl_l1_batches.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.mpcdl_cdr_decode.restype = C.c_int
+    lib.mpcdl_cdr_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.mpcdl_ffma2_peak.restype = C.c_int
     lib.mpcdl_ffma2_peak.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.mpcdl_dataset_stats.restype = C.c_int

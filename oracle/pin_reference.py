@@ -518,6 +518,39 @@ check("f4 validation loss: oracle == reference loop (bit)", vl_ref / nb_ == TR.v
 train_gold["Basic_64_2_32/valid800"] = np.asarray(vl_ref / nb_)
 np.savez_compressed(f"{GOLD}/train.npz", **train_gold)
 
+# ---------------------------------------------------------------------------- 8. rosbag2 CDR decode (f4) -- fixture + consistency
+# The deserialiser of the reference (rclpy + mpclab_msgs) is absent, so nothing here is a parity pin (oracle/cdr_ref.py
+# says so); this section exports one shipped bag as a fixture and checks what CAN be checked against the reference's own
+# files: message sizes, header.stamp == t, the 20 ms period, metadata.yaml's message count, setup_data's cut.
+import sqlite3  # noqa: E402
+import yaml  # noqa: E402
+from oracle import cdr_ref as CDR  # noqa: E402
+
+bag_dir = f"{REF}/data/rosbags/DAgger_827"
+con = sqlite3.connect(f"file:{bag_dir}/DAgger_827_GPS_0.db3?mode=ro", uri=True)
+raw = con.execute("SELECT TIMESTAMP, DATA FROM MESSAGES ORDER BY ID").fetchall()
+meta_y = yaml.safe_load(open(f"{bag_dir}/metadata.yaml"))["rosbag2_bagfile_information"]
+check("f4 cdr: message count == metadata.yaml, type VehicleStateMsg, serialization cdr",
+      len(raw) == meta_y["message_count"] and meta_y["topics_with_message_count"][0]["topic_metadata"]["type"] == "mpclab_msgs/msg/VehicleStateMsg"
+      and meta_y["topics_with_message_count"][0]["topic_metadata"]["serialization_format"] == "cdr")
+msgs_d = [CDR.decode(d) for _, d in raw]
+ts = np.array([m_["t"] for m_ in msgs_d])
+stamp = np.array([m_["header"]["stamp"]["sec"] + 1e-9 * m_["header"]["stamp"]["nanosec"] for m_ in msgs_d])
+check("f4 cdr: every message 468 bytes, t == header.stamp to 1 us, period 20 ms (median within 1 ms, jitter < 15 ms), recorder timestamps follow t",
+      all(len(d) == 468 for _, d in raw) and np.abs(ts - stamp).max() < 1e-6 and abs(np.median(np.diff(ts)) - 0.02) < 1e-3 and np.abs(np.diff(ts) - 0.02).max() < 15e-3
+      and np.abs(np.array([t_ for t_, _ in raw]) * 1e-9 - ts).max() < 0.1)
+rows9 = np.array([CDR.row9(m_) for m_ in msgs_d])
+check("f4 cdr: decoded fields inside the ranges of the validation pickles (BARC track, speeds, controls)",
+      np.abs(rows9[:, 1:3]).max() < 10 and np.abs(rows9[:, 5]).max() < 6 and np.abs(rows9[:, 7]).max() <= 2.0 and np.abs(rows9[:, 8]).max() <= 0.5)
+vals = [float(i) + 0.25 for i in range(34)]
+enc = CDR.encode(vals, ("", "", ""))
+check("f4 cdr: the independent CDR writer with empty frame_ids reproduces the shipped layout (468 bytes, same offsets)",
+      len(enc) == 468 and CDR.row9(CDR.decode(enc)) == [vals[i] for i in CDR.ROW_OF_VALS])
+clean = CDR.setup_data({"DAgger_827": dict(enumerate(msgs_d))})
+check("f4 setup_data restatement: sorted by t, last second dropped", len(clean[0]) == int((ts <= ts.max() - 1.0).sum()) and clean[0][0] == rows9[np.argsort(ts, kind="stable")[0], 1:].tolist())
+np.savez_compressed(f"{GOLD}/cdr_bag.npz", blobs=np.frombuffer(b"".join(d for _, d in raw), dtype=np.uint8).reshape(len(raw), 468),
+                    timestamps=np.array([t_ for t_, _ in raw], dtype=np.int64), rows9=rows9, clean=np.asarray(clean[0]))
+
 bad = [n for n, ok in checks if not ok]
 print(f"{len(checks) - len(bad)}/{len(checks)} checks passed")
 print("PINNED" if not bad else "NOT PINNED: " + "; ".join(bad))
