@@ -79,6 +79,9 @@ struct TcCtl {
     int li_it = 0, li_t = 0, li_l = 0, li_f = 0, li_part = 0, li_c = 0;   // load iterator
     bool li_done;
     int my_tiles, H;
+    // alias mode: loads of step s > 0 (tile-major step index) wait until the owner threads released the ring after step s - 1
+    uint64_t* ring_free = nullptr;
+    uint32_t gate_done = 0;
 
     __device__ TcCtl(const TcModel& m_, float* ring_, uint64_t* full_, uint64_t* empty_, int my_tiles_, int H_)
         : m(m_), ring(ring_), full(full_), empty(empty_), my_tiles(my_tiles_), H(H_) {
@@ -110,6 +113,15 @@ struct TcCtl {
     // issued when their slot is already free, so MMA issue never stalls behind MMAs that are still in flight.
     __device__ void top_up(uint32_t need) {
         while (!li_done && outstanding < (uint32_t)m.nslots) {
+            if (ring_free) {
+                const uint32_t step = (uint32_t)(li_it * H + li_t);
+                if (step > gate_done) {
+                    const uint32_t par = (step - 1u) & 1u;
+                    if (need != 0xFFFFFFFFu && ld_count <= need) mbar_wait(ring_free, par);
+                    else if (!mbar_try_wait(ring_free, par)) break;
+                    gate_done = step;
+                }
+            }
             if (ld_wrapped) {
                 if (need != 0xFFFFFFFFu && ld_count <= need) mbar_wait(&empty[ld_slot], ld_par);
                 else if (!mbar_try_wait(&empty[ld_slot], ld_par)) break;
@@ -174,7 +186,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
     constexpr int T = TC_T, HID = TC_HID, TN = TC_TN;
     extern __shared__ __align__(1024) float sm[];
     const TcModel& m = p.m;
-    const TcSmem L = tc_layout(m.nslots, m.slot_floats, m.layers, T, p.nz);
+    const bool alias = m.noise_alias != 0 && p.nz.enabled;     // noise-net buffers inside the weight ring (tc_params.h)
+    const TcSmem L = tc_layout(m.nslots, m.slot_floats, m.layers, T, p.nz, alias);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int H = p.io.H, NL = m.layers;
     const long long N = p.io.N;
@@ -185,11 +198,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
     uint64_t* opnd_ready = empty + TC_MAX_SLOTS;
     uint64_t* acc_ready = opnd_ready + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_ready + 1);
+    uint64_t* ring_free = acc_ready + 2;         // alias mode: the owner threads are done with the noise buffers of a step
 
     if (tid == 0) {
         for (int i = 0; i < m.nslots; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
         mbar_init(opnd_ready, TC_EPI_THREADS);
         mbar_init(acc_ready, 1);
+        mbar_init(ring_free, TC_TN);
         mbar_fence_init();
     }
     if (warp == 8) { umma::tmem_alloc(tmem_slot, 512); umma::tmem_relinquish(); }
@@ -204,7 +219,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
     }
     for (int i = tid; i < HID * 8 + 8; i += blockDim.x) sm[L.fc + i] = m.blob[m.fc_off + i];
     for (int i = tid; i < 2 * T * 8 + 12; i += blockDim.x) sm[L.norm + i] = p.io.norm[i];
-    if (p.nz.enabled)
+    if (p.nz.enabled && !alias)
         for (int i = tid; i < p.nz.blob_floats; i += blockDim.x) sm[L.nblob + i] = p.nz.blob[i];
     umma::fence_before_sync();
     __syncthreads();
@@ -217,6 +232,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == 8 && lane == 0) {
             TcCtl c(m, sm + L.ring, full, empty, my_tiles, H);
+            if (alias) c.ring_free = ring_free;
             uint32_t use_count = 0, cellpar = 0;
             uint32_t us = 0, up = 0;                         // slot / full-barrier parity of the next chunk to use
             const uint32_t ring_s = smem_u32(sm + L.ring);

@@ -58,7 +58,7 @@
             if (owner) {
                 float2 uu = load_control(p.io, n, t);
                 u[0] = uu.x; u[1] = uu.y;
-                if (p.nz.enabled) {                    // newest frame feeds the noise history
+                if (p.nz.enabled && !alias) {          // newest frame feeds the noise history
                     int pf = base + T - 1; if (pf >= T) pf -= T;
                     float s[6], uf[2];
 #pragma unroll
@@ -206,6 +206,25 @@
 #pragma unroll
                 for (int d = 0; d < 6; ++d) ypart[(uh * 8 + d) * TN + row] = y[d];
             }
+            if (alias) {
+                // The noise net's buffers alias the weight ring: every MMA of this step is complete (acc_ready of the last cell)
+                // and the control thread loads nothing for the next step before ring_free.  Weights are re-read (9 KB, L2) and the
+                // history is REBUILT from the window buffer: entry e (0 = oldest) of noise_model.py:95-99's deques at step t is
+                // window frame max(T - hist + e, T - 1 - t) -- the first push left-pads with copies of the then-newest frame.
+                for (int i = tid; i < p.nz.blob_floats; i += TC_EPI_THREADS) sm[L.nblob + i] = __ldg(p.nz.blob + i);
+                if (owner) {
+                    const int hist = p.nz.hist;
+                    for (int e = 0; e < hist; ++e) {
+                        int fe = T - hist + e;
+                        if (fe < T - 1 - t) fe = T - 1 - t;
+                        int pf = base + fe; if (pf >= T) pf -= T;
+#pragma unroll
+                        for (int i = 0; i < 6; ++i) nin[(e * 6 + i) * TN + row] = xwin[(pf * 8 + q_perm(i)) * TN + row];
+                        nin[(6 * hist + e * 2) * TN + row] = xwin[(pf * 8 + 6) * TN + row];
+                        nin[(6 * hist + e * 2 + 1) * TN + row] = xwin[(pf * 8 + 7) * TN + row];
+                    }
+                }
+            }
             named_bar_sync(1, TC_EPI_THREADS);
             if (p.nz.enabled) {                        // residual-noise net on the CUDA cores (noise_model.py:34-40)
                 const float* W = sm + L.nblob;
@@ -230,6 +249,7 @@
 #pragma unroll
                 for (int k = 0; k < 6; ++k) d[k * TN] = nxt[k];
                 d[6 * TN] = u[0]; d[7 * TN] = u[1];
+                if (alias) mbar_arrive(ring_free);     // this row's noise outputs are consumed: the ring may be refilled
             }
             base = base + 1 == T ? 0 : base + 1;
         }

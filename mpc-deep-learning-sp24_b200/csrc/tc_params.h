@@ -34,6 +34,8 @@ struct TcModel {
     int cell, prec, layers, window, stateful;
     int nslots, slot_floats, resident; // ring geometry; resident = a layer's chunks stay for all T frames
     int group;                         // 16-row weight chunks per ring slot (1, 2 or 4): one TMA/issue unit
+    int noise_alias;                   // the residual-noise net's buffers live INSIDE the weight ring (resident mode): at the end of a
+                                       // step every slot is dead until the next step's layer 0 is loaded, see tc_layout
 };
 
 struct TcRolloutParams {
@@ -46,7 +48,12 @@ struct TcSmem {       // float offsets
     int bars, ring, bias, fc, norm, xwin, ypart, ybuf, nblob, nin, nact0, nact1, nzb, total;
 };
 
-__host__ __device__ inline TcSmem tc_layout(int nslots, int slot_floats, int layers, int window, const NoiseParams& nz) {
+// alias: the noise net's weights, inputs, activations and outputs (59 KB for the default net) are carved out of the ring
+// instead of their own region, which is what lets a layer's tf32x3 weights (196 KB) stay resident with the noise net on.
+__host__ __device__ inline int tc_noise_floats(const NoiseParams& nz) {
+    return nz.enabled ? align_up(nz.blob_floats, 4) + (nz.in_dim + 2 * nz.size + 12) * TC_TN : 0;
+}
+__host__ __device__ inline TcSmem tc_layout(int nslots, int slot_floats, int layers, int window, const NoiseParams& nz, bool alias = false) {
     TcSmem L;
     int o = 0;
     L.bars = o;   o += 64;                                   // full[16] empty[16]... as uint64 + tmem ptr: 256 B
@@ -59,12 +66,14 @@ __host__ __device__ inline TcSmem tc_layout(int nslots, int slot_floats, int lay
     L.xwin = o;   o += window * 8 * TC_TN;
     L.ypart = o;  o += 2 * 8 * TC_TN;
     L.ybuf = o;   o += 8 * TC_TN;
+    const int end = o;
+    if (alias) o = L.ring;
     L.nblob = o;  o += nz.enabled ? align_up(nz.blob_floats, 4) : 0;
     L.nin = o;    o += nz.enabled ? nz.in_dim * TC_TN : 0;
     L.nact0 = o;  o += nz.enabled ? nz.size * TC_TN : 0;
     L.nact1 = o;  o += nz.enabled ? nz.size * TC_TN : 0;
     L.nzb = o;    o += nz.enabled ? 12 * TC_TN : 0;
-    L.total = o;
+    L.total = alias ? end : o;
     return L;
 }
 constexpr int TC_MAX_SLOTS = 12;

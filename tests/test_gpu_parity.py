@@ -266,3 +266,31 @@ def test_tensor_core_rejects_unsupported():
         g.rollout(torch.zeros(8, 3, 8, device=_dev()), torch.zeros(8, 3, 2, device=_dev()), None, precision="tf32")
     with pytest.raises(RuntimeError):
         g.rollout(torch.zeros(8, 4, 8, device=_dev()), torch.zeros(8, 3, 2, device=_dev()), None, precision="bf16")
+
+
+@pytest.mark.parametrize("prec", ["tf32x3", "tf32"])
+@pytest.mark.parametrize("n,h", [(1, 1), (129, 3), (300, 9)])
+def test_tensor_core_noise_buffers_inside_the_ring(prec, n, h, gold_stats):
+    """GRU + residual-noise net on the tcgen05 kernel: with the noise net's buffers aliased into the weight ring (what makes a
+    tf32x3 layer resident, api.cu make_tc_plan) the result equals the streaming launch (tune nslots = -1: own noise region,
+    history pushed step by step) bit for bit -- the history rebuilt from the window buffer is the deque of
+    noise_model.py:95-99, including the left-padding of the first steps."""
+    import mpcdl
+    from mpcdl import _lib, ops, synth
+    m, _ = mpcdl.from_checkpoint_name("GRU_64_4_4_16_False", load_ckpt("GRU_64_4_4_16_False"), _dev())
+    noise = mpcdl.FeedforwardNoiseModel(6, 2, 3, n_layers=2, size=32, activation="tanh", output_activation="identity")
+    noise.model.load_state_dict(load_ckpt("noise_seed0_h3_s32_l2"))
+    noise.to(_dev())
+    st = gold_stats[1]
+    init, U = synth.make_inputs(synth.load_rows(), n, h, window=4, seed=17)
+    eps = synth.make_eps(n, h, seed=6).to(_dev())
+    cost = tuple(c.to(_dev()) for c in synth.make_cost(synth.load_rows(), h))
+    init, U = init.to(_dev()), U.to(_dev())
+    pa = ops.plan(_lib.GRU, 64, 4, 4, n, h, noise_cfg=noise.cfg(), precision=prec)
+    ps = ops.plan(_lib.GRU, 64, 4, 4, n, h, noise_cfg=noise.cfg(), precision=prec, tune=(0, 0, -1, 0))
+    if prec == "tf32x3":
+        assert pa["resident"] == 1 and ps["resident"] == 0 and pa["smem_bytes"] <= 232448
+    for kw in (dict(eps=eps), dict(seed=9)):
+        a = m.rollout(init, U, st, noise=noise, cost=cost, precision=prec, **kw)
+        b = m.rollout(init, U, st, noise=noise, cost=cost, precision=prec, tune=(0, 0, -1, 0), **kw)
+        assert torch.isfinite(a[0]).all() and torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
