@@ -26,10 +26,11 @@ extern "C" {
 
 enum { MPCDL_MLP = 0, MPCDL_GRU = 1, MPCDL_LSTM = 2 };
 /* Arithmetic of the gate GEMMs.  FP32 = FFMA kernels (the parity path, <= 1e-5 one-step).  The tensor-core
- * modes run the [128 x 64].[64 x 64|192|256] layer / gate contractions on tcgen05 (hidden 64; GRU/LSTM window 4):
+ * modes run the [128 x 64].[64 x 64|192|256] layer / gate contractions on tcgen05 (hidden 64; GRU/LSTM window 4 or 8,
+ * window 8 needs the device scratch):
  * TF32X3 = three TF32 passes on hi/lo split operands (FP32-class accuracy, bound stated in DESIGN.md 5),
  * TF32 = one TF32 pass + MUFU.TANH activations.  State, accumulation, statistics and cost stay FP32.
- * BF16 = the wide LSTM (hidden 256, stateless, no noise net): gate GEMMs [128 x 256].[256 x 1024] on
+ * BF16 = the wide LSTM (hidden 256; stateless or stateful, with or without the noise net): gate GEMMs [128 x 256].[256 x 1024] on
  * tcgen05 with BF16 operands, FP32 accumulation, FP32 cell state; needs a device scratch (mpcdl_rollout_scratch_bytes). */
 enum { MPCDL_PREC_FP32 = 0, MPCDL_PREC_TF32X3 = 1, MPCDL_PREC_TF32 = 2, MPCDL_PREC_BF16 = 3 };
 enum { MPCDL_ACT_IDENTITY = 0, MPCDL_ACT_RELU = 1, MPCDL_ACT_TANH = 2, MPCDL_ACT_SIGMOID = 3 };
@@ -118,8 +119,8 @@ typedef struct {
     int32_t sample_controls, shared_init;
     float ctrl_sigma[2], ctrl_lo[2], ctrl_hi[2];
     uint64_t ctrl_seed;
-    /* MPCDL_PREC_BF16 only: device workspace of >= mpcdl_rollout_scratch_bytes(args) bytes (the per-CTA layer output
-     * sequences in BF16 operand layout); borrowed for the duration of the launch, contents undefined afterwards. */
+    /* MPCDL_PREC_BF16, and the TF32 modes with window 8: device workspace of >= mpcdl_rollout_scratch_bytes(args) bytes (the
+     * per-CTA layer output sequences: BF16 operand layout / FP32); borrowed for the duration of the launch, contents undefined afterwards. */
     void* scratch;
     uint64_t scratch_bytes;
     /* Stacked models (validation sweep over several checkpoints of one architecture, model_scripts/eval_models.py:14-65
@@ -139,7 +140,8 @@ typedef struct {
  * (model_scripts/eval_models.py:86). `stream` is a cudaStream_t (NULL = default stream). */
 int mpcdl_rollout(const mpcdl_rollout_args* args, void* stream);
 
-/* Bytes of args->scratch that mpcdl_rollout needs for these args (0 unless precision = MPCDL_PREC_BF16). */
+/* Bytes of args->scratch that mpcdl_rollout needs for these args (0 unless precision = MPCDL_PREC_BF16,
+ * or a TF32 mode with model.window = 8). */
 size_t mpcdl_rollout_scratch_bytes(const mpcdl_rollout_args* args);
 
 /* What mpcdl_rollout would launch for these args (no launch): tile size, grid, smem, config. */

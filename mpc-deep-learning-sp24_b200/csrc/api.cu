@@ -173,7 +173,7 @@ void fill_noise(NoiseParams& nz, const mpcdl_rollout_args& a) {
 
 
 // ---------------------------------------------------------------------------- tensor-core (tcgen05) path
-bool tc_supported(const mpcdl_model_desc& d) { return d.kind != MPCDL_MLP && d.hidden == TC_HID && d.window == TC_T; }
+bool tc_supported(const mpcdl_model_desc& d) { return d.kind != MPCDL_MLP && d.hidden == TC_HID && tc_window_ok(d.window); }
 
 // blob: [bias L*64*4][fc 64*8+8][pad to 32 floats][per layer: x chunks, h chunks]
 uint32_t build_tc_parts(const mpcdl_model_desc& d, TcPart* parts, uint32_t& bias_off, uint32_t& fc_off) {
@@ -220,7 +220,7 @@ int make_tc_plan(const mpcdl_rollout_args& a, TcPlan& pl, int num_sms) {
     const int per_part = TC_HID / TC_KS;
     NoiseParams nz;
     fill_noise(nz, a);
-    int budget = SMEM_LIMIT - tc_layout(0, 0, d.layers, TC_T, nz).total * 4;
+    int budget = SMEM_LIMIT - tc_layout(0, 0, d.layers, d.window, nz).total * 4;
     const int pref_x3[3] = {2, 4, 1}, pref_1[3] = {4, 2, 1};
     const int* pref = x3 ? pref_x3 : pref_1;
     int G = 0, nslots = 0, resident = 0, alias = 0;
@@ -232,10 +232,10 @@ int make_tc_plan(const mpcdl_rollout_args& a, TcPlan& pl, int num_sms) {
     // With the noise net on and no room for a resident layer beside it, keep the layer resident by lending the net the ring itself: at the end of a step
     // all weight slots are dead, so its buffers alias them (the history is rebuilt from the window buffer, which needs
     // history <= window).  C3 tf32x3: 16-row chunks streamed through 5 slots -> 2 matrices resident, 50 -> 33 ms.
-    if (!G && a.tune_kc >= 0 && nz.enabled && nz.hist <= TC_T && a.tune_nslots >= 0) {
+    if (!G && a.tune_kc >= 0 && nz.enabled && nz.hist <= d.window && a.tune_nslots >= 0) {
         NoiseParams none;
         memset(&none, 0, sizeof(none));
-        const int budget_alias = SMEM_LIMIT - tc_layout(0, 0, d.layers, TC_T, none).total * 4;
+        const int budget_alias = SMEM_LIMIT - tc_layout(0, 0, d.layers, d.window, none).total * 4;
         for (int i = 0; i < 3 && !G; ++i) {
             const int g = a.tune_ntg > 0 ? a.tune_ntg : pref[i], ns = std::min<int>(budget_alias / (int)(g * chunk * 4), TC_MAX_SLOTS);
             if (ns >= 2 * per_part / g && (long long)ns * g * chunk >= tc_noise_floats(nz)) { G = g; nslots = ns; resident = 1; alias = 1; }
@@ -250,7 +250,7 @@ int make_tc_plan(const mpcdl_rollout_args& a, TcPlan& pl, int num_sms) {
     if (a.tune_nslots > 0 && a.tune_nslots < nslots && !alias) { nslots = a.tune_nslots; if (nslots < 2 * per_part / G) resident = 0; }
     pl.group = G; pl.nslots = nslots; pl.resident = resident; pl.alias = alias;
     pl.slot_floats = (int)(G * chunk);
-    pl.smem_bytes = std::max(tc_layout(nslots, pl.slot_floats, d.layers, TC_T, nz, alias != 0).total * 4, 120 * 1024);   // > half an SM: one CTA (one TMEM owner) per SM
+    pl.smem_bytes = std::max(tc_layout(nslots, pl.slot_floats, d.layers, d.window, nz, alias != 0).total * 4, 120 * 1024);   // > half an SM: one CTA (one TMEM owner) per SM
     pl.ntiles = (int)((a.N + TC_TN - 1) / TC_TN);
     pl.grid = std::min(pl.ntiles, num_sms);
     return MPCDL_OK;
@@ -460,11 +460,15 @@ int check_args(const mpcdl_rollout_args* a) {
     } else if (a->precision != MPCDL_PREC_FP32) {
         if (a->precision != MPCDL_PREC_TF32X3 && a->precision != MPCDL_PREC_TF32) return fail(MPCDL_ERR_ARG, "unknown precision %d", a->precision);
         if (!tc_supported(a->model) && !mc_supported(a->model))
-            return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core precision needs hidden=%d (GRU/LSTM: window=%d); got kind=%d hidden=%d window=%d; use MPCDL_PREC_FP32",
-                        TC_HID, TC_T, a->model.kind, a->model.hidden, a->model.window);
+            return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core precision needs hidden=%d (GRU/LSTM: window=%d or %d); got kind=%d hidden=%d window=%d; use MPCDL_PREC_FP32",
+                        TC_HID, TC_T, TC_T_LONG, a->model.kind, a->model.hidden, a->model.window);
         if (a->model.kind == MPCDL_MLP && a->noise_wblob)
             return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core MLP rollout has no residual-noise path; use MPCDL_PREC_FP32");
         if (!a->wblob_tc) return fail(MPCDL_ERR_ARG, "tensor-core precision needs wblob_tc (mpcdl_pack_rnn_tc)");
+        const size_t need = mpcdl_rollout_scratch_bytes(a);
+        if (need && (!a->scratch || a->scratch_bytes < need))
+            return fail(MPCDL_ERR_ARG, "tensor-core rollout with window=%d needs a device scratch of %zu bytes (mpcdl_rollout_scratch_bytes), got %llu",
+                        a->model.window, need, (unsigned long long)a->scratch_bytes);
     }
     if (a->n_models > 1) {
         if (a->precision != MPCDL_PREC_FP32 || a->stateful || a->sample_controls || a->shared_init)
@@ -613,7 +617,7 @@ size_t mpcdl_blob_floats_tc(const mpcdl_model_desc* desc) {
     if (check_desc(desc)) return 0;
     if (mc_supported(*desc)) { McModel m; return build_mc_offsets(*desc, true, m); }
     if (lt_supported(*desc)) { LtModel m; return build_lt_offsets(*desc, m); }
-    if (!tc_supported(*desc)) { fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: hidden=%d only (GRU/LSTM: window=%d)", TC_HID, TC_T); return 0; }
+    if (!tc_supported(*desc)) { fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: hidden=%d only (GRU/LSTM: window=%d or %d)", TC_HID, TC_T, TC_T_LONG); return 0; }
     TcPart parts[2 * MAX_LAYERS];
     uint32_t bo, fo;
     return build_tc_parts(*desc, parts, bo, fo);
@@ -625,7 +629,7 @@ int mpcdl_pack_rnn_tc(const mpcdl_model_desc* desc, const float* const* w_ih, co
     if (rc) return rc;
     if (!w_ih || !w_hh || !b_ih || !b_hh || !fc_w || !fc_b || !blob) return fail(MPCDL_ERR_ARG, "mpcdl_pack_rnn_tc: bad arguments");
     if (lt_supported(*desc)) return pack_lt(*desc, w_ih, w_hh, b_ih, b_hh, fc_w, fc_b, blob);
-    if (!tc_supported(*desc)) return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: GRU/LSTM with hidden=%d window=%d, or LSTM hidden=%d, only", TC_HID, TC_T, LT_HID);
+    if (!tc_supported(*desc)) return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core blob: GRU/LSTM with hidden=%d window=%d|%d, or LSTM hidden=%d, only", TC_HID, TC_T, TC_T_LONG, LT_HID);
     TcPart parts[2 * MAX_LAYERS];
     uint32_t bias_off, fc_off;
     const uint32_t total = build_tc_parts(*desc, parts, bias_off, fc_off);
@@ -727,6 +731,11 @@ int mpcdl_pack_noise(int history, int size, int n_layers, const float* const* W,
 }
 
 size_t mpcdl_rollout_scratch_bytes(const mpcdl_rollout_args* a) {
+    if (a && (a->precision == MPCDL_PREC_TF32X3 || a->precision == MPCDL_PREC_TF32) && tc_supported(a->model) && a->N >= 1) {
+        // window 8 on the tcgen05 GRU / LSTM kernel: per-CTA layer output sequences (rollout_rnn_tc_epi.inl)
+        const long long ntiles = (a->N + TC_TN - 1) / TC_TN;
+        return (size_t)std::min<long long>(ntiles, planning_sms()) * tc_seq_bytes_per_cta(a->model.window);
+    }
     if (!a || a->precision != MPCDL_PREC_BF16 || !lt_supported(a->model) || a->N < 1) return 0;
     LtPlan lp;
     make_lt_plan(*a, lp, planning_sms());
@@ -827,6 +836,7 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
         q.m.nslots = tp.nslots; q.m.slot_floats = tp.slot_floats; q.m.resident = tp.resident; q.m.group = tp.group; q.m.noise_alias = tp.alias;
         fill_noise(q.nz, *a);
         fill_io(q.io, *a, tp.ntiles);
+        q.seqbuf = static_cast<float*>(a->scratch);
         cudaError_t e = launch_rnn_tc(q, tp.grid, tp.smem_bytes, st);
         if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "tensor-core kernel launch failed: %s (smem=%d nslots=%d)", cudaGetErrorString(e), tp.smem_bytes, tp.nslots);
         return MPCDL_OK;

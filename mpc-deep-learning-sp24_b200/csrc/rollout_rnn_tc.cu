@@ -179,11 +179,11 @@ __device__ __forceinline__ void issue_groups(int G, uint32_t tbase, uint32_t sb,
     else issue_group<CELL, X3, PART, TC_KS, 1>(tbase, sb, a_hi, a_lo, acc);
 }
 
-template <int CELL, int PREC>
+template <int CELL, int PREC, int T>
 __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __grid_constant__ TcRolloutParams p) {
     constexpr bool X3 = PREC == PREC_TF32X3;
     constexpr bool FAST = PREC == PREC_TF32;
-    constexpr int T = TC_T, HID = TC_HID, TN = TC_TN;
+    constexpr int HID = TC_HID, TN = TC_TN;
     extern __shared__ __align__(1024) float sm[];
     const TcModel& m = p.m;
     const bool alias = m.noise_alias != 0 && p.nz.enabled;     // noise-net buffers inside the weight ring (tc_params.h)
@@ -287,21 +287,27 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
 }
 
 // ------------------------------------------------------------------ launcher
-template <int CELL, int PREC>
+template <int CELL, int PREC, int T>
 static cudaError_t launch_rnn_tc_t(const TcRolloutParams& p, int grid, int smem_bytes, cudaStream_t st) {
-    auto k = rollout_rnn_tc_kernel<CELL, PREC>;
+    auto k = rollout_rnn_tc_kernel<CELL, PREC, T>;
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     if (e != cudaSuccess) return e;
     k<<<grid, TC_THREADS, smem_bytes, st>>>(p);
     return cudaGetLastError();
 }
-
-cudaError_t launch_rnn_tc(const TcRolloutParams& p, int grid, int smem_bytes, cudaStream_t st) {
+template <int T>
+static cudaError_t launch_rnn_tc_w(const TcRolloutParams& p, int grid, int smem_bytes, cudaStream_t st) {
     const bool gru = p.m.cell == CELL_GRU;
     if (p.m.prec == PREC_TF32X3)
-        return gru ? launch_rnn_tc_t<CELL_GRU, PREC_TF32X3>(p, grid, smem_bytes, st) : launch_rnn_tc_t<CELL_LSTM, PREC_TF32X3>(p, grid, smem_bytes, st);
+        return gru ? launch_rnn_tc_t<CELL_GRU, PREC_TF32X3, T>(p, grid, smem_bytes, st) : launch_rnn_tc_t<CELL_LSTM, PREC_TF32X3, T>(p, grid, smem_bytes, st);
     if (p.m.prec == PREC_TF32)
-        return gru ? launch_rnn_tc_t<CELL_GRU, PREC_TF32>(p, grid, smem_bytes, st) : launch_rnn_tc_t<CELL_LSTM, PREC_TF32>(p, grid, smem_bytes, st);
+        return gru ? launch_rnn_tc_t<CELL_GRU, PREC_TF32, T>(p, grid, smem_bytes, st) : launch_rnn_tc_t<CELL_LSTM, PREC_TF32, T>(p, grid, smem_bytes, st);
+    return cudaErrorInvalidConfiguration;
+}
+
+cudaError_t launch_rnn_tc(const TcRolloutParams& p, int grid, int smem_bytes, cudaStream_t st) {
+    if (p.m.window == TC_T) return launch_rnn_tc_w<TC_T>(p, grid, smem_bytes, st);
+    if (p.m.window == TC_T_LONG && p.seqbuf) return launch_rnn_tc_w<TC_T_LONG>(p, grid, smem_bytes, st);
     return cudaErrorInvalidConfiguration;
 }
 

@@ -4,6 +4,10 @@
 // frame loop is a real loop (4x less code than unrolling it): at cell (l, f)
 //   seq[0] = layer l-1 output of frame f (consumed as x, then overwritten by this cell's output)
 //   seq[T-1] = layer l output of frame f-1 (the recurrent input, f > 0)
+// Window 8 (T > TC_T) would need 256 registers for the sequence: there only seq[0] (x, then the output) and seq[1] (the
+// recurrent input) are registers and the sequence goes through p.seqbuf [T][64 units][128 rows] (global memory, L2): a
+// thread stores its 32 units of frame f after the cell and loads the next cell's input -- always words it wrote itself,
+// so no barrier or fence is involved; layer l overwrites frame f only after it has consumed layer l-1's frame f.
 {
     const int q = warp & 3, uh = warp >> 2;
     const int row = q * 32 + lane;
@@ -21,6 +25,9 @@
     const float4* const biasS = reinterpret_cast<const float4*>(sm + L.bias);
     const float* const fcS = sm + L.fc;
     uint32_t cellpar = 0;
+    constexpr bool SCR = T > TC_T;                     // sequence through the global scratch (see the header)
+    constexpr int SR = SCR ? 2 : T;
+    float* const seqb = SCR ? p.seqbuf + (size_t)blockIdx.x * T * HID * TN : nullptr;
     constexpr float C_SIG = FAST ? 0.5f : -1.4426950408889634f;       // pre-activation scale of sigmoid gates
     constexpr float C_TANH = FAST ? 1.0f : 2.8853900817779268f;       // ... of tanh gates (biases pre-scaled alike)
 
@@ -48,9 +55,9 @@
             }
         }
         int base = 0;                                  // physical slot of logical frame 0
-        float seq[T][32];
+        float seq[SR][32];
 #pragma unroll
-        for (int f = 0; f < T; ++f)
+        for (int f = 0; f < SR; ++f)
 #pragma unroll
             for (int j = 0; j < 32; ++j) seq[f][j] = 0.f;
         for (int t = 0; t < H; ++t) {
@@ -102,8 +109,8 @@
                         stage16<X3>(tlane + TC_AX_HI + u0 + 16, tlane + TC_AX_LO + u0 + 16, &seq[0][16]);
                     }
                     if (f > 0) {
-                        stage16<X3>(tlane + TC_AH_HI + u0, tlane + TC_AH_LO + u0, &seq[T - 1][0]);
-                        stage16<X3>(tlane + TC_AH_HI + u0 + 16, tlane + TC_AH_LO + u0 + 16, &seq[T - 1][16]);
+                        stage16<X3>(tlane + TC_AH_HI + u0, tlane + TC_AH_LO + u0, &seq[SR - 1][0]);
+                        stage16<X3>(tlane + TC_AH_HI + u0 + 16, tlane + TC_AH_LO + u0 + 16, &seq[SR - 1][16]);
                     } else if (stateful) {
                         float hv[16];
 #pragma unroll
@@ -138,7 +145,7 @@
                         }
                         if (f > 0) {
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) hold[i] = seq[T - 1][ub * 8 + i];
+                            for (int i = 0; i < 8; ++i) hold[i] = seq[SR - 1][ub * 8 + i];
                         } else if (stateful) {
                             float4 v0 = *reinterpret_cast<const float4*>(carry_h + ub * 8), v1 = *reinterpret_cast<const float4*>(carry_h + ub * 8 + 4);
                             hold[0] = v0.x; hold[1] = v0.y; hold[2] = v0.z; hold[3] = v0.w;
@@ -181,12 +188,27 @@
                         }
                     }
                     // ---- rotate: this cell's output becomes seq[T-1], the next frame's input becomes seq[0]
+                    if (!SCR) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const float o = seq[0][j];
+                        for (int j = 0; j < 32; ++j) {
+                            const float o = seq[0][j];
 #pragma unroll
-                        for (int k = 0; k + 1 < T; ++k) seq[k][j] = seq[k + 1][j];
-                        seq[T - 1][j] = o;
+                            for (int k = 0; k + 1 < SR; ++k) seq[k][j] = seq[k + 1][j];
+                            seq[SR - 1][j] = o;
+                        }
+                    } else {
+                        float* const sq = seqb + u0 * TN + row;
+                        if (l + 1 < NL) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) __stcg(sq + (f * HID + j) * TN, seq[0][j]);
+                        }
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) seq[1][j] = seq[0][j];
+                        const int nf = f + 1 < T ? f + 1 : 0, nl = f + 1 < T ? l : l + 1;     // the next cell of this step
+                        if (nl > 0 && nl < NL) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) seq[0][j] = __ldcg(sq + (nf * HID + j) * TN);
+                        }
                     }
                 }
             }
@@ -199,7 +221,7 @@
                 for (int j = 0; j < 32; ++j) {
                     const float4 w0 = *reinterpret_cast<const float4*>(fcS + (u0 + j) * 8);
                     const float4 w1 = *reinterpret_cast<const float4*>(fcS + (u0 + j) * 8 + 4);
-                    const float a = seq[T - 1][j];
+                    const float a = seq[SR - 1][j];
                     y[0] = fmaf(a, w0.x, y[0]); y[1] = fmaf(a, w0.y, y[1]); y[2] = fmaf(a, w0.z, y[2]); y[3] = fmaf(a, w0.w, y[3]);
                     y[4] = fmaf(a, w1.x, y[4]); y[5] = fmaf(a, w1.y, y[5]);
                 }

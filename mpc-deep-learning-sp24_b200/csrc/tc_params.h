@@ -8,7 +8,9 @@ namespace mpcdl {
 
 constexpr int TC_TN = 128;            // trajectories per CTA tile = MMA M (one TMEM lane per trajectory)
 constexpr int TC_HID = 64;            // hidden units (the shipped GRU/LSTM checkpoints)
-constexpr int TC_T = 4;               // window frames (deep_models.py:99 FT_SIZE)
+constexpr int TC_T = 4;               // window frames (deep_models.py:99 FT_SIZE): a layer's output sequence stays in registers
+constexpr int TC_T_LONG = 8;          // the other ft_size of the reference's training grid (deep_models.py:184): the sequence
+                                      //   goes through a per-CTA scratch in global memory (L2), each thread re-reading its own writes
 constexpr int TC_EPI_THREADS = 256;   // 8 epilogue warps: lane quarter = warp % 4, unit half = warp / 4
 constexpr int TC_THREADS = 384;       // + 1 control warpgroup (TMA producer + MMA issuer = one elected lane of warp 8);
                                       //   a whole warpgroup so that setmaxnreg can move its registers to the epilogue warps
@@ -42,7 +44,11 @@ struct TcRolloutParams {
     TcModel m;
     IoParams io;
     NoiseParams nz;
+    float* seqbuf;           // window > TC_T: [grid][window][TC_HID][TC_TN] layer output sequences, else unused
 };
+
+__host__ __device__ inline bool tc_window_ok(int window) { return window == TC_T || window == TC_T_LONG; }
+__host__ __device__ inline size_t tc_seq_bytes_per_cta(int window) { return window > TC_T ? (size_t)window * TC_HID * TC_TN * 4 : 0; }
 
 struct TcSmem {       // float offsets
     int bars, ring, bias, fc, norm, xwin, ypart, ybuf, nblob, nin, nact0, nact1, nzb, total;

@@ -152,9 +152,9 @@ std::tuple<Tensor, Tensor> rollout(int kind, const OptTensor& wblob, const Tenso
     a.n_models = (int32_t)n_models; a.share_inputs = share_inputs;
     c10::cuda::CUDAGuard guard(dev);                     // the launch goes to the tensors' device
     Tensor scratch;
-    if (a.precision == MPCDL_PREC_BF16) {
-        // per-CTA layer output sequences of the BF16 LSTM-256 kernel; from the caching allocator, so the buffer is tied to
-        // the current stream like every other tensor of the call
+    if (a.precision != MPCDL_PREC_FP32) {
+        // per-CTA layer output sequences of the BF16 LSTM-256 kernel and of the window-8 tcgen05 GRU / LSTM kernel; from the
+        // caching allocator, so the buffer is tied to the current stream like every other tensor of the call
         const size_t nscratch = mpcdl_rollout_scratch_bytes(&a);
         if (nscratch) {
             scratch = at::empty({(int64_t)nscratch}, U.options().dtype(at::kByte));

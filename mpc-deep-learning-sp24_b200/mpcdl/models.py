@@ -115,7 +115,7 @@ class _RolloutMixin:
         noise FeedforwardNoiseModel (residual injection); eps [N,H,6] draws or None -> Philox(seed).
         cost  (ref [H,6], qw [6], rw [2]) -> per-trajectory quadratic tracking cost.
         precision "fp32" (FFMA kernels, the parity path) | "tf32x3" | "tf32" (tcgen05 tensor-core kernels,
-              GRU/LSTM hidden 64 window 4 only) | "bf16" (tcgen05 kernel of the LSTM with hidden 256: BF16
+              GRU/LSTM hidden 64, window 4 or 8) | "bf16" (tcgen05 kernel of the LSTM with hidden 256: BF16
               operands, FP32 accumulation and cell state); anything else raises -- there is no silent fallback.
         sample  MPPI call: dict(n=N, sigma=(s_a, s_steer), lo=(..), hi=(..), seed=int) -> U is the NOMINAL sequence
               [H,2] and trajectory n applies clamp(U + sigma * z_n) with z_n drawn in-kernel (Philox keyed by

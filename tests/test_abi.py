@@ -109,7 +109,18 @@ def test_tensor_core_plans_and_errors():
                     assert p["ksplit"] in (1, 2, 4) and p["grid"] == 148 and p["ntiles"] == 512
                     if p["resident"]:
                         assert p["nslots"] * p["ksplit"] >= 8          # a layer's two 64-row matrices stay in the ring
-    for args in [(1, 128, 2, 4), (1, 64, 4, 8), (0, 16, 4, 0)]:           # hidden 128 / window 8 / MLP hidden 16: FP32 kernels only
+    for kind in (1, 2):                                                    # window 8: same kernel, the sequence through a per-CTA scratch
+        p = ops.plan(kind, 64, 4, 8, 65536, 100, noise_cfg=[3, 32, 2, 2], precision="tf32x3")
+        assert p["variant"] == 4 and p["grid"] == 148 and 120 * 1024 <= p["smem_bytes"] <= 232448
+        a = _lib.RolloutArgs()
+        a.model = _lib.ModelDesc(kind, 64, 4, 8)
+        a.precision, a.N, a.H = _lib.PRECISION["tf32x3"], 65536, 100
+        assert _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a)) == 148 * 8 * 64 * 128 * 4
+        a.N = 1000
+        assert _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a)) == 8 * 8 * 64 * 128 * 4
+        a.model = _lib.ModelDesc(kind, 64, 4, 4)
+        assert _lib.lib.mpcdl_rollout_scratch_bytes(C.byref(a)) == 0
+    for args in [(1, 128, 2, 4), (1, 64, 4, 6), (0, 16, 4, 0)]:           # hidden 128 / window 6 / MLP hidden 16: FP32 kernels only
         with pytest.raises(RuntimeError):
             ops.plan(args[0], args[1], args[2], args[3], 100, 5, precision="tf32x3")
     with pytest.raises(RuntimeError):                                      # tcgen05 MLP has no residual-noise path
