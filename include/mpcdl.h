@@ -140,6 +140,17 @@ typedef struct {
  * (model_scripts/eval_models.py:86). `stream` is a cudaStream_t (NULL = default stream). */
 int mpcdl_rollout(const mpcdl_rollout_args* args, void* stream);
 
+/* mpcdl_rollout for callers that may not allocate device memory (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same arguments, results and
+ * status codes as mpcdl_rollout, for the one kernel family whose scratch it replaces: GRU / LSTM, hidden 64, window 8,
+ * precision MPCDL_PREC_TF32X3 or MPCDL_PREC_TF32.  args->scratch / scratch_bytes are ignored: the per-CTA layer output
+ * sequences live in a static device array inside the library (16 MB on every GPU that loads it, held until exit), which
+ * bounds a call to N <= MPCDL_STATIC_SCRATCH_MAX_TRAJ trajectories; larger N and other shapes return MPCDL_ERR_UNSUPPORTED.
+ * The call allocates and frees nothing.  All calls on a device share the array (contents of the previous call remain, none
+ * of it needs clearing): two calls that overlap on the GPU (different streams) race; serialise them. */
+#define MPCDL_STATIC_SCRATCH_MAX_TRAJ 8192
+int mpcdl_rollout_static_scratch(const mpcdl_rollout_args* args, void* stream);
+
 /* Bytes of args->scratch that mpcdl_rollout needs for these args (0 unless precision = MPCDL_PREC_BF16,
  * or a TF32 mode with model.window = 8). */
 size_t mpcdl_rollout_scratch_bytes(const mpcdl_rollout_args* args);

@@ -785,6 +785,39 @@ int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
     return MPCDL_OK;
 }
 
+int mpcdl_rollout_static_scratch(const mpcdl_rollout_args* a, void* stream) {
+    if (!a) return fail(MPCDL_ERR_ARG, "args is NULL");
+    if ((a->precision != MPCDL_PREC_TF32X3 && a->precision != MPCDL_PREC_TF32) || !tc_supported(a->model) || a->model.window != TC_T_LONG)
+        return fail(MPCDL_ERR_UNSUPPORTED, "mpcdl_rollout_static_scratch: the GRU / LSTM tensor-core rollout with hidden=%d window=%d (TF32X3 or TF32) only; "
+                    "got kind=%d hidden=%d window=%d precision=%d", TC_HID, TC_T_LONG, a->model.kind, a->model.hidden, a->model.window, a->precision);
+    if (a->N > TC_STATIC_MAX_TRAJ)
+        return fail(MPCDL_ERR_UNSUPPORTED, "mpcdl_rollout_static_scratch: N=%lld exceeds the static scratch (%lld trajectories = %d tiles of %d); "
+                    "use mpcdl_rollout with a caller scratch", (long long)a->N, TC_STATIC_MAX_TRAJ, TC_STATIC_CTAS, TC_TN);
+    mpcdl_rollout_args b = *a;                           // the caller's scratch fields are ignored: stand-ins that pass check_args
+    b.scratch = &b;
+    b.scratch_bytes = (uint64_t)TC_STATIC_CTAS * tc_seq_bytes_per_cta(TC_T_LONG);
+    int rc = check_args(&b);
+    if (rc) return rc;
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    TcPlan tp;
+    rc = make_tc_plan(b, tp, di->sms);
+    if (rc) return rc;
+    if (tp.grid > TC_STATIC_CTAS) return fail(MPCDL_ERR_UNSUPPORTED, "mpcdl_rollout_static_scratch: grid %d exceeds %d CTAs", tp.grid, TC_STATIC_CTAS);
+    TcRolloutParams q;
+    memset(&q, 0, sizeof(q));
+    build_tc_parts(b.model, q.m.parts, q.m.bias_off, q.m.fc_off);
+    q.m.blob = b.wblob_tc;
+    q.m.cell = b.model.kind == MPCDL_GRU ? 0 : 1;
+    q.m.prec = b.precision; q.m.layers = b.model.layers; q.m.window = b.model.window; q.m.stateful = b.stateful != 0;
+    q.m.nslots = tp.nslots; q.m.slot_floats = tp.slot_floats; q.m.resident = tp.resident; q.m.group = tp.group; q.m.noise_alias = tp.alias;
+    fill_noise(q.nz, b);
+    fill_io(q.io, b, tp.ntiles);
+    cudaError_t e = launch_rnn_tc_static(q, tp.grid, tp.smem_bytes, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "mpcdl_rollout_static_scratch: launch failed: %s (smem=%d grid=%d)", cudaGetErrorString(e), tp.smem_bytes, tp.grid);
+    return MPCDL_OK;
+}
+
 int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
     int rc = check_args(a);
     if (rc) return rc;

@@ -34,6 +34,8 @@ cudaError_t launch_mlp2(const RolloutParams& p, int rt, int rj, int ks, int ng, 
 int mlp2_smem_bytes(int blob_floats, int hid, int TN, int ks, int rt, int rj, int ng);
 cudaError_t launch_rnn(const RolloutParams& p, int cell, int rt, int rj, int grid, int smem_bytes, cudaStream_t st);
 cudaError_t launch_rnn_tc(const TcRolloutParams& p, int grid, int smem_bytes, cudaStream_t st);
+// window 8 with the sequences in the library's static device array (grid <= TC_STATIC_CTAS); allocates nothing
+cudaError_t launch_rnn_tc_static(TcRolloutParams p, int grid, int smem_bytes, cudaStream_t st);
 cudaError_t launch_lstm_tc(const LtRolloutParams& p, int grid, int smem_bytes, cudaStream_t st);
 cudaError_t launch_mlp_tc(const McRolloutParams& p, int grid, int smem_bytes, cudaStream_t st);
 constexpr int AUX_TN = 128, AUX_THREADS = 256;       // noise-net entry points: 128 samples per CTA tile

@@ -21,6 +21,7 @@
 #include "umma.cuh"
 #include "tc_params.h"
 #include "launch.h"
+#include <mutex>
 
 namespace mpcdl {
 
@@ -309,6 +310,39 @@ cudaError_t launch_rnn_tc(const TcRolloutParams& p, int grid, int smem_bytes, cu
     if (p.m.window == TC_T) return launch_rnn_tc_w<TC_T>(p, grid, smem_bytes, st);
     if (p.m.window == TC_T_LONG && p.seqbuf) return launch_rnn_tc_w<TC_T_LONG>(p, grid, smem_bytes, st);
     return cudaErrorInvalidConfiguration;
+}
+
+// ------------------------------------------------------------------ static scratch (mpcdl_rollout_static_scratch)
+// Callers that may not allocate (CUDA graph capture, serving loops) get the window-8 sequences from this array instead of a
+// caller buffer.  Every GPU that loads the library holds its 16 MB until exit; every call on a device shares it, so calls
+// that overlap on the GPU race.  Nothing in it has to start at zero: a thread only ever loads words it stored earlier in
+// the same rollout step (rollout_rnn_tc_epi.inl), so stale contents of the previous call are never read.
+static __device__ __align__(256) float g_tc_static_seq[(size_t)TC_STATIC_CTAS * TC_T_LONG * TC_HID * TC_TN];
+
+// In host code `g_tc_static_seq` is only a handle: the device address comes from cudaGetSymbolAddress, once per device, with
+// that device current.
+static float* g_tc_static_ptr[64];
+static std::mutex g_tc_static_mu;
+
+cudaError_t launch_rnn_tc_static(TcRolloutParams p, int grid, int smem_bytes, cudaStream_t st) {
+    if (p.m.window != TC_T_LONG || grid < 1 || grid > TC_STATIC_CTAS) return cudaErrorInvalidConfiguration;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    float* ptr;
+    {
+        std::lock_guard<std::mutex> lk(g_tc_static_mu);
+        if (!g_tc_static_ptr[dev]) {
+            void* q = nullptr;
+            e = cudaGetSymbolAddress(&q, g_tc_static_seq);
+            if (e != cudaSuccess) return e;
+            g_tc_static_ptr[dev] = static_cast<float*>(q);
+        }
+        ptr = g_tc_static_ptr[dev];
+    }
+    p.seqbuf = ptr;
+    return launch_rnn_tc_w<TC_T_LONG>(p, grid, smem_bytes, st);
 }
 
 }  // namespace mpcdl

@@ -47,6 +47,10 @@ struct TcRolloutParams {
     float* seqbuf;           // window > TC_T: [grid][window][TC_HID][TC_TN] layer output sequences, else unused
 };
 
+// mpcdl_rollout_static_scratch: the window-8 sequences live in a file-scope __device__ array of rollout_rnn_tc.cu sized for
+// this many CTAs (64 x 256 KB = 16 MB per GPU that loads the library) -> at most 64 x 128 = 8192 trajectories per call.
+constexpr int TC_STATIC_CTAS = 64;
+constexpr long long TC_STATIC_MAX_TRAJ = (long long)TC_STATIC_CTAS * TC_TN;
 __host__ __device__ inline bool tc_window_ok(int window) { return window == TC_T || window == TC_T_LONG; }
 __host__ __device__ inline size_t tc_seq_bytes_per_cta(int window) { return window > TC_T ? (size_t)window * TC_HID * TC_TN * 4 : 0; }
 

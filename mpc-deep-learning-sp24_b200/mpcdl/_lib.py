@@ -122,7 +122,7 @@ class Plan(C.Structure):
 
 
 EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_pack_mlp_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
-           "mpcdl_rollout", "mpcdl_rollout_scratch_bytes", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_ffma2_peak", "mpcdl_last_error", "mpcdl_version",
+           "mpcdl_rollout", "mpcdl_rollout_static_scratch", "mpcdl_rollout_scratch_bytes", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_ffma2_peak", "mpcdl_last_error", "mpcdl_version",
            "mpcdl_dataset_stats", "mpcdl_dataset_build", "mpcdl_rollout_inputs", "mpcdl_curve_metrics", "mpcdl_resample",
            "mpcdl_train_param_count", "mpcdl_train_mlp_epoch", "mpcdl_l1_batches", "mpcdl_cdr_decode",
            "mpcdl_debug_poison_smem")
@@ -153,6 +153,8 @@ def _load():
     lib.mpcdl_pack_noise.argtypes = [C.c_int, C.c_int, C.c_int, fpp, fpp, fp]
     lib.mpcdl_rollout.restype = C.c_int
     lib.mpcdl_rollout.argtypes = [C.POINTER(RolloutArgs), C.c_void_p]
+    lib.mpcdl_rollout_static_scratch.restype = C.c_int
+    lib.mpcdl_rollout_static_scratch.argtypes = [C.POINTER(RolloutArgs), C.c_void_p]
     lib.mpcdl_rollout_scratch_bytes.restype = C.c_size_t
     lib.mpcdl_rollout_scratch_bytes.argtypes = [C.POINTER(RolloutArgs)]
     lib.mpcdl_rollout_plan.restype = C.c_int
