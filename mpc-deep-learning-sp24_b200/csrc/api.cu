@@ -278,12 +278,16 @@ struct McPlan { int smem_bytes, ntiles, grid, tiles_per_cta; };
 int make_mc_plan(const mpcdl_rollout_args& a, McPlan& pl, int num_sms) {
     McModel m;
     build_mc_offsets(a.model, a.precision == MPCDL_PREC_TF32X3, m);
-    pl.smem_bytes = std::max(mc_layout((int)m.w_floats, a.model.layers).total * 4, 120 * 1024);
-    if (pl.smem_bytes > SMEM_LIMIT)
-        return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core MLP: %d layers of tf32 hi/lo weights (%d KB) do not fit shared memory; use MPCDL_PREC_TF32 or FP32",
-                    a.model.layers, pl.smem_bytes / 1024);
+    NoiseParams nz;
+    fill_noise(nz, a);
     pl.ntiles = (int)((a.N + TC_TN - 1) / TC_TN);
     pl.tiles_per_cta = (a.tune_ntg == 1 || a.tune_ntg == 2) ? a.tune_ntg : (pl.ntiles > num_sms ? MC_TILES : 1);
+    // the noise net's buffers are per tile: when two sets do not fit beside the weights (tf32x3, 4 layers), one tile per CTA
+    if (pl.tiles_per_cta == 2 && mc_layout((int)m.w_floats, a.model.layers, nz, 2).total * 4 > SMEM_LIMIT) pl.tiles_per_cta = 1;
+    pl.smem_bytes = std::max(mc_layout((int)m.w_floats, a.model.layers, nz, pl.tiles_per_cta).total * 4, 120 * 1024);
+    if (pl.smem_bytes > SMEM_LIMIT)
+        return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core MLP: %d layers of tf32 hi/lo weights%s (%d KB) do not fit shared memory; use MPCDL_PREC_TF32 or FP32",
+                    a.model.layers, nz.enabled ? " + the noise net" : "", pl.smem_bytes / 1024);
     pl.grid = std::min((pl.ntiles + pl.tiles_per_cta - 1) / pl.tiles_per_cta, num_sms);
     return MPCDL_OK;
 }
@@ -462,8 +466,6 @@ int check_args(const mpcdl_rollout_args* a) {
         if (!tc_supported(a->model) && !mc_supported(a->model))
             return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core precision needs hidden=%d (GRU/LSTM: window=%d or %d); got kind=%d hidden=%d window=%d; use MPCDL_PREC_FP32",
                         TC_HID, TC_T, TC_T_LONG, a->model.kind, a->model.hidden, a->model.window);
-        if (a->model.kind == MPCDL_MLP && a->noise_wblob)
-            return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core MLP rollout has no residual-noise path; use MPCDL_PREC_FP32");
         if (!a->wblob_tc) return fail(MPCDL_ERR_ARG, "tensor-core precision needs wblob_tc (mpcdl_pack_rnn_tc)");
         const size_t need = mpcdl_rollout_scratch_bytes(a);
         if (need && (!a->scratch || a->scratch_bytes < need))
@@ -851,6 +853,7 @@ int mpcdl_rollout(const mpcdl_rollout_args* a, void* stream) {
         memset(&q, 0, sizeof(q));
         build_mc_offsets(a->model, a->precision == MPCDL_PREC_TF32X3, q.m);
         q.m.blob = a->wblob_tc; q.m.prec = a->precision; q.m.tiles_per_cta = mp.tiles_per_cta;
+        fill_noise(q.nz, *a);
         fill_io(q.io, *a, mp.ntiles);
         cudaError_t e = launch_mlp_tc(q, mp.grid, mp.smem_bytes, st);
         if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "tensor-core MLP kernel launch failed: %s (smem=%d)", cudaGetErrorString(e), mp.smem_bytes);

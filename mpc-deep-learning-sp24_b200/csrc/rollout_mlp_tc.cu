@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
     constexpr int HID = TC_HID, TN = TC_TN;
     extern __shared__ __align__(1024) float sm[];
     const McModel& m = p.m;
-    const McSmem L = mc_layout((int)m.w_floats, m.layers);
+    const McSmem L = mc_layout((int)m.w_floats, m.layers, p.nz, m.tiles_per_cta);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int H = p.io.H, NL = m.layers;
     const long long N = p.io.N;
@@ -93,6 +93,8 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
     for (int i = tid; i < (NL + 1) * HID; i += blockDim.x) sm[L.bias + i] = m.blob[m.bias_off + i];
     for (int i = tid; i < HID * 8 + 8; i += blockDim.x) sm[L.out + i] = m.blob[m.out_off + i];
     for (int i = tid; i < 28; i += blockDim.x) sm[L.norm + i] = p.io.norm[i];       // f_mean8 f_std8 l_mean6 l_std6
+    if (p.nz.enabled)
+        for (int i = tid; i < p.nz.blob_floats; i += blockDim.x) sm[L.nblob + i] = p.nz.blob[i];
     umma::fence_before_sync();
     __syncthreads();
     umma::fence_after_sync();
@@ -136,6 +138,12 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
         const float* const normS = sm + L.norm;
         const float* const outS = sm + L.out;
         float* const ypart = sm + L.ypart + ts * 6 * TN;
+        // residual-noise net (noise_model.py:34-40, 86-103): per-tile buffers, evaluated by the tile's 256 epilogue threads
+        float* const nin = sm + L.ntile + ts * L.ntile_floats;
+        float* const nact0 = nin + p.nz.in_dim * TN;
+        const int nact_flip = p.nz.size * TN;
+        float* const nzb = nact0 + 2 * nact_flip;
+        const int etid = tid - ts * EW * 32;
         uint32_t par = 0;
         if (ts < tpc)
             for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
@@ -170,6 +178,21 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                     }
                     umma::fence_before_sync();
                     mbar_arrive(&opnd[ts]);
+                    if (p.nz.enabled) {
+                        // The net sees the history up to (s_t, u_t) only, so it runs here, under the MMAs of the input layer.
+                        if (owner) noise_push(nin, TN, row, p.nz.hist, t == 0, s, u);
+                        named_bar_sync(1 + ts, EW * 32);
+                        const float* W = sm + L.nblob;
+                        int K = p.nz.in_dim;
+                        for (int ph = 0; ph <= p.nz.nlayers; ++ph) {
+                            const bool lastp = ph == p.nz.nlayers;
+                            const int outw = lastp ? 12 : p.nz.size;
+                            dense_resident<4, 4>(ph == 0 ? nin : nact0 + ((ph - 1) & 1) * nact_flip, K, W, outw, outw,
+                                                 lastp ? ACT_IDENTITY : p.nz.act, lastp ? nzb : nact0 + (ph & 1) * nact_flip, TN, etid, EW * 32);
+                            W += (K + 1) * outw; K = p.nz.size;
+                            named_bar_sync(1 + ts, EW * 32);
+                        }
+                    }
                     float y[6];
 #pragma unroll
                     for (int d = 0; d < 6; ++d) y[d] = owner ? outS[HID * 8 + d] : 0.f;
@@ -219,8 +242,12 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                     if (owner) {
 #pragma unroll
                         for (int d = 0; d < 6; ++d) y[d] += ypart[d * TN + row];
-                        float nxt[6];
-                        owner_finish(p, normS + 16, y, nullptr, 1, 0, n, valid, t, u, nxt, cost);
+                        float nxt[6], nzr[12];
+                        if (p.nz.enabled) {
+#pragma unroll
+                            for (int i = 0; i < 12; ++i) nzr[i] = nzb[i * TN + row];
+                        }
+                        owner_finish(p, normS + 16, y, nzr, 1, 0, n, valid, t, u, nxt, cost);
 #pragma unroll
                         for (int d = 0; d < 6; ++d) s[d] = nxt[d];
                     }

@@ -111,10 +111,11 @@ struct McModel {
 struct McRolloutParams {
     McModel m;
     IoParams io;
-    NoiseParams nz;                   // never enabled (owner_finish reads the flag)
+    NoiseParams nz;                   // residual-noise net on the tile's epilogue warps (CUDA cores), per-tile buffers
 };
-struct McSmem { int bars, w, bias, out, norm, ypart, total; };
-__host__ __device__ inline McSmem mc_layout(int w_floats, int layers) {
+struct McSmem { int bars, w, bias, out, norm, ypart, nblob, ntile, ntile_floats, total; };
+// per-tile noise buffers (ntile + ts * ntile_floats): nin [in_dim][TN], nact0 / nact1 [size][TN], nzb [12][TN]
+__host__ __device__ inline McSmem mc_layout(int w_floats, int layers, const NoiseParams& nz, int tiles) {
     McSmem L;
     int o = 0;
     L.bars = o;  o += 64;
@@ -123,6 +124,10 @@ __host__ __device__ inline McSmem mc_layout(int w_floats, int layers) {
     L.out = o;   o += TC_HID * 8 + 8;
     L.norm = o;  o += 32;
     L.ypart = o; o += MC_TILES * 6 * TC_TN;     // output-layer partial sums of the unit-half-1 threads
+    L.nblob = o; o += nz.enabled ? align_up(nz.blob_floats, 4) : 0;
+    L.ntile = o;
+    L.ntile_floats = nz.enabled ? (nz.in_dim + 2 * nz.size + 12) * TC_TN : 0;
+    o += tiles * L.ntile_floats;
     L.total = o;
     return L;
 }

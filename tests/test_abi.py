@@ -123,8 +123,11 @@ def test_tensor_core_plans_and_errors():
     for args in [(1, 128, 2, 4), (1, 64, 4, 6), (0, 16, 4, 0)]:           # hidden 128 / window 6 / MLP hidden 16: FP32 kernels only
         with pytest.raises(RuntimeError):
             ops.plan(args[0], args[1], args[2], args[3], 100, 5, precision="tf32x3")
-    with pytest.raises(RuntimeError):                                      # tcgen05 MLP has no residual-noise path
-        ops.plan(0, 64, 4, 0, 100, 5, noise_cfg=[3, 32, 2, 2], precision="tf32")
+    # tcgen05 MLP + residual-noise net: per-tile noise buffers; two tiles per CTA only where both sets fit beside the weights
+    p = ops.plan(0, 64, 4, 0, 1 << 20, 50, noise_cfg=[3, 32, 2, 2], precision="tf32")
+    assert p["variant"] == 5 and p["ksplit"] == 2 and p["smem_bytes"] <= 232448
+    p = ops.plan(0, 64, 4, 0, 1 << 20, 50, noise_cfg=[3, 32, 2, 2], precision="tf32x3")
+    assert p["variant"] == 5 and p["ksplit"] in (1, 2) and p["grid"] == 148 and p["smem_bytes"] <= 232448
     # tcgen05 MLP (rollout_mlp_tc.cu): 128-trajectory tiles, two ping-pong tiles per CTA once there are more tiles than SMs
     for prec in ("tf32x3", "tf32"):
         for layers in (1, 2, 4):
