@@ -773,7 +773,7 @@ int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
         rc = make_tc_plan(*a, tp, sms);
         if (rc) return rc;
         memset(out, 0, sizeof(*out));
-        out->rt = 1; out->rj = 32; out->n_tg = TC_TN; out->tile_traj = TC_TN; out->threads = TC_THREADS; out->grid = tp.grid;
+        out->rt = 1; out->rj = TC_UPT; out->n_tg = TC_TN; out->tile_traj = TC_TN; out->threads = TC_THREADS; out->grid = tp.grid;
         out->smem_bytes = tp.smem_bytes; out->resident = tp.resident; out->nslots = tp.nslots; out->slot_floats = tp.slot_floats;
         out->ntiles = tp.ntiles; out->variant = 4; out->ksplit = tp.group;
         return MPCDL_OK;

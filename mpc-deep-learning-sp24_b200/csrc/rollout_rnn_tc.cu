@@ -184,7 +184,7 @@ template <int CELL, int PREC, int T>
 __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __grid_constant__ TcRolloutParams p) {
     constexpr bool X3 = PREC == PREC_TF32X3;
     constexpr bool FAST = PREC == PREC_TF32;
-    constexpr int HID = TC_HID, TN = TC_TN;
+    constexpr int HID = TC_HID, TN = TC_TN, CW = TC_EPI_THREADS / 32;      // CW = first warp of the control warpgroup
     extern __shared__ __align__(1024) float sm[];
     const TcModel& m = p.m;
     const bool alias = m.noise_alias != 0 && p.nz.enabled;     // noise-net buffers inside the weight ring (tc_params.h)
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
         mbar_init(ring_free, TC_TN);
         mbar_fence_init();
     }
-    if (warp == 8) { umma::tmem_alloc(tmem_slot, 512); umma::tmem_relinquish(); }
+    if (warp == CW) { umma::tmem_alloc(tmem_slot, 512); umma::tmem_relinquish(); }
     // tile-invariant constants -> shared memory.  Gate biases are pre-scaled for the exp2-based activations:
     //   sigmoid(g + b) = 1 / (1 + 2^(-log2e g - log2e b)),  tanh(g + b) = 1 - 2 / (1 + 2^(2 log2e g + 2 log2e b));
     //   the MUFU.TANH mode (TF32) uses sigmoid(x) = 0.5 tanh(0.5 x) + 0.5 -> 0.5 b for sigmoid gates, b for tanh gates.
@@ -228,10 +228,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
     const uint32_t tbase = *tmem_slot;
     const int my_tiles = (p.io.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
-    if (warp >= 8) {
+    if (warp >= CW) {
         // ============================================================== control warpgroup (one active thread)
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-        if (warp == 8 && lane == 0) {
+        // the register pool of a CTA is what it was launched with (threads x 96 here; 168 for 8 epilogue warps): the two
+        // setmaxnreg values must add up to at most that, or the .inc never returns
+        if (TC_UG == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        else asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
+        if (warp == CW && lane == 0) {
             TcCtl c(m, sm + L.ring, full, empty, my_tiles, H);
             if (alias) c.ring_free = ring_free;
             uint32_t use_count = 0, cellpar = 0;
@@ -278,13 +281,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
         }
         __syncwarp();
     } else {
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        if (TC_UG == 2) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+        else asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");        // 512 x 112 + 128 x 32 = 640 x 96
 #include "rollout_rnn_tc_epi.inl"
     }
     // ------------------------------------------------------------------ teardown
     umma::fence_before_sync();
     __syncthreads();
-    if (warp == 8) umma::tmem_dealloc(tbase, 512);
+    if (warp == CW) umma::tmem_dealloc(tbase, 512);
 }
 
 // ------------------------------------------------------------------ launcher

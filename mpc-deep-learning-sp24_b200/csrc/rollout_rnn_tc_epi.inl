@@ -1,23 +1,23 @@
-// Epilogue warps of rollout_rnn_tc_kernel (included inside the kernel body; warps 0..7).
-// Thread <-> data: TMEM lane / trajectory row = 32*(warp%4) + lane; hidden units [32*uh, 32*uh+32), uh = warp/4.
-// The layer's sequence lives in registers as seq[T][32] and is ROTATED by one frame after every cell, so the
+// Epilogue warps of rollout_rnn_tc_kernel (included inside the kernel body; warps 0 .. 4 TC_UG - 1).
+// Thread <-> data: TMEM lane / trajectory row = 32*(warp%4) + lane; hidden units [UPT*uh, UPT*uh+UPT), uh = warp/4, UPT = TC_UPT.
+// The layer's sequence lives in registers as seq[T][UPT] and is ROTATED by one frame after every cell, so the
 // frame loop is a real loop (4x less code than unrolling it): at cell (l, f)
 //   seq[0] = layer l-1 output of frame f (consumed as x, then overwritten by this cell's output)
 //   seq[T-1] = layer l output of frame f-1 (the recurrent input, f > 0)
 // Window 8 (T > TC_T) would need 256 registers for the sequence: there only seq[0] (x, then the output) and seq[1] (the
 // recurrent input) are registers and the sequence goes through p.seqbuf [T][64 units][128 rows] (global memory, L2): a
-// thread stores its 32 units of frame f after the cell and loads the next cell's input -- always words it wrote itself,
+// thread stores its UPT units of frame f after the cell and loads the next cell's input -- always words it wrote itself,
 // so no barrier or fence is involved; layer l overwrites frame f only after it has consumed layer l-1's frame f.
 {
     const int q = warp & 3, uh = warp >> 2;
     const int row = q * 32 + lane;
-    const int u0 = uh * 32;
+    constexpr int UPT = TC_UPT;
+    const int u0 = uh * UPT;
     const bool owner = uh == 0;
     const uint32_t tlane = tbase + (static_cast<uint32_t>(q * 32) << 16);
     float* const normS = sm + L.norm;                  // f_mean[T*8] f_std[T*8] l_mean[6] l_std[6]
     float* const xwin = sm + L.xwin;                   // raw window [T][8][TN]
-    float* const ypart = sm + L.ypart;                 // [2][8][TN]
-    float* const ybuf = sm + L.ybuf;                   // [8][TN]
+    float* const ypart = sm + L.ypart;                 // [TC_UG][6][TN]
     float* const nin = sm + L.nin;
     float* const nact0 = sm + L.nact0;
     const int nact_flip = L.nact1 - L.nact0;
@@ -35,8 +35,8 @@
         uint32_t zr[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) zr[i] = 0u;
-        umma::tmem_st16(tlane + TC_D + 192 + u0, zr);
-        umma::tmem_st16(tlane + TC_D + 192 + u0 + 16, zr);
+#pragma unroll
+        for (int b = 0; b < UPT; b += 16) umma::tmem_st16(tlane + TC_D + 192 + u0 + b, zr);
     }
 
     for (int tile = blockIdx.x; tile < p.io.ntiles; tile += gridDim.x) {
@@ -55,11 +55,11 @@
             }
         }
         int base = 0;                                  // physical slot of logical frame 0
-        float seq[SR][32];
+        float seq[SR][UPT];
 #pragma unroll
         for (int f = 0; f < SR; ++f)
 #pragma unroll
-            for (int j = 0; j < 32; ++j) seq[f][j] = 0.f;
+            for (int j = 0; j < UPT; ++j) seq[f][j] = 0.f;
         for (int t = 0; t < H; ++t) {
             float u[2] = {0.f, 0.f};
             if (owner) {
@@ -75,9 +75,9 @@
                 }
             }
             for (int l = 0; l < NL; ++l) {
-                float cst[32];                         // LSTM cell state (register resident across the frames)
+                float cst[UPT];                        // LSTM cell state (register resident across the frames)
 #pragma unroll
-                for (int j = 0; j < 32; ++j) cst[j] = 0.f;
+                for (int j = 0; j < UPT; ++j) cst[j] = 0.f;
                 const float* carry_h = p.io.carry;
                 float* carry_c = p.io.carry;
                 if (stateful) {
@@ -85,7 +85,7 @@
                     if (CELL == CELL_LSTM) {
                         carry_c = p.io.carry + ((long long)(NL + l) * N + n) * HID + u0;
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
+                        for (int j = 0; j < UPT; j += 4) {
                             float4 v = *reinterpret_cast<const float4*>(carry_c + j);
                             cst[j] = v.x; cst[j + 1] = v.y; cst[j + 2] = v.z; cst[j + 3] = v.w;
                         }
@@ -105,16 +105,16 @@
                             stage8<X3>(tlane + TC_AX_HI, tlane + TC_AX_LO, xn);
                         }
                     } else {
-                        stage16<X3>(tlane + TC_AX_HI + u0, tlane + TC_AX_LO + u0, &seq[0][0]);
-                        stage16<X3>(tlane + TC_AX_HI + u0 + 16, tlane + TC_AX_LO + u0 + 16, &seq[0][16]);
+#pragma unroll
+                        for (int b = 0; b < UPT; b += 16) stage16<X3>(tlane + TC_AX_HI + u0 + b, tlane + TC_AX_LO + u0 + b, &seq[0][b]);
                     }
                     if (f > 0) {
-                        stage16<X3>(tlane + TC_AH_HI + u0, tlane + TC_AH_LO + u0, &seq[SR - 1][0]);
-                        stage16<X3>(tlane + TC_AH_HI + u0 + 16, tlane + TC_AH_LO + u0 + 16, &seq[SR - 1][16]);
+#pragma unroll
+                        for (int b = 0; b < UPT; b += 16) stage16<X3>(tlane + TC_AH_HI + u0 + b, tlane + TC_AH_LO + u0 + b, &seq[SR - 1][b]);
                     } else if (stateful) {
                         float hv[16];
 #pragma unroll
-                        for (int hb = 0; hb < 2; ++hb) {
+                        for (int hb = 0; hb < UPT / 16; ++hb) {
 #pragma unroll
                             for (int j = 0; j < 16; j += 4) {
                                 float4 v = *reinterpret_cast<const float4*>(carry_h + hb * 16 + j);
@@ -130,15 +130,25 @@
                     mbar_wait(acc_ready, cellpar);
                     cellpar ^= 1u;
                     umma::fence_after_sync();
+                    // Software pipeline over blocks of 8 units: the tcgen05.ld of block ub + 1 is in flight while block ub goes
+                    // through the MUFU chain (the warps of an SM sub-partition leave the barrier together, so without it the
+                    // TMEM read port and the MUFU pipe take turns).
+                    float gq[2][4][8];
+                    {
+                        const uint32_t c0 = tlane + TC_D + u0;
+                        umma::tmem_ld8(c0, gq[0][0]); umma::tmem_ld8(c0 + 64, gq[0][1]);
+                        umma::tmem_ld8(c0 + 128, gq[0][2]); umma::tmem_ld8(c0 + 192, gq[0][3]);
+                    }
 #pragma unroll
-                    for (int ub = 0; ub < 4; ++ub) {
-                        float g0[8], g1[8], g2[8], g3[8], hold[8];
+                    for (int ub = 0; ub < UPT / 8; ++ub) {
+                        float hold[8];
+                        float (&g0)[8] = gq[ub & 1][0], (&g1)[8] = gq[ub & 1][1], (&g2)[8] = gq[ub & 1][2], (&g3)[8] = gq[ub & 1][3];
                         const uint32_t c0 = tlane + TC_D + u0 + ub * 8;
-                        umma::tmem_ld8(c0, g0);
-                        umma::tmem_ld8(c0 + 64, g1);
-                        umma::tmem_ld8(c0 + 128, g2);
-                        umma::tmem_ld8(c0 + 192, g3);
                         umma::wait_ld();
+                        if (ub + 1 < UPT / 8) {
+                            umma::tmem_ld8(c0 + 8, gq[(ub + 1) & 1][0]); umma::tmem_ld8(c0 + 8 + 64, gq[(ub + 1) & 1][1]);
+                            umma::tmem_ld8(c0 + 8 + 128, gq[(ub + 1) & 1][2]); umma::tmem_ld8(c0 + 8 + 192, gq[(ub + 1) & 1][3]);
+                        }
                         if (CELL == CELL_GRU) {        // nh: re-zero for the next cell's accumulate-only recurrent part
                             const uint32_t zr[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
                             umma::tmem_st8(c0 + 192, zr);
@@ -181,7 +191,7 @@
                     if (stateful && f == T - 1 && valid) {
                         float* ch = p.io.carry + ((long long)l * N + n) * HID + u0;
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
+                        for (int j = 0; j < UPT; j += 4) {
                             *reinterpret_cast<float4*>(ch + j) = make_float4(seq[0][j], seq[0][j + 1], seq[0][j + 2], seq[0][j + 3]);
                             if (CELL == CELL_LSTM)
                                 *reinterpret_cast<float4*>(carry_c + j) = make_float4(cst[j], cst[j + 1], cst[j + 2], cst[j + 3]);
@@ -190,7 +200,7 @@
                     // ---- rotate: this cell's output becomes seq[T-1], the next frame's input becomes seq[0]
                     if (!SCR) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
+                        for (int j = 0; j < UPT; ++j) {
                             const float o = seq[0][j];
 #pragma unroll
                             for (int k = 0; k + 1 < SR; ++k) seq[k][j] = seq[k + 1][j];
@@ -200,25 +210,25 @@
                         float* const sq = seqb + u0 * TN + row;
                         if (l + 1 < NL) {
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) __stcg(sq + (f * HID + j) * TN, seq[0][j]);
+                            for (int j = 0; j < UPT; ++j) __stcg(sq + (f * HID + j) * TN, seq[0][j]);
                         }
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) seq[1][j] = seq[0][j];
+                        for (int j = 0; j < UPT; ++j) seq[1][j] = seq[0][j];
                         const int nf = f + 1 < T ? f + 1 : 0, nl = f + 1 < T ? l : l + 1;     // the next cell of this step
                         if (nl > 0 && nl < NL) {
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) seq[0][j] = __ldcg(sq + (nf * HID + j) * TN);
+                            for (int j = 0; j < UPT; ++j) seq[0][j] = __ldcg(sq + (nf * HID + j) * TN);
                         }
                     }
                 }
             }
-            // ---- head: full_c(out[:, -1, :]) partial sums over this thread's 32 units (last frame = seq[T-1])
+            // ---- head: full_c(out[:, -1, :]) partial sums over this thread's UPT units (last frame = seq[T-1])
             {
                 float y[8];
 #pragma unroll
                 for (int d = 0; d < 8; ++d) y[d] = 0.f;
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
+                for (int j = 0; j < UPT; ++j) {
                     const float4 w0 = *reinterpret_cast<const float4*>(fcS + (u0 + j) * 8);
                     const float4 w1 = *reinterpret_cast<const float4*>(fcS + (u0 + j) * 8 + 4);
                     const float a = seq[SR - 1][j];
@@ -226,7 +236,7 @@
                     y[4] = fmaf(a, w1.x, y[4]); y[5] = fmaf(a, w1.y, y[5]);
                 }
 #pragma unroll
-                for (int d = 0; d < 6; ++d) ypart[(uh * 8 + d) * TN + row] = y[d];
+                for (int d = 0; d < 6; ++d) ypart[(uh * 6 + d) * TN + row] = y[d];
             }
             if (alias) {
                 // The noise net's buffers alias the weight ring: every MMA of this step is complete (acc_ready of the last cell)
@@ -254,7 +264,7 @@
                 for (int ph = 0; ph <= p.nz.nlayers; ++ph) {
                     const bool last = ph == p.nz.nlayers;
                     const int outw = last ? 12 : p.nz.size;
-                    dense_resident<4, 4>(ph == 0 ? nin : nact0 + ((ph - 1) & 1) * nact_flip, K, W, outw, outw,
+                    dense_resident<8 / TC_UG, 4>(ph == 0 ? nin : nact0 + ((ph - 1) & 1) * nact_flip, K, W, outw, outw,
                                          last ? ACT_IDENTITY : p.nz.act, last ? nzb : nact0 + (ph & 1) * nact_flip, TN, tid, TC_EPI_THREADS);
                     W += (K + 1) * outw; K = p.nz.size;
                     named_bar_sync(1, TC_EPI_THREADS);
@@ -262,11 +272,20 @@
             }
             // ---- owner: next state, shift the window (overwrite the oldest physical frame)
             if (owner) {
+                float yv[6], nzr[12];                  // bias, then the unit groups in ascending order
 #pragma unroll
-                for (int d = 0; d < 6; ++d)
-                    ybuf[d * TN + row] = (fcS[HID * 8 + d] + ypart[d * TN + row]) + ypart[(8 + d) * TN + row];
+                for (int d = 0; d < 6; ++d) {
+                    float a = fcS[HID * 8 + d];
+#pragma unroll
+                    for (int g = 0; g < TC_UG; ++g) a += ypart[(g * 6 + d) * TN + row];
+                    yv[d] = a;
+                }
+                if (p.nz.enabled) {
+#pragma unroll
+                    for (int i = 0; i < 12; ++i) nzr[i] = nzb[i * TN + row];
+                }
                 float nxt[6];
-                owner_finish(p, normS + 2 * T * 8, ybuf, nzb, TN, row, n, valid, t, u, nxt, cost);
+                owner_finish(p, normS + 2 * T * 8, yv, nzr, 1, 0, n, valid, t, u, nxt, cost);
                 float* d = xwin + base * 8 * TN + row;
 #pragma unroll
                 for (int k = 0; k < 6; ++k) d[k * TN] = nxt[k];

@@ -11,8 +11,13 @@ constexpr int TC_HID = 64;            // hidden units (the shipped GRU/LSTM chec
 constexpr int TC_T = 4;               // window frames (deep_models.py:99 FT_SIZE): a layer's output sequence stays in registers
 constexpr int TC_T_LONG = 8;          // the other ft_size of the reference's training grid (deep_models.py:184): the sequence
                                       //   goes through a per-CTA scratch in global memory (L2), each thread re-reading its own writes
-constexpr int TC_EPI_THREADS = 256;   // 8 epilogue warps: lane quarter = warp % 4, unit half = warp / 4
-constexpr int TC_THREADS = 384;       // + 1 control warpgroup (TMA producer + MMA issuer = one elected lane of warp 8);
+#ifndef MPCDL_TC_UG
+#define MPCDL_TC_UG 2
+#endif
+constexpr int TC_UG = MPCDL_TC_UG;    // hidden-unit groups (2 or 4): an epilogue thread owns one trajectory row x TC_UPT units.  4 groups
+constexpr int TC_UPT = TC_HID / TC_UG;//   (16 warps x 16 units, 112 registers) measured no faster than 2 (8 warps x 32 units): profiles/r02/epi16
+constexpr int TC_EPI_THREADS = 128 * TC_UG;   // epilogue warps: lane quarter = warp % 4, unit group = warp / 4
+constexpr int TC_THREADS = TC_EPI_THREADS + 128;   // + 1 control warpgroup (TMA producer + MMA issuer = one elected lane of its first warp);
                                       //   a whole warpgroup so that setmaxnreg can move its registers to the epilogue warps
 constexpr int TC_KS = 16;             // K rows per weight chunk (2 tf32 MMA k-steps)
 
@@ -55,7 +60,7 @@ __host__ __device__ inline bool tc_window_ok(int window) { return window == TC_T
 __host__ __device__ inline size_t tc_seq_bytes_per_cta(int window) { return window > TC_T ? (size_t)window * TC_HID * TC_TN * 4 : 0; }
 
 struct TcSmem {       // float offsets
-    int bars, ring, bias, fc, norm, xwin, ypart, ybuf, nblob, nin, nact0, nact1, nzb, total;
+    int bars, ring, bias, fc, norm, xwin, ypart, nblob, nin, nact0, nact1, nzb, total;
 };
 
 // alias: the noise net's weights, inputs, activations and outputs (59 KB for the default net) are carved out of the ring
@@ -74,8 +79,7 @@ __host__ __device__ inline TcSmem tc_layout(int nslots, int slot_floats, int lay
     L.fc = o;     o += TC_HID * 8 + 8;
     L.norm = o;   o += align_up(2 * window * 8 + 12, 4);
     L.xwin = o;   o += window * 8 * TC_TN;
-    L.ypart = o;  o += 2 * 8 * TC_TN;
-    L.ybuf = o;   o += 8 * TC_TN;
+    L.ypart = o;  o += 4 * 6 * TC_TN;                        // head partial sums [unit group][6][TN] (same 12 KB for 2 or 4 groups)
     const int end = o;
     if (alias) o = L.ring;
     L.nblob = o;  o += nz.enabled ? align_up(nz.blob_floats, 4) : 0;
