@@ -141,7 +141,7 @@ def test_tensor_core_plans_and_errors():
     # BF16 tcgen05 kernel of the hidden-256 LSTM (rollout_lstm_tc.cu): 128-trajectory tiles, 16 epilogue warps + one
     # control warpgroup, CTA pairs (even grid), a per-CTA scratch of 2 x window operand tiles; everything else refuses the precision
     p = ops.plan(2, 256, 4, 4, 65536, 100, precision="bf16")
-    assert p["variant"] == 6 and p["tile_traj"] == 128 and p["threads"] == 384 and p["grid"] == 148 and p["ntiles"] == 512
+    assert p["variant"] == 6 and p["tile_traj"] == 128 and p["threads"] == 640 and p["grid"] == 148 and p["ntiles"] == 512
     assert p["smem_bytes"] <= 232448
     assert ops.plan(2, 256, 4, 4, 129, 5, precision="bf16")["grid"] == 2 and ops.plan(2, 256, 4, 4, 3 * 128, 5, precision="bf16")["grid"] == 4
     a = _lib.RolloutArgs()
