@@ -286,6 +286,33 @@ typedef struct {
 } mpcdl_train_args;
 int64_t mpcdl_train_param_count(int32_t hidden, int32_t layers);
 int mpcdl_train_mlp_epoch(const mpcdl_train_args* args, void* stream);
+/* ---- Training step of the recurrent models ("fused fwd+bwd for MLP/GRU") ----------------------------
+ * One launch = one EPOCH of train_model (model_scripts/deep_models.py:106-146) for n_models models at once (one CTA per
+ * model): for every batch of `batch` (<= 16) windows in the order `perm` gives (DataLoader(shuffle=False) over the
+ * random_split subset; the last batch may be short): forward of GRU_Model / LSTM_Model (deep_models.py:57-66, 81-92) from
+ * h0 = 0 (init_hidden runs before every batch, :118-119), nn.L1Loss, back-propagation through the window, torch.optim.Adam
+ * step (single-tensor formulas, FP32).  kind 1 = GRU, 2 = LSTM; hidden in {16, 32, 64, 128}; layers 1..8; window 1..8.
+ * theta / adam_m / adam_v hold the model's parameters()  flattened in torch order (per layer weight_ih, weight_hh, bias_ih,
+ * bias_hh; then full_c.weight, full_c.bias), one model every `param_stride` floats (>= mpcdl_train_rnn_param_count, a
+ * multiple of 4; all three 16-byte aligned).  work = caller-allocated scratch of n_models * mpcdl_train_rnn_work_floats
+ * floats (16-byte aligned; contents need no initialisation). */
+typedef struct {
+    float* theta;              /* device [n_models, param_stride]                                                        */
+    float* adam_m;             /* device [n_models, param_stride] exp_avg                                                */
+    float* adam_v;             /* device [n_models, param_stride] exp_avg_sq                                             */
+    const float* featrs;       /* device [n_rows, window, 8] z-scored windows (deep_models.RobotData.featrs)             */
+    const float* labels;       /* device [n_rows, 6]                                                                     */
+    const int32_t* perm;       /* device [n_models, n_samples] row of every training sample of this epoch, in order      */
+    float* losses;             /* device [n_models, ceil(n_samples / batch)] or NULL                                     */
+    float* work;               /* device [n_models, mpcdl_train_rnn_work_floats(...)]                                    */
+    int64_t n_rows, param_stride;
+    int32_t n_models, n_samples, batch, kind, hidden, layers, window;
+    int64_t step0;             /* optimizer steps already taken                                                          */
+    double lr, beta1, beta2, eps;
+} mpcdl_train_rnn_args;
+int64_t mpcdl_train_rnn_param_count(int32_t kind, int32_t hidden, int32_t layers);
+int64_t mpcdl_train_rnn_work_floats(int32_t kind, int32_t hidden, int32_t layers, int32_t window);
+int mpcdl_train_rnn_epoch(const mpcdl_train_rnn_args* args, void* stream);
 /* Validation loss of basic_model.py:112-122: losses[i] = L1 loss of batch i of `batch` consecutive rows of output / labels [n,6]. */
 int mpcdl_l1_batches(const float* output, const float* labels, int64_t n, int32_t batch, float* losses, void* stream);
 

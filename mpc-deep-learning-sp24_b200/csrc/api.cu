@@ -1084,6 +1084,49 @@ int mpcdl_train_mlp_epoch(const mpcdl_train_args* a, void* stream) {
     return MPCDL_OK;
 }
 
+int64_t mpcdl_train_rnn_param_count(int32_t kind, int32_t hidden, int32_t layers) {
+    if ((kind != 1 && kind != 2) || hidden < 1 || layers < 1) return 0;
+    return train_rnn_param_count(kind, hidden, layers);
+}
+
+int64_t mpcdl_train_rnn_work_floats(int32_t kind, int32_t hidden, int32_t layers, int32_t window) {
+    if ((kind != 1 && kind != 2) || hidden < 1 || layers < 1 || window < 1) return 0;
+    return train_rnn_work_floats(kind, hidden, layers, window);
+}
+
+int mpcdl_train_rnn_epoch(const mpcdl_train_rnn_args* a, void* stream) {
+    if (!a) return fail(MPCDL_ERR_ARG, "args is NULL");
+    if (!a->theta || !a->adam_m || !a->adam_v || !a->featrs || !a->labels || !a->perm || !a->work)
+        return fail(MPCDL_ERR_ARG, "theta/adam_m/adam_v/featrs/labels/perm/work must be non-NULL device pointers");
+    if (a->n_models < 1 || a->n_samples < 1 || a->batch < 1 || a->n_rows < 1 || a->step0 < 0)
+        return fail(MPCDL_ERR_ARG, "n_models=%d n_samples=%d batch=%d n_rows=%lld step0=%lld must be positive", a->n_models, a->n_samples, a->batch,
+                    (long long)a->n_rows, (long long)a->step0);
+    if ((a->kind != 1 && a->kind != 2) || (a->hidden != 16 && a->hidden != 32 && a->hidden != 64 && a->hidden != 128) || a->layers < 1 ||
+        a->layers > MAX_LAYERS || a->window < 1 || a->window > MAX_WINDOW || a->batch > TRAIN_RNN_MAXB)
+        return fail(MPCDL_ERR_UNSUPPORTED, "recurrent training kernel: kind=%d (1 GRU, 2 LSTM) hidden=%d (16, 32, 64, 128) layers=%d (1..%d) window=%d (1..%d) batch=%d (1..%d)",
+                    a->kind, a->hidden, a->layers, MAX_LAYERS, a->window, MAX_WINDOW, a->batch, TRAIN_RNN_MAXB);
+    if (!(a->lr > 0.0) || !(a->beta1 >= 0.0 && a->beta1 < 1.0) || !(a->beta2 >= 0.0 && a->beta2 < 1.0) || !(a->eps >= 0.0))
+        return fail(MPCDL_ERR_ARG, "Adam hyper-parameters out of range (lr=%g beta1=%g beta2=%g eps=%g)", a->lr, a->beta1, a->beta2, a->eps);
+    const long long np = train_rnn_param_count(a->kind, a->hidden, a->layers);
+    if (a->param_stride < np || (a->param_stride & 3))
+        return fail(MPCDL_ERR_ARG, "param_stride=%lld must be a multiple of 4 and >= %lld parameters", (long long)a->param_stride, np);
+    if (((uintptr_t)a->theta | (uintptr_t)a->adam_m | (uintptr_t)a->adam_v | (uintptr_t)a->work) & 15)
+        return fail(MPCDL_ERR_ARG, "theta/adam_m/adam_v/work must be 16-byte aligned");
+    const int smem = train_rnn_smem_bytes(a->kind, a->hidden);
+    if (smem > SMEM_LIMIT) return fail(MPCDL_ERR_UNSUPPORTED, "recurrent training kernel: hidden=%d needs %d bytes of shared memory", a->hidden, smem);
+    const DevInfo* di = nullptr;
+    if (int drc = sm100_device(di)) return drc;
+    TrainRnnParams p;
+    memset(&p, 0, sizeof(p));
+    p.theta = a->theta; p.adam_m = a->adam_m; p.adam_v = a->adam_v; p.featrs = a->featrs; p.labels = a->labels; p.perm = a->perm;
+    p.losses = a->losses; p.work = a->work; p.work_floats = train_rnn_work_floats(a->kind, a->hidden, a->layers, a->window);
+    p.param_stride = a->param_stride; p.n_samples = a->n_samples; p.batch = a->batch; p.kind = a->kind; p.hidden = a->hidden;
+    p.layers = a->layers; p.window = a->window; p.step0 = a->step0; p.lr = a->lr; p.beta1 = a->beta1; p.beta2 = a->beta2; p.eps = a->eps;
+    cudaError_t e = launch_train_rnn(p, a->n_models, smem, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "recurrent training kernel launch failed: %s (smem=%d)", cudaGetErrorString(e), smem);
+    return MPCDL_OK;
+}
+
 int mpcdl_l1_batches(const float* output, const float* labels, int64_t n, int32_t batch, float* losses, void* stream) {
     if (!output || !labels || !losses || n < 1 || batch < 1) return fail(MPCDL_ERR_ARG, "mpcdl_l1_batches: bad arguments");
     const DevInfo* di = nullptr;

@@ -78,6 +78,23 @@ struct TrainParams {
     double lr, beta1, beta2, eps;
 };
 
+// fused training epoch of the recurrent models (train_rnn_kernels.cu; deep_models.py:106-146): one CTA per model
+constexpr int TRAIN_RNN_MAXB = 16;     // batch rows per optimizer step (the reference's BATCH_S grid is 8 / 16)
+struct TrainRnnParams {
+    float* theta;            // [n_models][param_stride] parameters in torch order (per layer w_ih, w_hh, b_ih, b_hh; full_c.weight, .bias), in/out
+    float* adam_m;           // [n_models][param_stride] exp_avg, in/out
+    float* adam_v;           // [n_models][param_stride] exp_avg_sq, in/out
+    const float* featrs;     // [n_rows, window, 8]  (shared by all models)
+    const float* labels;     // [n_rows, 6]
+    const int* perm;         // [n_models][n_samples]
+    float* losses;           // [n_models][ceil(n_samples / batch)] or null
+    float* work;             // [n_models][work_floats] scratch (k-major weight copies, saved activations, gate gradients)
+    long long work_floats, param_stride;
+    int n_samples, batch, kind, hidden, layers, window;
+    long long step0;
+    double lr, beta1, beta2, eps;
+};
+
 // standalone noise-net entry points (aux_kernels.cu): forward (H = 1, explicit history) and DynamicsNN closed loop
 struct AuxParams {
     NoiseParams nz;

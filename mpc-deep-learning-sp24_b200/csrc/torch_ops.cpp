@@ -412,6 +412,40 @@ Tensor train_mlp_epoch(Tensor theta, Tensor adam_m, Tensor adam_v, const Tensor&
     check_status(mpcdl_train_mlp_epoch(&a, at::cuda::getCurrentCUDAStream(dev.index()).stream()));
     return losses;
 }
+// one epoch of train_model (model_scripts/deep_models.py:106-146) for n_models recurrent models in one launch: theta / adam_m /
+// adam_v [n_models, param_stride] updated in place; featrs [n, window, 8]; perm [n_models, n_samples] int32; work = scratch
+// [n_models, mpcdl_train_rnn_work_floats]; -> per-batch losses [n_models, n_batches]
+Tensor train_rnn_epoch(Tensor theta, Tensor adam_m, Tensor adam_v, const Tensor& featrs, const Tensor& labels, const Tensor& perm, Tensor work,
+                       int64_t kind, int64_t hidden, int64_t layers, int64_t batch, int64_t step0, double lr, double beta1, double beta2, double eps) {
+    TORCH_CHECK(theta.is_cuda(), "mpcdl: theta must be a CUDA tensor (no CPU fallback), got ", theta.device());
+    const c10::Device dev = theta.device();
+    TORCH_CHECK(featrs.dim() == 3 && featrs.size(2) == 8 && labels.dim() == 2 && labels.size(1) == 6 && labels.size(0) == featrs.size(0),
+                "mpcdl: featrs [n,window,8] and labels [n,6] expected, got ", featrs.sizes(), " ", labels.sizes());
+    const int64_t window = featrs.size(1);
+    const int64_t np = mpcdl_train_rnn_param_count((int32_t)kind, (int32_t)hidden, (int32_t)layers);
+    const int64_t wf = mpcdl_train_rnn_work_floats((int32_t)kind, (int32_t)hidden, (int32_t)layers, (int32_t)window);
+    TORCH_CHECK(np > 0 && wf > 0, "mpcdl: kind must be 1 (GRU) or 2 (LSTM), hidden / layers / window positive");
+    TORCH_CHECK(theta.dim() == 2 && theta.size(1) >= np && theta.size(1) % 4 == 0, "mpcdl: theta must be [n_models, stride] with stride a multiple of 4 and >= ",
+                np, " for hidden=", hidden, " layers=", layers, ", got ", theta.sizes());
+    TORCH_CHECK(adam_m.sizes() == theta.sizes() && adam_v.sizes() == theta.sizes(), "mpcdl: adam_m / adam_v must have theta's shape");
+    TORCH_CHECK(perm.scalar_type() == at::kInt && perm.is_cuda() && perm.device() == dev && perm.is_contiguous() && perm.dim() == 2 &&
+                perm.size(0) == theta.size(0) && perm.size(1) >= 1, "mpcdl: perm must be a contiguous int32 CUDA tensor [n_models, n_samples]");
+    TORCH_CHECK(work.numel() >= theta.size(0) * wf, "mpcdl: work must hold n_models x ", wf, " floats, got ", work.numel());
+    TORCH_CHECK(batch >= 1 && step0 >= 0, "mpcdl: batch >= 1 and step0 >= 0 expected");
+    mpcdl_train_rnn_args a;
+    memset(&a, 0, sizeof(a));
+    a.theta = f32c(theta, "theta", dev); a.adam_m = f32c(adam_m, "adam_m", dev); a.adam_v = f32c(adam_v, "adam_v", dev);
+    a.featrs = f32c(featrs, "featrs", dev); a.labels = f32c(labels, "labels", dev); a.work = f32c(work, "work", dev);
+    a.perm = static_cast<const int32_t*>(perm.data_ptr());
+    a.n_rows = featrs.size(0); a.param_stride = theta.size(1); a.n_models = (int32_t)theta.size(0); a.n_samples = (int32_t)perm.size(1);
+    a.batch = (int32_t)batch; a.kind = (int32_t)kind; a.hidden = (int32_t)hidden; a.layers = (int32_t)layers; a.window = (int32_t)window;
+    a.step0 = step0; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
+    Tensor losses = at::empty({theta.size(0), (perm.size(1) + batch - 1) / batch}, theta.options());
+    a.losses = static_cast<float*>(losses.data_ptr());
+    c10::cuda::CUDAGuard guard(dev);
+    check_status(mpcdl_train_rnn_epoch(&a, at::cuda::getCurrentCUDAStream(dev.index()).stream()));
+    return losses;
+}
 // per-batch L1 loss of consecutive batches (the validation loop of basic_model.py:112-122): output / labels [n,6] -> [ceil(n / batch)]
 Tensor l1_batches(const Tensor& output, const Tensor& labels, int64_t batch) {
     TORCH_CHECK(output.is_cuda(), "mpcdl: output must be a CUDA tensor (no CPU fallback), got ", output.device());
@@ -473,6 +507,8 @@ TORCH_LIBRARY(mpcdl, m) {
     m.def("resample(Tensor t, Tensor q, Tensor u, float dataset_dt, int step, int n_interp) -> (Tensor, Tensor)");
     m.def("train_mlp_epoch(Tensor(a!) theta, Tensor(b!) adam_m, Tensor(c!) adam_v, Tensor featrs, Tensor labels, Tensor perm, int hidden, int layers, "
           "int batch, int step0, float lr, float beta1, float beta2, float eps) -> Tensor");
+    m.def("train_rnn_epoch(Tensor(a!) theta, Tensor(b!) adam_m, Tensor(c!) adam_v, Tensor featrs, Tensor labels, Tensor perm, Tensor(d!) work, "
+          "int kind, int hidden, int layers, int batch, int step0, float lr, float beta1, float beta2, float eps) -> Tensor");
     m.def("l1_batches(Tensor output, Tensor labels, int batch) -> Tensor");
     m.def("cdr_decode(Tensor blob, Tensor offsets) -> (Tensor, Tensor)");
     m.def("debug_poison_smem(Tensor like) -> ()");
@@ -493,6 +529,7 @@ TORCH_LIBRARY_IMPL(mpcdl, CUDA, m) {
     m.impl("curve_metrics", &curve_metrics);
     m.impl("resample", &resample);
     m.impl("train_mlp_epoch", &train_mlp_epoch);
+    m.impl("train_rnn_epoch", &train_rnn_epoch);
     m.impl("l1_batches", &l1_batches);
     m.impl("cdr_decode", &cdr_decode);
     m.impl("debug_poison_smem", &debug_poison_smem);

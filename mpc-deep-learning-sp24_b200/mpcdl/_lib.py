@@ -80,6 +80,14 @@ class TrainArgs(C.Structure):
                 ("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
 
 
+class TrainRnnArgs(C.Structure):
+    _fields_ = [("theta", C.c_void_p), ("adam_m", C.c_void_p), ("adam_v", C.c_void_p), ("featrs", C.c_void_p), ("labels", C.c_void_p),
+                ("perm", C.c_void_p), ("losses", C.c_void_p), ("work", C.c_void_p), ("n_rows", C.c_int64), ("param_stride", C.c_int64),
+                ("n_models", C.c_int32), ("n_samples", C.c_int32), ("batch", C.c_int32), ("kind", C.c_int32), ("hidden", C.c_int32),
+                ("layers", C.c_int32), ("window", C.c_int32), ("step0", C.c_int64),
+                ("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
+
+
 class MppiArgs(C.Structure):
     _fields_ = [
         ("costs", C.c_void_p),
@@ -124,7 +132,8 @@ class Plan(C.Structure):
 EXPORTS = ("mpcdl_blob_floats", "mpcdl_pack_mlp", "mpcdl_pack_rnn", "mpcdl_blob_floats_tc", "mpcdl_pack_rnn_tc", "mpcdl_pack_mlp_tc", "mpcdl_noise_blob_floats", "mpcdl_pack_noise",
            "mpcdl_rollout", "mpcdl_rollout_static_scratch", "mpcdl_rollout_scratch_bytes", "mpcdl_rollout_plan", "mpcdl_noise_forward", "mpcdl_error_metrics", "mpcdl_mppi_workspace_floats", "mpcdl_mppi_min", "mpcdl_mppi_reduce", "mpcdl_ffma_peak", "mpcdl_ffma2_peak", "mpcdl_last_error", "mpcdl_version",
            "mpcdl_dataset_stats", "mpcdl_dataset_build", "mpcdl_rollout_inputs", "mpcdl_curve_metrics", "mpcdl_resample",
-           "mpcdl_train_param_count", "mpcdl_train_mlp_epoch", "mpcdl_l1_batches", "mpcdl_cdr_decode",
+           "mpcdl_train_param_count", "mpcdl_train_mlp_epoch", "mpcdl_train_rnn_param_count", "mpcdl_train_rnn_work_floats",
+           "mpcdl_train_rnn_epoch", "mpcdl_l1_batches", "mpcdl_cdr_decode",
            "mpcdl_debug_poison_smem")
 
 
@@ -173,6 +182,12 @@ def _load():
     lib.mpcdl_ffma_peak.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.mpcdl_train_param_count.restype = C.c_int64
     lib.mpcdl_train_param_count.argtypes = [C.c_int32, C.c_int32]
+    lib.mpcdl_train_rnn_param_count.restype = C.c_int64
+    lib.mpcdl_train_rnn_param_count.argtypes = [C.c_int32, C.c_int32, C.c_int32]
+    lib.mpcdl_train_rnn_work_floats.restype = C.c_int64
+    lib.mpcdl_train_rnn_work_floats.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+    lib.mpcdl_train_rnn_epoch.restype = C.c_int
+    lib.mpcdl_train_rnn_epoch.argtypes = [C.POINTER(TrainRnnArgs), C.c_void_p]
     lib.mpcdl_train_mlp_epoch.restype = C.c_int
     lib.mpcdl_train_mlp_epoch.argtypes = [C.POINTER(TrainArgs), C.c_void_p]
     lib.mpcdl_l1_batches.restype = C.c_int

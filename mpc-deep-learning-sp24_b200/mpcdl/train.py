@@ -11,7 +11,13 @@ validation loss = mean of the per-batch L1 losses, ReduceLROnPlateau(default set
 "Early stop triggered." / "Bad loss" messages.  What differs is where the random numbers come from: the sample orders are
 drawn with an explicit torch.Generator (the reference uses the global RNG through DataLoader), so a run is reproducible
 and the oracle (oracle/train_ref.py) can be handed the same orders.  Dropout (do_drop=True) is not implemented in the
-fused step and raises."""
+fused step and raises.
+
+Recurrent models (round 2): ``train_model`` of model_scripts/deep_models.py:106-146 for GRU_Model / LSTM_Model runs on
+csrc/train_rnn_kernels.cu (forward over the window, L1 loss, back-propagation through time, Adam; one CTA per model).  The
+reference's loop differs from the MLP's in two places, both kept: the DataLoader does NOT shuffle (``shuffle=False``, :112),
+so every epoch walks the random_split subset in the same order; and ``init_hidden`` runs before every batch when STATE_F
+(:118-119), so a training batch always starts from h = 0 whether the model is stateful or not."""
 from __future__ import annotations
 
 import torch
@@ -37,19 +43,34 @@ class AdamState:
     """exp_avg / exp_avg_sq / step of torch.optim.Adam for the flattened parameter vectors of n_models models"""
 
     def __init__(self, n_models, n_params, device):
+        self.n_params = n_params
         self.m = torch.zeros(n_models, n_params, device=device)
         self.v = torch.zeros(n_models, n_params, device=device)
         self.step = 0
+        self._work = None                         # scratch of the recurrent kernel, kept between epochs
 
 
 def _check_model(model):
-    from .models import Basic_Model
+    """-> ("mlp", hidden, layers) | ("gru" | "lstm", hidden, layers)"""
+    from .models import Basic_Model, GRU_Model, LSTM_Model
+    if isinstance(model, GRU_Model):
+        return "gru", model.hidden, model.layers
+    if isinstance(model, LSTM_Model):
+        return "lstm", model.hidden, model.layers
     if not isinstance(model, Basic_Model):
-        raise RuntimeError("mpcdl.train: the fused training step exists for Basic_Model (basic_model.py); got " + type(model).__name__)
+        raise RuntimeError("mpcdl.train: the fused training step exists for Basic_Model (basic_model.py) and GRU_Model / LSTM_Model "
+                           "(deep_models.py); got " + type(model).__name__)
     if any(isinstance(l, torch.nn.Dropout) for l in model.layers):
         raise RuntimeError("mpcdl.train: do_drop=True (Dropout between the layers) is not implemented in the fused training step")
     hidden, layers, _ = model._desc()
-    return hidden, layers
+    return "mlp", hidden, layers
+
+
+def param_count(model):
+    kind, hidden, layers = _check_model(model)
+    if kind == "mlp":
+        return _lib.lib.mpcdl_train_param_count(hidden, layers)
+    return _lib.lib.mpcdl_train_rnn_param_count(_lib.GRU if kind == "gru" else _lib.LSTM, hidden, layers)
 
 
 def train_epoch(models, state, featrs, labels, perm, batch_s=16, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
@@ -58,19 +79,37 @@ def train_epoch(models, state, featrs, labels, perm, batch_s=16, lr=1e-3, betas=
     the order the batches take them.  Updates the modules' parameters and `state` in place; returns the per-batch L1 losses
     [n_models, n_batches] (what ``loss.item()`` would give, basic_model.py:106)."""
     models = list(models) if isinstance(models, (list, tuple)) else [models]
-    hidden, layers = _check_model(models[0])
+    kind, hidden, layers = _check_model(models[0])
     for m in models[1:]:
-        if _check_model(m) != (hidden, layers):
-            raise RuntimeError("mpcdl.train: the models of one launch must share hidden and layers")
+        if _check_model(m) != (kind, hidden, layers):
+            raise RuntimeError("mpcdl.train: the models of one launch must share family, hidden and layers")
     dev = featrs.device
     flats = [_flat(m) for m in models]
-    theta = torch.stack([f[0].to(dev) for f in flats]).contiguous()
     perm = perm.to(device=dev, dtype=torch.int32)
     if perm.dim() == 1:
         perm = perm[None].expand(len(models), -1)
     perm = perm.contiguous()
-    losses = torch.ops.mpcdl.train_mlp_epoch(theta, state.m, state.v, featrs.contiguous(), labels.contiguous(), perm, hidden, layers,
-                                             int(batch_s), int(state.step), float(lr), float(betas[0]), float(betas[1]), float(eps))
+    if kind == "mlp":
+        theta = torch.stack([f[0].to(dev) for f in flats]).contiguous()
+        losses = torch.ops.mpcdl.train_mlp_epoch(theta, state.m, state.v, featrs.contiguous(), labels.contiguous(), perm, hidden, layers,
+                                                 int(batch_s), int(state.step), float(lr), float(betas[0]), float(betas[1]), float(eps))
+    else:
+        if featrs.dim() != 3:
+            raise RuntimeError("mpcdl.train: a recurrent model trains on windows [n, ft_size, 8] (deep_models.RobotData.featrs)")
+        k = _lib.GRU if kind == "gru" else _lib.LSTM
+        n_params = state.n_params
+        stride = (n_params + 3) // 4 * 4          # the kernel reads a model's vectors as float4: one model every 4k floats
+        theta, am, av = (torch.zeros(len(models), stride, device=dev) for _ in range(3))
+        theta[:, :n_params] = torch.stack([f[0].to(dev) for f in flats])
+        am[:, :n_params], av[:, :n_params] = state.m, state.v
+        wf = _lib.lib.mpcdl_train_rnn_work_floats(k, hidden, layers, int(featrs.shape[1]))
+        if state._work is None or state._work.numel() < len(models) * wf:
+            state._work = torch.empty(len(models) * wf, device=dev)
+        losses = torch.ops.mpcdl.train_rnn_epoch(theta, am, av, featrs.contiguous(), labels.contiguous(), perm, state._work, k,
+                                                 hidden, layers, int(batch_s), int(state.step), float(lr), float(betas[0]), float(betas[1]),
+                                                 float(eps))
+        theta = theta[:, :n_params]
+        state.m.copy_(am[:, :n_params]); state.v.copy_(av[:, :n_params])
     state.step += (perm.shape[1] + batch_s - 1) // batch_s
     for (_, ps), row in zip(flats, theta):
         _unflat(row, ps)
@@ -80,6 +119,8 @@ def train_epoch(models, state, featrs, labels, perm, batch_s=16, lr=1e-3, betas=
 def validation_loss(model, featrs, labels, batch_s=16):
     """v_loss of basic_model.py:112-122: mean over the batches of consecutive samples of the per-batch L1 loss"""
     with torch.no_grad():
+        if getattr(model, "state_f", False):
+            model.init_hidden(featrs.shape[0], featrs.device)       # deep_models.py:136-137: zeros before every validation batch
         out = model(featrs)
     return torch.ops.mpcdl.l1_batches(out.contiguous(), labels.contiguous(), int(batch_s)).mean().item()
 
@@ -123,13 +164,14 @@ def train_model(model, dataset, epochs=100, batch_s=16, learn_r=1e-3, seed=0, pa
     g = torch.Generator().manual_seed(seed)
     t_idx, v_idx = split_indices(featrs.shape[0], g)
     vf, vl = featrs[v_idx.to(dev)].contiguous(), labels[v_idx.to(dev)].contiguous()
-    hidden, layers = _check_model(model)
-    state = AdamState(1, _lib.lib.mpcdl_train_param_count(hidden, layers), dev)
+    kind, hidden, layers = _check_model(model)
+    state = AdamState(1, param_count(model), dev)
     sched = _Plateau(learn_r)
     lr, min_loss, patience = learn_r, float("inf"), 0
     hist = dict(valid_loss=[], train_loss=[], lr=[], best=None, code=None)
     for i in range(epochs):
-        order = t_idx[torch.randperm(t_idx.numel(), generator=g)]            # DataLoader(shuffle=True): a new order every epoch
+        # basic_model.py:84 DataLoader(shuffle=True): a new order every epoch; deep_models.py:112 shuffle=False: the subset's own order
+        order = t_idx[torch.randperm(t_idx.numel(), generator=g)] if kind == "mlp" else t_idx
         losses = train_epoch(model, state, featrs, labels, order, batch_s, lr)
         v_loss = validation_loss(model, vf, vl, batch_s)
         lr = sched.step(v_loss)

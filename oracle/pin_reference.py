@@ -18,7 +18,8 @@ What it does
   4. drives the REFERENCE modules in a python loop (closed loop of DESIGN.md) and stores the
      trajectories as golden vectors; checks oracle.rollout_* reproduces them bit-for-bit.
   5.-7. DynamicsDataset resampling, the second validation pickle + the validation sweep, and the training step
-     (reference Basic_Model + nn.L1Loss + optim.Adam over explicit batches == oracle/train_ref.py, golden train.npz).
+     (reference Basic_Model + nn.L1Loss + optim.Adam over explicit batches == oracle/train_ref.py, golden train.npz;
+     7b: the same for the reference's GRU_Model / LSTM_Model, state_f False and True, golden train_rnn.npz).
 Exit code 0 and "PINNED" on the last line when everything holds.
 """
 from __future__ import annotations
@@ -517,6 +518,61 @@ with torch.no_grad():
 check("f4 validation loss: oracle == reference loop (bit)", vl_ref / nb_ == TR.validation_loss(mine_t, mfn[:800], mln[:800], 32))
 train_gold["Basic_64_2_32/valid800"] = np.asarray(vl_ref / nb_)
 np.savez_compressed(f"{GOLD}/train.npz", **train_gold)
+
+# ---------------------------------------------------------------------------- 7b. training step of the recurrent models (f4)
+# The reference's GRU_Model / LSTM_Model classes (deep_models.py:44-92), nn.L1Loss and optim.Adam stepped the way
+# deep_models.py:114-127 does (init_hidden before the batch when STATE_F) == oracle/train_ref.train_steps_rnn on the restated
+# modules, bit for bit, for state_f False and True; losses + parameters after 20 steps stored in tests/golden/train_rnn.npz.
+rf8, rl8 = R.rnn_dataset(bags, 8)
+rfn8, rln8 = R.apply_zscore(rf8, rl8, R.zscore_stats(rf8, rl8))
+rnn_gold = {}
+for kind_, hidden_, layers_, ft_, batch_, state_f_ in (("GRU", 32, 2, 4, 16, False), ("LSTM", 16, 4, 8, 8, True), ("GRU", 16, 1, 4, 16, True)):
+    feats_, labs_ = (rfn, rln) if ft_ == 4 else (rfn8, rln8)
+    torch.manual_seed(200 + hidden_)
+    ref_t = getattr(rnn, f"{kind_}_Model")(8, hidden_, 6, layers_, state_f_).cpu()
+    mine_t = (R.RefGRU if kind_ == "GRU" else R.RefLSTM)(8, hidden_, 6, layers_)
+    mine_t.load_state_dict(ref_t.state_dict())
+    init_flat = torch.cat([p_.detach().reshape(-1) for p_ in ref_t.parameters()]).clone()
+    order_ = torch.randperm(feats_.shape[0], generator=torch.Generator().manual_seed(6))[:20 * batch_ - 5]    # last batch short
+    opt_ref = torch.optim.Adam(ref_t.parameters(), lr=rnn.LEARN_R)
+    crit_ref = torch.nn.L1Loss()
+    ref_t.train()
+    ref_losses = []
+    for b0_ in range(0, len(order_), batch_):                       # the body of deep_models.py:115-127 on explicit batches
+        idx_ = order_[b0_:b0_ + batch_]
+        if state_f_:
+            ref_t.init_hidden(len(idx_))
+        opt_ref.zero_grad()
+        loss_ = crit_ref(ref_t(feats_[idx_]), labs_[idx_])
+        loss_.backward()
+        opt_ref.step()
+        ref_losses.append(loss_.item())
+    my_losses, _ = TR.train_steps_rnn(mine_t, feats_, labs_, order_, batch_, rnn.LEARN_R)
+    flat_ref = torch.cat([p_.detach().reshape(-1) for p_ in ref_t.parameters()])
+    flat_mine = torch.cat([p_.detach().reshape(-1) for p_ in mine_t.parameters()])
+    check(f"f4 training: {len(ref_losses)} Adam steps of {kind_}_{hidden_}_{layers_}_{ft_} (batch {batch_}, state_f {state_f_}): oracle == reference "
+          f"class + optimizer (bit), loss {ref_losses[0]:.4f} -> {ref_losses[-1]:.4f}",
+          torch.equal(flat_ref, flat_mine) and torch.equal(torch.tensor(ref_losses), my_losses))
+    if kind_ == "GRU" and hidden_ == 16:
+        continue                                                    # the stateful GRU is a check only
+    tag = f"{kind_}_{hidden_}_{layers_}_{ft_}_{batch_}"
+    rnn_gold[f"{tag}/init"], rnn_gold[f"{tag}/order"] = init_flat.numpy(), order_.numpy()
+    rnn_gold[f"{tag}/losses"], rnn_gold[f"{tag}/final"] = np.asarray(ref_losses, dtype=np.float32), flat_ref.numpy()
+vl_ref = 0.0
+with torch.no_grad():
+    ref_t = rnn.LSTM_Model(8, 16, 6, 4, True).cpu()
+    torch.nn.utils.vector_to_parameters(torch.from_numpy(rnn_gold["LSTM_16_4_8_8/final"]).clone(), ref_t.parameters())
+    mine_t = R.RefLSTM(8, 16, 6, 4)
+    mine_t.load_state_dict(ref_t.state_dict())
+    ref_t.eval()
+    nb_ = 0
+    for b0_ in range(0, 400, 8):                                    # deep_models.py:130-146 on the first 400 windows
+        ref_t.init_hidden(len(rfn8[b0_:b0_ + 8]))
+        vl_ref += crit_ref(ref_t(rfn8[b0_:b0_ + 8]), rln8[b0_:b0_ + 8]).item()
+        nb_ += 1
+check("f4 validation loss of a recurrent model: oracle == reference loop (bit)", vl_ref / nb_ == TR.validation_loss_rnn(mine_t, rfn8[:400], rln8[:400], 8))
+rnn_gold["LSTM_16_4_8_8/valid400"] = np.asarray(vl_ref / nb_)
+np.savez_compressed(f"{GOLD}/train_rnn.npz", **rnn_gold)
 
 # ---------------------------------------------------------------------------- 8. rosbag2 CDR decode (f4) -- fixture + consistency
 # The deserialiser of the reference (rclpy + mpclab_msgs) is absent, so nothing here is a parity pin (oracle/cdr_ref.py

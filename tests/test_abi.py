@@ -179,6 +179,36 @@ def test_training_entry_points_without_device():
     assert lib.mpcdl_l1_batches(None, None, 10, 16, None, None) == -1
 
 
+def test_recurrent_training_entry_points_without_device():
+    """mpcdl_train_rnn_epoch: parameter / scratch counts and the argument checks, which come before any device work"""
+    from mpcdl import _lib
+    lib = _lib.lib
+    # SURVEY.md App. B: GRU_64_4 89 478 and LSTM_64_4 119 174 parameters
+    assert lib.mpcdl_train_rnn_param_count(_lib.GRU, 64, 4) == 89478 and lib.mpcdl_train_rnn_param_count(_lib.LSTM, 64, 4) == 119174
+    assert lib.mpcdl_train_rnn_param_count(0, 64, 4) == 0 and lib.mpcdl_train_rnn_work_floats(3, 64, 4, 4) == 0
+    # scratch: k-major weight copies + [L][T][16][h] outputs + [L][T][16][4h | 5h] saved gates + 2 [T][16][Gh] gate gradients + dY + the batch
+    assert lib.mpcdl_train_rnn_work_floats(_lib.GRU, 64, 4, 4) == 89480 + 16384 + 65536 + 2 * 12288 + 4096 + 512
+    assert lib.mpcdl_train_rnn_work_floats(_lib.LSTM, 16, 2, 8) == 3944 + 4096 + 20480 + 2 * 8192 + 2048 + 1024
+    assert lib.mpcdl_train_rnn_epoch(None, None) == -1
+    a = _lib.TrainRnnArgs()
+    assert lib.mpcdl_train_rnn_epoch(C.byref(a), None) == -1 and b"non-NULL" in lib.mpcdl_last_error()
+    for f in ("theta", "adam_m", "adam_v", "featrs", "labels", "perm", "work"):
+        setattr(a, f, 16)
+    a.n_models, a.n_samples, a.batch, a.n_rows, a.kind, a.hidden, a.layers, a.window = 1, 100, 16, 100, _lib.GRU, 64, 4, 4
+    a.lr, a.beta1, a.beta2, a.eps, a.param_stride = 1e-3, 0.9, 0.999, 1e-8, 89480
+    for field, bad in (("hidden", 48), ("batch", 17), ("window", 9), ("kind", 0)):
+        good = getattr(a, field)
+        setattr(a, field, bad)
+        assert lib.mpcdl_train_rnn_epoch(C.byref(a), None) == -2 and f"{field}={bad}".encode() in lib.mpcdl_last_error()   # MPCDL_ERR_UNSUPPORTED
+        setattr(a, field, good)
+    a.param_stride = 89478
+    assert lib.mpcdl_train_rnn_epoch(C.byref(a), None) == -1 and b"param_stride" in lib.mpcdl_last_error()
+    a.param_stride, a.theta = 89480, 20
+    assert lib.mpcdl_train_rnn_epoch(C.byref(a), None) == -1 and b"16-byte" in lib.mpcdl_last_error()
+    a.theta, a.lr = 16, -1.0
+    assert lib.mpcdl_train_rnn_epoch(C.byref(a), None) == -1 and b"Adam" in lib.mpcdl_last_error()
+
+
 def test_mppi_entry_points_without_device():
     from mpcdl import _lib
     lib = _lib.lib
@@ -214,7 +244,8 @@ def test_ctypes_mirror_matches_the_compiled_header(tmp_path):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     structs = {"mpcdl_rollout_args": _lib.RolloutArgs, "mpcdl_noise_args": _lib.NoiseArgs, "mpcdl_mppi_args": _lib.MppiArgs,
                "mpcdl_plan": _lib.Plan, "mpcdl_model_desc": _lib.ModelDesc, "mpcdl_dataset_desc": _lib.DatasetDesc,
-               "mpcdl_resample_args": _lib.ResampleArgs, "mpcdl_train_args": _lib.TrainArgs}
+               "mpcdl_resample_args": _lib.ResampleArgs, "mpcdl_train_args": _lib.TrainArgs,
+               "mpcdl_train_rnn_args": _lib.TrainRnnArgs}
     cfield = {"lam": "lambda"}                       # `lambda` is a Python keyword: the mirror calls it lam
     lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "mpcdl.h"', 'int main(void) {']
     for cname, cls in structs.items():
