@@ -137,6 +137,7 @@ __global__ void __launch_bounds__(TRN_THREADS, 1) train_rnn_kernel(const TrainRn
                             for (int g = 0; g < 4; ++g) a[g][r] = bih[g * h + jj] + bhh[g * h + jj];
                         }
                     }
+                    const float* wp = wihT + jj;
 #pragma unroll 2
                     for (int k = 0; k < in; k += 4) {
                         float4 xv[4];
@@ -144,10 +145,10 @@ __global__ void __launch_bounds__(TRN_THREADS, 1) train_rnn_kernel(const TrainRn
                         for (int r = 0; r < 4; ++r) xv[r] = *reinterpret_cast<const float4*>(xs + (r0 + r) * in + k);
 #pragma unroll
                         for (int kk = 0; kk < 4; ++kk) {
-                            const float* w = wihT + (size_t)(k + kk) * GH + jj;
                             float wg[G];
 #pragma unroll
-                            for (int g = 0; g < G; ++g) wg[g] = w[g * h];
+                            for (int g = 0; g < G; ++g) wg[g] = wp[g * h];
+                            wp += GH;
 #pragma unroll
                             for (int r = 0; r < 4; ++r) {
                                 const float x = kk == 0 ? xv[r].x : kk == 1 ? xv[r].y : kk == 2 ? xv[r].z : xv[r].w;
@@ -157,6 +158,7 @@ __global__ void __launch_bounds__(TRN_THREADS, 1) train_rnn_kernel(const TrainRn
                         }
                     }
                     if (f > 0) {            // h_{-1} = 0: the recurrent product of frame 0 vanishes
+                        const float* wq = whhT + jj;
 #pragma unroll 2
                         for (int k = 0; k < h; k += 4) {
                             float4 xv[4];
@@ -164,10 +166,10 @@ __global__ void __launch_bounds__(TRN_THREADS, 1) train_rnn_kernel(const TrainRn
                             for (int r = 0; r < 4; ++r) xv[r] = *reinterpret_cast<const float4*>(hp + (r0 + r) * h + k);
 #pragma unroll
                             for (int kk = 0; kk < 4; ++kk) {
-                                const float* w = whhT + (size_t)(k + kk) * GH + jj;
                                 float wg[G];
 #pragma unroll
-                                for (int g = 0; g < G; ++g) wg[g] = w[g * h];
+                                for (int g = 0; g < G; ++g) wg[g] = wq[g * h];
+                                wq += GH;
 #pragma unroll
                                 for (int r = 0; r < 4; ++r) {
                                     const float x = kk == 0 ? xv[r].x : kk == 1 ? xv[r].y : kk == 2 ? xv[r].z : xv[r].w;
@@ -314,35 +316,43 @@ __global__ void __launch_bounds__(TRN_THREADS, 1) train_rnn_kernel(const TrainRn
                 }
                 __syncthreads();
                 // -- phase B: dh_{f-1} = direct + g_r W_hh  (f > 0);  d x_f = g_i W_ih -> DY[f] of the layer below (l > 0).
-                //    task = (4 rows, column k): lanes over k read W[j][k] coalesced
+                //    task = (2 rows, 4 columns k0..k0+3): lanes over column groups read W[j][k0..] as coalesced float4; running
+                //    pointers, two j-steps of four rows in flight (the loop waits on L2 / L1 latency, not on bandwidth)
                 const float* const gr_s = KIND == 1 ? gsr : gsi;
-                const int nt_h = f > 0 ? (RB / 4) * h : 0, nt_x = l > 0 ? (RB / 4) * in : 0;
+                const int nt_h = f > 0 ? (RB / 2) * (h / 4) : 0, nt_x = l > 0 ? (RB / 2) * (in / 4) : 0;
                 for (int task = tid; task < nt_h + nt_x; task += TRN_THREADS) {
                     const bool rec = task < nt_h;
                     const int t2 = rec ? task : task - nt_h;
-                    const int ncol = rec ? h : in;
-                    const int bq = t2 / ncol, k = t2 - bq * ncol, r0 = bq * 4;
-                    const float* W = (rec ? whh : wih) + k;
-                    const float* gsrc = rec ? gr_s : gsi;
-                    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+                    const int ncol = rec ? h : in, ncq = ncol >> 2;
+                    const int bq = t2 / ncq, k0 = (t2 - bq * ncq) * 4, r0 = bq * 2;
+                    const float* wp = (rec ? whh : wih) + k0;
+                    const float* g0 = (rec ? gr_s : gsi) + r0 * GH;
+                    const float* g1 = g0 + GH;
+                    float a0[4] = {0.f, 0.f, 0.f, 0.f}, a1[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 2
                     for (int j = 0; j < GH; j += 4) {
-                        float4 gv[4];
+                        const float4 ga = *reinterpret_cast<const float4*>(g0 + j), gb = *reinterpret_cast<const float4*>(g1 + j);
+                        float4 w[4];
 #pragma unroll
-                        for (int r = 0; r < 4; ++r) gv[r] = *reinterpret_cast<const float4*>(gsrc + (r0 + r) * GH + j);
-                        const float w0 = W[(size_t)j * ncol], w1 = W[(size_t)(j + 1) * ncol], w2 = W[(size_t)(j + 2) * ncol], w3 = W[(size_t)(j + 3) * ncol];
+                        for (int q = 0; q < 4; ++q) { w[q] = *reinterpret_cast<const float4*>(wp); wp += ncol; }
+                        const float gav[4] = {ga.x, ga.y, ga.z, ga.w}, gbv[4] = {gb.x, gb.y, gb.z, gb.w};
 #pragma unroll
-                        for (int r = 0; r < 4; ++r) {
-                            acc[r] = fmaf(gv[r].x, w0, acc[r]); acc[r] = fmaf(gv[r].y, w1, acc[r]);
-                            acc[r] = fmaf(gv[r].z, w2, acc[r]); acc[r] = fmaf(gv[r].w, w3, acc[r]);
+                        for (int q = 0; q < 4; ++q) {
+                            a0[0] = fmaf(gav[q], w[q].x, a0[0]); a0[1] = fmaf(gav[q], w[q].y, a0[1]);
+                            a0[2] = fmaf(gav[q], w[q].z, a0[2]); a0[3] = fmaf(gav[q], w[q].w, a0[3]);
+                            a1[0] = fmaf(gbv[q], w[q].x, a1[0]); a1[1] = fmaf(gbv[q], w[q].y, a1[1]);
+                            a1[2] = fmaf(gbv[q], w[q].z, a1[2]); a1[3] = fmaf(gbv[q], w[q].w, a1[3]);
                         }
                     }
                     if (rec) {
+                        float* d0 = dhs + r0 * h + k0;
+                        const float* e0 = dhd + r0 * h + k0;
 #pragma unroll
-                        for (int r = 0; r < 4; ++r) dhs[(r0 + r) * h + k] = dhd[(r0 + r) * h + k] + acc[r];
+                        for (int c = 0; c < 4; ++c) { d0[c] = e0[c] + a0[c]; d0[h + c] = e0[h + c] + a1[c]; }
                     } else {
-#pragma unroll
-                        for (int r = 0; r < 4; ++r) DY[(size_t)f * RB * h + (r0 + r) * h + k] = acc[r];
+                        float* d0 = DY + (size_t)f * RB * h + r0 * h + k0;
+                        *reinterpret_cast<float4*>(d0) = make_float4(a0[0], a0[1], a0[2], a0[3]);
+                        *reinterpret_cast<float4*>(d0 + h) = make_float4(a1[0], a1[1], a1[2], a1[3]);
                     }
                 }
                 __syncthreads();
@@ -366,19 +376,20 @@ __global__ void __launch_bounds__(TRN_THREADS, 1) train_rnn_kernel(const TrainRn
                         for (int c = 0; c < 4; ++c) acc[a][c] = 0.f;
                     const float* gsrc = ih ? GI : GR;
                     if (KIND != 1) gsrc = GI;
-                    for (int f = ih ? 0 : 1; f < T; ++f) {
-                        const float* xf = ih ? Xl + (size_t)f * RB * ncol : Yl + (size_t)(f - 1) * RB * h;
-                        const float* gf = gsrc + (size_t)f * RB * GH;
+                    // frames and rows are contiguous: one flat loop over (f, b) with running pointers; W_hh pairs g_f with h_{f-1}
+                    const float* gp = gsrc + (ih ? 0 : (size_t)RB * GH) + j0;
+                    const float* xp = (ih ? Xl : Yl) + k0;
+                    const int nfb = (ih ? T : T - 1) * RB;
 #pragma unroll 4
-                        for (int b = 0; b < RB; ++b) {
-                            const float4 gv = *reinterpret_cast<const float4*>(gf + b * GH + j0);
-                            const float4 xv = *reinterpret_cast<const float4*>(xf + b * ncol + k0);
-                            const float ga[4] = {gv.x, gv.y, gv.z, gv.w}, xa[4] = {xv.x, xv.y, xv.z, xv.w};
+                    for (int n = 0; n < nfb; ++n) {
+                        const float4 gv = *reinterpret_cast<const float4*>(gp);
+                        const float4 xv = *reinterpret_cast<const float4*>(xp);
+                        gp += GH; xp += ncol;
+                        const float ga[4] = {gv.x, gv.y, gv.z, gv.w}, xa[4] = {xv.x, xv.y, xv.z, xv.w};
 #pragma unroll
-                            for (int a = 0; a < 4; ++a)
+                        for (int a = 0; a < 4; ++a)
 #pragma unroll
-                                for (int c = 0; c < 4; ++c) acc[a][c] = fmaf(ga[a], xa[c], acc[a][c]);
-                        }
+                            for (int c = 0; c < 4; ++c) acc[a][c] = fmaf(ga[a], xa[c], acc[a][c]);
                     }
                     const int base = ih ? O.wih[l] : O.whh[l];
 #pragma unroll
