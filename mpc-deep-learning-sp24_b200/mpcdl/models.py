@@ -7,7 +7,8 @@ forward / rollout run on the fused sm_100a kernels.
 
 The torch sub-modules (``layers``, ``gru``/``lstm``, ``full_c``, ``model``) are kept purely as parameter
 containers so ``load_state_dict(torch.load(file))`` of the shipped checkpoints works unchanged
-(eval_models.py:27-28, 54-55); no torch kernel runs in forward()/rollout().  Inputs must be CUDA
+(eval_models.py:27-28, 54-55); rollout() is one launch of the library and no torch compute kernel (forward() of a recurrent
+model adds a zero fill of its dummy controls and a copy of the carried h_state).  Inputs must be CUDA
 tensors: there is no CPU path (the dispatcher raises for CPU tensors).
 """
 from __future__ import annotations
