@@ -24,6 +24,8 @@ prints one JSON line.
             figure, which also counts the recurrent GEMM of window frame 0 that a stateless model never runs (h0 = 0)
   workloads (N = 1, default workload only) the same device-timed measurement for every other BASELINE configuration:
             c2, c3 (fp32 / tf32x3 / tf32), c3s, c4 (bf16, fp32), c5 on the tcgen05 kernel (tf32x3 / tf32), c5g -- about a minute
+  training  (same run) one device-timed epoch of the fused training kernels for 148 models side by side: MLP / GRU / LSTM 64 x 4,
+            batches of 16 -> Adam model-steps/s (a side table, not the headline metric)
   cpu_baseline   oracle port (reference nn.Modules in the python loop, oracle/rollout_ref.py) on the host cores,
             rank 0, N = 1 only, bounded sample
 --impl reference times that same oracle port as the reference arm (the reference is pure Python and /root/reference
@@ -401,6 +403,48 @@ def roofline_of(pb, k_ms, fp32_peak, peaks):
                     "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
 
 
+def training_entries(dev, n_models=148):
+    """Device-timed epoch of the fused training kernels (csrc/train_kernels.cu, train_rnn_kernels.cu) for
+    n_models models side by side (one CTA each) on the validation bag: the reference's 80 % split in batches of 16 -> Adam
+    model-steps / s.  A side table of the default run, not part of the headline metric."""
+    import mpcdl
+    from mpcdl import _lib, synth
+    bags = synth.load_bags()
+    out = {}
+    for name, kind, hidden, layers, window in (("mlp_64_4", 0, 64, 4, None), ("gru_64_4_4", _lib.GRU, 64, 4, 4), ("lstm_64_4_4", _lib.LSTM, 64, 4, 4)):
+        ds = mpcdl.RobotData(bags, window)
+        f, l = ds.featrs.float().to(dev).contiguous(), ds.labels.float().to(dev).contiguous()
+        n_train, batch = int(f.shape[0] * 0.8), 16
+        steps = (n_train + batch - 1) // batch
+        nm = n_models if kind == 0 else 2 * n_models          # recurrent kernel: two models per SM beyond one per SM
+        torch.manual_seed(0)
+        m = (mpcdl.Basic_Model(8, hidden, 6, layers, False) if kind == 0 else
+             (mpcdl.GRU_Model if kind == _lib.GRU else mpcdl.LSTM_Model)(8, hidden, 6, layers, False))
+        flat = torch.cat([p.detach().reshape(-1) for p in m.parameters()]).to(dev)
+        stride = flat.numel() if kind == 0 else (flat.numel() + 3) // 4 * 4
+        theta = torch.zeros(nm, stride, device=dev)
+        theta[:, :flat.numel()] = flat
+        am, av = torch.zeros_like(theta), torch.zeros_like(theta)
+        g = torch.Generator().manual_seed(0)
+        orders = torch.stack([torch.randperm(f.shape[0], generator=g)[:n_train] for _ in range(nm)]).int().to(dev)
+        if kind == 0:
+            run = lambda s0: torch.ops.mpcdl.train_mlp_epoch(theta, am, av, f, l, orders, hidden, layers, batch, s0, 1e-3, 0.9, 0.999, 1e-8)  # noqa: E731
+        else:
+            work = torch.empty(nm * _lib.lib.mpcdl_train_rnn_work_floats(kind, hidden, layers, window), device=dev)
+            run = lambda s0: torch.ops.mpcdl.train_rnn_epoch(theta, am, av, f, l, orders, work, kind, hidden, layers, batch, s0, 1e-3, 0.9, 0.999, 1e-8)  # noqa: E731
+        run(0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        losses = run(steps)
+        e1.record()
+        e1.synchronize()
+        ms = e0.elapsed_time(e1)
+        out[name] = {"value": nm * steps / (ms * 1e-3), "unit": "Adam model-steps/s", "n_models": nm, "steps_per_epoch": steps,
+                     "batch": batch, "epoch_ms": ms, "us_per_step": ms / steps * 1e3, "gpu_launches": 2,
+                     "mean_loss_second_epoch": float(losses.mean().item())}
+    return out
+
+
 def table_entry(key, prec, max_steps, dev, flush, fp32_peak, peaks, local):
     """device-timed measurement of one more BASELINE configuration (N = 1): >= 3 warm-ups, L2 flushed between steps"""
     pb = Problem(key, prec, dev, 0, 1)
@@ -561,6 +605,11 @@ def run_native(args, key):
                 table[f"{k2}_{p2}"] = {"error": f"{type(e).__name__}: {e}"}
         line["workloads"] = table
         line["gpu_launches_total"] += sum(v.get("gpu_launches", 0) + 3 for v in table.values())
+        try:
+            line["training"] = training_entries(dev)
+            line["gpu_launches_total"] += sum(v["gpu_launches"] for v in line["training"].values())
+        except Exception as e:              # a side table: never at the price of the headline line
+            line["training"] = {"error": f"{type(e).__name__}: {e}"}
     if rank == 0:
         if world == 1 and not args.skip_cpu:
             val, med, threads, sample, _ = time_cpu(w, 9, 1)

@@ -1122,7 +1122,7 @@ int mpcdl_train_rnn_epoch(const mpcdl_train_rnn_args* a, void* stream) {
     p.losses = a->losses; p.work = a->work; p.work_floats = train_rnn_work_floats(a->kind, a->hidden, a->layers, a->window);
     p.param_stride = a->param_stride; p.n_samples = a->n_samples; p.batch = a->batch; p.kind = a->kind; p.hidden = a->hidden;
     p.layers = a->layers; p.window = a->window; p.step0 = a->step0; p.lr = a->lr; p.beta1 = a->beta1; p.beta2 = a->beta2; p.eps = a->eps;
-    cudaError_t e = launch_train_rnn(p, a->n_models, smem, static_cast<cudaStream_t>(stream));
+    cudaError_t e = launch_train_rnn(p, a->n_models, di->sms, smem, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return fail(MPCDL_ERR_CUDA, "recurrent training kernel launch failed: %s (smem=%d)", cudaGetErrorString(e), smem);
     return MPCDL_OK;
 }

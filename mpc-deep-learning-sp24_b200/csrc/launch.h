@@ -56,7 +56,7 @@ cudaError_t launch_train_mlp(const TrainParams& p, int n_models, int smem_bytes,
 long long train_rnn_param_count(int kind, int hidden, int layers);
 long long train_rnn_work_floats(int kind, int hidden, int layers, int window);
 int train_rnn_smem_bytes(int kind, int hidden);
-cudaError_t launch_train_rnn(const TrainRnnParams& p, int n_models, int smem_bytes, cudaStream_t st);
+cudaError_t launch_train_rnn(const TrainRnnParams& p, int n_models, int num_sms, int smem_bytes, cudaStream_t st);
 cudaError_t launch_l1_batches(const float* output, const float* labels, long long n, int batch, float* losses, cudaStream_t st);
 cudaError_t launch_poison_smem(int num_sms, cudaStream_t st);
 cudaError_t launch_ffma_peak(float* out, int iters, int grid, bool packed, cudaStream_t st);

@@ -45,8 +45,11 @@ __device__ __forceinline__ float adam_update(float w, float g, float& m, float& 
 
 // KIND: 1 = GRU, 2 = LSTM.  theta / adam_m / adam_v [n_models][n_params]; featrs [n_rows][T][8]; labels [n_rows][6];
 // perm [n_models][n_samples]; work [n_models][work_floats]; losses [n_models][n_batches]
-template <int KIND>
-__global__ void __launch_bounds__(TRN_THREADS, 1) train_rnn_kernel(const TrainRnnParams p) {
+// MINB = CTAs per SM the register allocation allows: 1 (up to 255 registers: fastest for a single model, 367 us per step of
+// GRU 64 x 4) when there are no more models than SMs, 2 (128 registers) beyond that -- two models per SM hide each other's
+// load latency: 2.8e5 -> 3.8e5 model-steps/s for 296 models (profiles/r02/train_rnn/timing_two_per_sm.log)
+template <int KIND, int MINB>
+__global__ void __launch_bounds__(TRN_THREADS, MINB) train_rnn_kernel(const TrainRnnParams p) {
     constexpr int G = KIND == 1 ? 3 : 4;          // gate blocks of a weight matrix
     constexpr int NS = KIND == 1 ? 4 : 5;         // saved planes per cell: GRU r z n nh / LSTM i f g o c
     extern __shared__ __align__(16) float sm[];
@@ -444,18 +447,18 @@ int train_rnn_smem_bytes(int kind, int hidden) {
     return (RB * h + 2 * RB * h + 2 * RB * GH + 3 * RB * h + RB * 8 + TRN_THREADS) * 4;
 }
 
-cudaError_t launch_train_rnn(const TrainRnnParams& p, int n_models, int smem_bytes, cudaStream_t st) {
-    cudaError_t e;
-    if (p.kind == 1) {
-        e = cudaFuncSetAttribute(train_rnn_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-        if (e != cudaSuccess) return e;
-        train_rnn_kernel<1><<<n_models, TRN_THREADS, smem_bytes, st>>>(p);
-    } else {
-        e = cudaFuncSetAttribute(train_rnn_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
-        if (e != cudaSuccess) return e;
-        train_rnn_kernel<2><<<n_models, TRN_THREADS, smem_bytes, st>>>(p);
-    }
+template <int KIND, int MINB>
+static cudaError_t launch_train_rnn_t(const TrainRnnParams& p, int n_models, int smem_bytes, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(train_rnn_kernel<KIND, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+    if (e != cudaSuccess) return e;
+    train_rnn_kernel<KIND, MINB><<<n_models, TRN_THREADS, smem_bytes, st>>>(p);
     return cudaGetLastError();
+}
+
+cudaError_t launch_train_rnn(const TrainRnnParams& p, int n_models, int num_sms, int smem_bytes, cudaStream_t st) {
+    const bool two = n_models > num_sms && 2 * (smem_bytes + 1024) <= SMEM_LIMIT;       // two CTAs fit one SM's shared memory
+    if (p.kind == 1) return two ? launch_train_rnn_t<1, 2>(p, n_models, smem_bytes, st) : launch_train_rnn_t<1, 1>(p, n_models, smem_bytes, st);
+    return two ? launch_train_rnn_t<2, 2>(p, n_models, smem_bytes, st) : launch_train_rnn_t<2, 1>(p, n_models, smem_bytes, st);
 }
 
 }  // namespace mpcdl

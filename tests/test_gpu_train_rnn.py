@@ -174,3 +174,25 @@ def test_rnn_train_model_learns_and_follows_the_reference_protocol(bags):
         train.train_model(mpcdl.GRU_Model(8, 16, 6, 2, False).to(DEV), ds, epochs=1, batch_s=32, verbose=False)
     with pytest.raises(RuntimeError):                 # an MLP dataset (rows, not windows)
         train.train_model(mpcdl.GRU_Model(8, 16, 6, 2, False).to(DEV), mpcdl.RobotData(bags), epochs=1, verbose=False)
+
+
+def test_rnn_more_models_than_sms_run_two_per_sm_with_identical_results(bags):
+    """above one model per SM the launcher picks the 128-register instantiation (two CTAs per SM): same arithmetic, so a
+    model's result must not depend on which instantiation trained it"""
+    from mpcdl import train
+    f, l = _data(bags, 4)
+    fd, ld = f.to(DEV), l.to(DEV)
+    n_big = torch.cuda.get_device_properties(0).multi_processor_count + 12
+    order = torch.randperm(f.shape[0], generator=torch.Generator().manual_seed(4))[:5 * 16 - 2]
+    for kind in ("gru", "lstm"):
+        base = [_models(kind, 32, 2, False, seed=s)[0] for s in (5, 6)]
+        many = [copy.deepcopy(base[i % 2]) for i in range(n_big)]
+        st = train.AdamState(n_big, _flat(base[0]).numel(), DEV)
+        loss = train.train_epoch(many, st, fd, ld, order, 16, 1e-3)
+        assert loss.shape == (n_big, 5)
+        for i in (0, 1):
+            s1 = train.AdamState(1, _flat(base[i]).numel(), DEV)
+            l1 = train.train_epoch(base[i], s1, fd, ld, order, 16, 1e-3)
+            for j in (i, i + 2, n_big - 1 - ((n_big - 1 - i) % 2)):       # copies of model i sit at the indices of its parity
+                assert j % 2 == i and j < n_big
+                assert torch.equal(l1[0], loss[j]) and torch.equal(_flat(base[i]), _flat(many[j])), (kind, i, j)

@@ -16,3 +16,8 @@ for k, v in d.get("workloads", {}).items():
     rr = v["roofline"]
     print(f"  {k:12s} {v['value']:.4g} traj-steps/s  kernel {v['kernel_ms']:9.3f} ms x{v['steps']:3d}  frac {rr['frac']:.3f} ({rr['bound']}, survey-flop {rr['frac_survey_flop']:.3f})  "
           f"clk {v['clocks']['sm_mhz']} {v['clocks']['reasons']}")
+for k, v in d.get("training", {}).items():
+    if not isinstance(v, dict):
+        print(f"  training ERROR {v}")
+        break
+    print(f"  train {k:12s} {v['value']:.4g} {v['unit']}  {v['n_models']} models x {v['steps_per_epoch']} steps in {v['epoch_ms']:.2f} ms ({v['us_per_step']:.1f} us per step)")

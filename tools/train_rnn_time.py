@@ -32,7 +32,7 @@ for kind, hidden, layers, window, batch in (("gru", 16, 4, 4, 16), ("gru", 64, 4
     fd, ld = f.cuda(), l.cuda()
     flat = torch.cat([p.detach().reshape(-1) for p in ref.parameters()])
     steps = (n_train + batch - 1) // batch
-    for nm in (1, 148, 296):
+    for nm in (1, 148, 296, 592):
         theta = torch.zeros(nm, stride, device="cuda"); theta[:, :npar] = flat.cuda()
         am, av = torch.zeros_like(theta), torch.zeros_like(theta)
         work = torch.empty(nm * wf, device="cuda")
