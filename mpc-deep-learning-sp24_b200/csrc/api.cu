@@ -281,7 +281,11 @@ int make_mc_plan(const mpcdl_rollout_args& a, McPlan& pl, int num_sms) {
     NoiseParams nz;
     fill_noise(nz, a);
     pl.ntiles = (int)((a.N + TC_TN - 1) / TC_TN);
-    pl.tiles_per_cta = (a.tune_ntg == 1 || a.tune_ntg == 2) ? a.tune_ntg : (pl.ntiles > num_sms ? MC_TILES : 1);
+    pl.tiles_per_cta = (a.tune_ntg == 1 || a.tune_ntg == 2 || a.tune_ntg == 4) ? a.tune_ntg : (pl.ntiles > num_sms ? MC_TILES : 1);
+    // four tile slots per CTA (128 TMEM columns each: D + A_hi): one-pass TF32 without the noise net, and enough tiles to fill them
+    const bool four_ok = a.precision == MPCDL_PREC_TF32 && !nz.enabled;
+    if (!a.tune_ntg && four_ok && pl.ntiles >= 8 * num_sms) pl.tiles_per_cta = MC_TILES_MAX;
+    if (pl.tiles_per_cta == 4 && !four_ok) return fail(MPCDL_ERR_UNSUPPORTED, "tensor-core MLP: four tiles per CTA need MPCDL_PREC_TF32 without the noise net");
     // the noise net's buffers are per tile: when two sets do not fit beside the weights (tf32x3, 4 layers), one tile per CTA
     if (pl.tiles_per_cta == 2 && mc_layout((int)m.w_floats, a.model.layers, nz, 2).total * 4 > SMEM_LIMIT) pl.tiles_per_cta = 1;
     pl.smem_bytes = std::max(mc_layout((int)m.w_floats, a.model.layers, nz, pl.tiles_per_cta).total * 4, 120 * 1024);
@@ -763,7 +767,7 @@ int mpcdl_rollout_plan(const mpcdl_rollout_args* a, mpcdl_plan* out) {
         rc = make_mc_plan(*a, mp, sms);
         if (rc) return rc;
         memset(out, 0, sizeof(*out));
-        out->rt = 1; out->rj = 64; out->n_tg = TC_TN; out->tile_traj = TC_TN; out->threads = MC_THREADS; out->grid = mp.grid;
+        out->rt = 1; out->rj = 64; out->n_tg = TC_TN; out->tile_traj = TC_TN; out->threads = mc_threads(mp.tiles_per_cta); out->grid = mp.grid;
         out->smem_bytes = mp.smem_bytes; out->resident = 1; out->nslots = 1; out->ntiles = mp.ntiles; out->variant = 5;
         out->ksplit = mp.tiles_per_cta;
         return MPCDL_OK;

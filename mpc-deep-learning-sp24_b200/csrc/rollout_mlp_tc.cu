@@ -59,8 +59,16 @@ __device__ __forceinline__ void mc_stage16(uint32_t t_hi, uint32_t t_lo, const f
     if (X3) umma::tmem_st16(t_lo, lo);
 }
 
-template <int PREC>
-__global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __grid_constant__ McRolloutParams p) {
+// TILES x EW: 2 tiles with 8 epilogue warps each (two threads per trajectory, 256 TMEM columns per tile: both precisions, noise
+// net), or -- TF32 without the noise net, enough tiles -- 4 tiles with 4 epilogue warps each (one thread per trajectory and all
+// 64 units, 128 columns per tile: D + A_hi): a layer of a tile is a latency chain (MMAs -> commit -> tcgen05.ld -> bias / ReLU
+// -> tcgen05.st -> arrive, ~1900 clocks) and four chains in flight keep the tensor pipe busier than two (1 M x 50: 8.15 ->
+// 5.50 ms).  Two tcgen05.ld blocks in flight per wait were measured on top: slower (5.75 ms, register pressure at 640 threads).
+template <int PREC, int TILES, int EW>
+__global__ void __launch_bounds__(mc_threads(TILES), 1) rollout_mlp_tc_kernel(const __grid_constant__ McRolloutParams p) {
+    static_assert((TILES == 2 && EW == 8) || (TILES == 4 && EW == 4 && PREC == PREC_TF32), "tile configurations of tc_params.h");
+    constexpr int TCOLS = 512 / TILES;               // TMEM columns per tile
+    constexpr int UPT = TC_HID / (EW / 4);           // hidden units per epilogue thread
     constexpr bool X3 = PREC == PREC_TF32X3;
     constexpr int HID = TC_HID, TN = TC_TN;
     extern __shared__ __align__(1024) float sm[];
@@ -71,13 +79,13 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
     const long long N = p.io.N;
 
     uint64_t* wfull = reinterpret_cast<uint64_t*>(sm + L.bars);
-    uint64_t* opnd = wfull + 1;                      // [2] operands of the next layer are in TMEM
-    uint64_t* accb = opnd + 2;                       // [2] the layer's MMAs have completed
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accb + 2);
+    uint64_t* opnd = wfull + 1;                      // [TILES] operands of the next layer are in TMEM
+    uint64_t* accb = opnd + TILES;                   // [TILES] the layer's MMAs have completed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accb + TILES);
 
     if (tid == 0) {
         mbar_init(wfull, 1);
-        for (int t = 0; t < MC_TILES; ++t) { mbar_init(&opnd[t], MC_EPI_WARPS * 32); mbar_init(&accb[t], 1); }
+        for (int t = 0; t < TILES; ++t) { mbar_init(&opnd[t], EW * 32); mbar_init(&accb[t], 1); }
         mbar_fence_init();
         // weights -> shared memory, once (hi blocks, and lo blocks for tf32x3)
         uint32_t bytes = 0;
@@ -89,7 +97,7 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                 bulk_g2s(sm + L.w + m.w_smem[l] + o, m.blob + m.w_off[l] + o, min(4096u, n - o) * 4u, wfull);
         }
     }
-    if (warp == MC_TILES * MC_EPI_WARPS) { umma::tmem_alloc(tmem_slot, 512); umma::tmem_relinquish(); }
+    if (warp == TILES * EW) { umma::tmem_alloc(tmem_slot, 512); umma::tmem_relinquish(); }
     for (int i = tid; i < (NL + 1) * HID; i += blockDim.x) sm[L.bias + i] = m.blob[m.bias_off + i];
     for (int i = tid; i < HID * 8 + 8; i += blockDim.x) sm[L.out + i] = m.blob[m.out_off + i];
     for (int i = tid; i < 28; i += blockDim.x) sm[L.norm + i] = p.io.norm[i];       // f_mean8 f_std8 l_mean6 l_std6
@@ -102,11 +110,11 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
     const int tpc = m.tiles_per_cta;
     const int ngroups = (p.io.ntiles + tpc - 1) / tpc;                 // tile groups, one per CTA iteration
 
-    constexpr int EW = MC_EPI_WARPS, NEPI = MC_TILES * MC_EPI_WARPS;
+    constexpr int NEPI = TILES * EW;
     if (warp >= NEPI) {
         // ============================================================== MMA issuer of tile slot (warp - NEPI)
         const int ts = warp - NEPI;
-        const uint32_t tcol = tbase + ts * MC_TILE_COLS;
+        const uint32_t tcol = tbase + ts * TCOLS;
         const uint32_t wbase = smem_u32(sm + L.w);
         uint32_t par = 0;
         mbar_wait(wfull, 0);
@@ -132,9 +140,9 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
         const int ts = warp / EW, we = warp % EW;
         const int q = we & 3, uh = we >> 2;                 // TMEM lane quarter, hidden-unit half
         const int row = q * 32 + lane;
-        const int u0 = uh * 32;
+        const int u0 = uh * UPT;
         const bool owner = uh == 0;
-        const uint32_t tlane = tbase + ts * MC_TILE_COLS + (static_cast<uint32_t>(q * 32) << 16);
+        const uint32_t tlane = tbase + ts * TCOLS + (static_cast<uint32_t>(q * 32) << 16);
         const float* const normS = sm + L.norm;
         const float* const outS = sm + L.out;
         float* const ypart = sm + L.ypart + ts * 6 * TN;
@@ -203,7 +211,7 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                         par ^= 1u;
                         umma::fence_after_sync();
 #pragma unroll
-                        for (int b = 0; b < 2; ++b) {
+                        for (int b = 0; b < UPT / 16; ++b) {
                             float v[16];
                             umma::tmem_ld16(tlane + MC_D + u0 + b * 16, v);
                             umma::wait_ld();
@@ -234,14 +242,18 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
                         }
                     }
                     // the unit-half-1 thread hands its partial output sums to the trajectory's owner thread
-                    if (!owner) {
+                    if (EW == 8) {
+                        if (!owner) {
 #pragma unroll
-                        for (int d = 0; d < 6; ++d) ypart[d * TN + row] = y[d];
+                            for (int d = 0; d < 6; ++d) ypart[d * TN + row] = y[d];
+                        }
+                        named_bar_sync(1 + ts, EW * 32);
                     }
-                    named_bar_sync(1 + ts, EW * 32);
                     if (owner) {
+                        if (EW == 8) {
 #pragma unroll
-                        for (int d = 0; d < 6; ++d) y[d] += ypart[d * TN + row];
+                            for (int d = 0; d < 6; ++d) y[d] += ypart[d * TN + row];
+                        }
                         float nxt[6], nzr[12];
                         if (p.nz.enabled) {
 #pragma unroll
@@ -258,18 +270,22 @@ __global__ void __launch_bounds__(MC_THREADS, 1) rollout_mlp_tc_kernel(const __g
     // ------------------------------------------------------------------ teardown
     umma::fence_before_sync();
     __syncthreads();
-    if (warp == MC_TILES * MC_EPI_WARPS) umma::tmem_dealloc(tbase, 512);
+    if (warp == TILES * EW) umma::tmem_dealloc(tbase, 512);
 }
 
 cudaError_t launch_mlp_tc(const McRolloutParams& p, int grid, int smem_bytes, cudaStream_t st) {
-    auto launch = [&](auto k) {
+    auto launch = [&](auto k, int threads) {
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
         if (e != cudaSuccess) return e;
-        k<<<grid, MC_THREADS, smem_bytes, st>>>(p);
+        k<<<grid, threads, smem_bytes, st>>>(p);
         return cudaGetLastError();
     };
-    if (p.m.prec == PREC_TF32X3) return launch(rollout_mlp_tc_kernel<PREC_TF32X3>);
-    if (p.m.prec == PREC_TF32) return launch(rollout_mlp_tc_kernel<PREC_TF32>);
+    if (p.m.tiles_per_cta == 4) {
+        if (p.m.prec != PREC_TF32 || p.nz.enabled) return cudaErrorInvalidConfiguration;
+        return launch(rollout_mlp_tc_kernel<PREC_TF32, 4, 4>, mc_threads(4));
+    }
+    if (p.m.prec == PREC_TF32X3) return launch(rollout_mlp_tc_kernel<PREC_TF32X3, 2, 8>, mc_threads(2));
+    if (p.m.prec == PREC_TF32) return launch(rollout_mlp_tc_kernel<PREC_TF32, 2, 8>, mc_threads(2));
     return cudaErrorInvalidConfiguration;
 }
 

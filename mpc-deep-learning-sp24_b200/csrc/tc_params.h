@@ -97,10 +97,12 @@ constexpr int TC_MAX_SLOTS = 12;
 // ------------------------------------------------------------------ tensor-core MLP kernel (rollout_mlp_tc.cu)
 namespace mpcdl {
 
-constexpr int MC_TILES = 2;           // trajectory tiles per CTA: the MMA phase of one overlaps the epilogue of the other
-constexpr int MC_EPI_WARPS = 8;       // epilogue warps per tile: lane quarter = warp % 4, unit half = warp / 4 (2 threads per trajectory)
-constexpr int MC_THREADS = (MC_TILES * MC_EPI_WARPS + MC_TILES) * 32;   // + one MMA-issuing warp per tile
-constexpr int MC_TILE_COLS = 256;     // TMEM columns per tile: D [0,64), A_hi [64,128), A_lo [128,192)
+constexpr int MC_TILES = 2;           // trajectory tiles per CTA: the MMA phase of one overlaps the epilogue of the other;
+                                      //   8 epilogue warps per tile (lane quarter = warp % 4, unit half = warp / 4: 2 threads per trajectory),
+                                      //   256 TMEM columns per tile: D [0,64), A_hi [64,128), A_lo [128,192)
+constexpr int MC_TILES_MAX = 4;       // TF32 without the noise net: 4 tiles of 128 columns (D, A_hi), 4 epilogue warps per tile
+// threads of a CTA with `tiles` tile slots: the epilogue warps + one MMA-issuing warp per tile
+__host__ __device__ constexpr int mc_threads(int tiles) { return tiles == 4 ? (4 * 4 + 4) * 32 : (2 * 8 + 2) * 32; }
 
 // blob: [bias (L+1) x 64][out: W^T [64][8], bias [8]][pad to 32] then per layer l = 0..L the matrix
 // W_l [64 rows = units][K = 8 | 64] as [hi block][lo block] in the canonical K-major UMMA order (N = 64).

@@ -257,6 +257,45 @@ def test_t3_mlp_tensor_core_horizon(name, n, prec, gold_stats):
     assert torch.equal(part, states[128:])
 
 
+@pytest.mark.parametrize("name", ["Basic_64_4_32", "Basic_64_1_32"])
+def test_t3_mlp_tensor_core_four_tiles_per_cta(name, gold_stats):
+    """One-pass TF32 with FOUR tile slots per CTA (128 TMEM columns each, one epilogue thread per trajectory): forced with
+    tune=(0, 4) on a ragged batch (97 tiles -> 25 CTAs, the last with one tile) and picked by the planner at >= 8 tiles per SM.
+    Same MMAs as the two-tile form; the FP32 output layer sums its 64 units in one thread instead of two halves, so the two
+    forms agree to FP32 rounding of that sum (<= 2e-6 of the state scale per step, fed back), not bit for bit.  Bounds: T3."""
+    from mpcdl import ops, synth
+    from oracle import rollout_ref as R
+    m, _ = _model(name)
+    st = gold_stats[0]
+    n = 96 * 128 + 70
+    init, U = synth.make_inputs(synth.load_rows(), n, 50, window=0, seed=6)
+    d_init, d_U = init.to(_dev()), U.to(_dev())
+    cost = (torch.zeros(50, 6), torch.ones(6), torch.ones(2))
+    s4, c4 = m.rollout(d_init, d_U, st, precision="tf32", cost=cost, tune=(0, 4, 0, 0))
+    s2, c2 = m.rollout(d_init, d_U, st, precision="tf32", cost=cost, tune=(0, 2, 0, 0))
+    assert torch.isfinite(s4).all() and not torch.equal(s4, torch.zeros_like(s4))
+    one = R.rel_err(s4[:, :1].cpu(), s2[:, :1].cpu()).max().item()
+    assert one <= 2e-6, one                                # the first step differs only by the output layer's summation order
+    ns = 1500
+    sl = slice(n - ns, n)
+    ref64 = R.as_double(R.build_from_name(name, load_ckpt(name))[0])
+    y64 = R.rollout_mlp(ref64, {k: v.double() for k, v in st.items()}, init[sl].double(), U[sl].double())[0]
+    q = _quantiles(R.rel_err(s4[sl].cpu(), y64))
+    for a, b in zip(q, MC_BOUNDS["tf32"][1]):
+        assert a <= b, (q, MC_BOUNDS["tf32"][1])
+    want = (s4 ** 2).sum((1, 2)) + (d_U ** 2).sum((1, 2))
+    assert ((c4 - want).abs() / want).max().item() <= 1e-4
+    # shard invariance and repeatability, bit for bit, in the four-tile form
+    part = m.rollout(d_init[640:].contiguous(), d_U[640:].contiguous(), st, precision="tf32", tune=(0, 4, 0, 0))[0]
+    assert torch.equal(part, s4[640:])
+    assert torch.equal(m.rollout(d_init, d_U, st, precision="tf32", cost=cost, tune=(0, 4, 0, 0))[0], s4)
+    # the planner's pick at >= 8 tiles per SM, cost-only (1200 tiles per ... 160 000 trajectories): equals the forced form
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    assert ops.plan(0, 64, 4, 0, 8 * sms * 128, 50, precision="tf32")["ksplit"] == 4
+    with pytest.raises(RuntimeError):                      # tf32x3 needs 192 columns per tile: no four-tile form
+        m.rollout(d_init, d_U, st, precision="tf32x3", tune=(0, 4, 0, 0))
+
+
 def test_tensor_core_rejects_unsupported():
     m, _ = _model("Basic_16_4_32")
     with pytest.raises(RuntimeError):           # hidden 16: FP32 kernels only, no silent fallback
