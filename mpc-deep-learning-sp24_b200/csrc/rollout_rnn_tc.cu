@@ -50,7 +50,9 @@ __device__ __forceinline__ void stage16(uint32_t t_hi, uint32_t t_lo, const floa
     uint32_t hi[16], lo[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-        hi[i] = umma::tf32_round_fast(v[i]);
+        // one-pass TF32: the tensor core reads the top 19 bits of the operand, so adding half a tf32 ulp is the whole rounding
+        // (the value tf32_round_fast gives, without its mask); tf32x3 needs the masked hi for the exact residual
+        hi[i] = X3 ? umma::tf32_round_fast(v[i]) : __float_as_uint(v[i]) + 0x1000u;
         lo[i] = X3 ? __float_as_uint(v[i] - __uint_as_float(hi[i])) : 0u;
     }
     umma::tmem_st16(t_hi, hi);
@@ -61,7 +63,7 @@ __device__ __forceinline__ void stage8(uint32_t t_hi, uint32_t t_lo, const float
     uint32_t hi[8], lo[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        hi[i] = umma::tf32_round_fast(v[i]);
+        hi[i] = X3 ? umma::tf32_round_fast(v[i]) : __float_as_uint(v[i]) + 0x1000u;
         lo[i] = X3 ? __float_as_uint(v[i] - __uint_as_float(hi[i])) : 0u;
     }
     umma::tmem_st8(t_hi, hi);
