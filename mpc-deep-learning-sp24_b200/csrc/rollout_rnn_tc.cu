@@ -265,9 +265,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) rollout_rnn_tc_kernel(const __g
                                 mbar_wait(&full[us], up);
                                 umma::fence_after_sync();
                                 const uint32_t sb = ring_s + us * slot_bytes;
-                                if (ch < nkx) {              // input part: weight_ih_l{l} . x_f
-                                    if (l == 0) issue_group<CELL, X3, 0, 8, 1>(tbase, sb, tbase + TC_AX_HI, tbase + TC_AX_LO, acc);
-                                    else issue_groups<CELL, X3, 0>(G, tbase, sb, tbase + TC_AX_HI + ch * kg, tbase + TC_AX_LO + ch * kg, acc);
+                                if (ch < nkx) {              // input part: weight_ih_l{l} . x_f (one-pass TF32, window 4: x double-buffered by f & 1)
+                                    const uint32_t ax = tbase + TC_AX_HI + ((FAST && T == TC_T) ? (uint32_t)(f & 1) * 64u : 0u);
+                                    if (l == 0) issue_group<CELL, X3, 0, 8, 1>(tbase, sb, ax, tbase + TC_AX_LO, acc);
+                                    else issue_groups<CELL, X3, 0>(G, tbase, sb, ax + ch * kg, tbase + TC_AX_LO + ch * kg, acc);
                                 } else {                     // recurrent part: weight_hh_l{l} . h_{f-1} (always accumulates)
                                     uint32_t acc_h = 1;
                                     const int k0 = (ch - nkx) * kg;

@@ -27,6 +27,7 @@
     uint32_t cellpar = 0;
     constexpr bool SCR = T > TC_T;                     // sequence through the global scratch (see the header)
     constexpr int SR = SCR ? 2 : T;
+    constexpr bool PRE = FAST && !SCR && T % 2 == 0;   // next cell's input operand staged under this cell's MMAs (TF32, window 4)
     float* const seqb = SCR ? p.seqbuf + (size_t)blockIdx.x * T * HID * TN : nullptr;
     constexpr float C_SIG = FAST ? 0.5f : -1.4426950408889634f;       // pre-activation scale of sigmoid gates
     constexpr float C_TANH = FAST ? 1.0f : 2.8853900817779268f;       // ... of tanh gates (biases pre-scaled alike)
@@ -95,18 +96,24 @@
                 for (int f = 0; f < T; ++f) {
                     const bool has_h = f > 0 || stateful;
                     // ---- publish the A operands of cell (l, f)
-                    if (l == 0) {
-                        if (owner) {                   // per-position z-score of frame f (deep_models.py:35)
-                            int pf = base + f; if (pf >= T) pf -= T;
-                            float xn[8];
+                    // One-pass TF32 leaves the lo columns free: the input operand is double-buffered there (PRE), buffer = f & 1,
+                    // and every cell but a step's first finds its x already staged by the cell before it (see below).
+                    const uint32_t axo = PRE ? static_cast<uint32_t>(f & 1) * 64u : 0u;
+                    auto stage_x0 = [&](int fr, uint32_t off) {        // layer 0: per-position z-score of frame fr (deep_models.py:35)
+                        int pf = base + fr; if (pf >= T) pf -= T;
+                        float xn[8];
 #pragma unroll
-                            for (int k = 0; k < 8; ++k)
-                                xn[k] = __fdiv_rn(__fsub_rn(xwin[(pf * 8 + k) * TN + row], normS[f * 8 + k]), normS[T * 8 + f * 8 + k]);
-                            stage8<X3>(tlane + TC_AX_HI, tlane + TC_AX_LO, xn);
+                        for (int k = 0; k < 8; ++k)
+                            xn[k] = __fdiv_rn(__fsub_rn(xwin[(pf * 8 + k) * TN + row], normS[fr * 8 + k]), normS[T * 8 + fr * 8 + k]);
+                        stage8<X3>(tlane + TC_AX_HI + off, tlane + TC_AX_LO, xn);
+                    };
+                    if (!PRE || (l == 0 && f == 0)) {
+                        if (l == 0) {
+                            if (owner) stage_x0(f, axo);
+                        } else {
+#pragma unroll
+                            for (int b = 0; b < UPT; b += 16) stage16<X3>(tlane + TC_AX_HI + u0 + b, tlane + TC_AX_LO + u0 + b, &seq[0][b]);
                         }
-                    } else {
-#pragma unroll
-                        for (int b = 0; b < UPT; b += 16) stage16<X3>(tlane + TC_AX_HI + u0 + b, tlane + TC_AX_LO + u0 + b, &seq[0][b]);
                     }
                     if (f > 0) {
 #pragma unroll
@@ -126,6 +133,18 @@
                     umma::wait_st();
                     umma::fence_before_sync();
                     mbar_arrive(opnd_ready);
+                    if (PRE && !(l == NL - 1 && f == T - 1)) {
+                        // While this cell's MMAs run the warps would only wait: stage the NEXT cell's input operand into the other
+                        // buffer.  It never depends on this cell: frame f + 1 of layer l - 1 (or of the window), or -- last frame
+                        // of a layer -- frame 0 of layer l, computed T - 1 cells ago; before the rotation both are seq[1].
+                        const uint32_t nxo = static_cast<uint32_t>((f + 1) & 1) * 64u;     // T is even: frame 0 of the next layer -> 0
+                        if (l == 0 && f + 1 < T) {
+                            if (owner) stage_x0(f + 1, nxo);
+                        } else {
+#pragma unroll
+                            for (int b = 0; b < UPT; b += 16) stage16<X3>(tlane + TC_AX_HI + nxo + u0 + b, tlane + TC_AX_LO, &seq[SR > 1 ? 1 : 0][b]);
+                        }
+                    }
                     // ---- gate pre-activations of this cell
                     mbar_wait(acc_ready, cellpar);
                     cellpar ^= 1u;
