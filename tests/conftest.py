@@ -17,6 +17,11 @@ RNN = [f"{k}_64_4_4_{b}_{s}" for k in ("GRU", "LSTM") for b in (16, 64) for s in
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200, sm_100a)")
+    # On the GPU boxes torch's multi-threaded CPU GRU has evaluated the oracle to one of two digests (1 of 44 fresh processes
+    # with all host threads, 0 of 74 with one thread; DESIGN.md 2, profiles/r02/oracle_moved/): the parity session runs the
+    # oracle single-threaded -- the whole GPU suite takes the same 47 s either way.
+    if torch.cuda.is_available() and "MPCDL_TEST_THREADS" not in os.environ:
+        torch.set_num_threads(1)
 
 
 def pytest_collection_modifyitems(config, items):
