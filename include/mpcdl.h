@@ -288,7 +288,7 @@ int64_t mpcdl_train_param_count(int32_t hidden, int32_t layers);
 int mpcdl_train_mlp_epoch(const mpcdl_train_args* args, void* stream);
 /* ---- Training step of the recurrent models ("fused fwd+bwd for MLP/GRU") ----------------------------
  * One launch = one EPOCH of train_model (model_scripts/deep_models.py:106-146) for n_models models at once (one CTA per
- * model): for every batch of `batch` (<= 16) windows in the order `perm` gives (DataLoader(shuffle=False) over the
+ * model): for every batch of `batch` windows (above 16: micro-batches of 16 whose gradients are summed) in the order `perm` gives (DataLoader(shuffle=False) over the
  * random_split subset; the last batch may be short): forward of GRU_Model / LSTM_Model (deep_models.py:57-66, 81-92) from
  * h0 = 0 (init_hidden runs before every batch, :118-119), nn.L1Loss, back-propagation through the window, torch.optim.Adam
  * step (single-tensor formulas, FP32).  kind 1 = GRU, 2 = LSTM; hidden in {16, 32, 64, 128}; layers 1..8; window 1..8.

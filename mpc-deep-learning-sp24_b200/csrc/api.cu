@@ -1106,9 +1106,9 @@ int mpcdl_train_rnn_epoch(const mpcdl_train_rnn_args* a, void* stream) {
         return fail(MPCDL_ERR_ARG, "n_models=%d n_samples=%d batch=%d n_rows=%lld step0=%lld must be positive", a->n_models, a->n_samples, a->batch,
                     (long long)a->n_rows, (long long)a->step0);
     if ((a->kind != 1 && a->kind != 2) || (a->hidden != 16 && a->hidden != 32 && a->hidden != 64 && a->hidden != 128) || a->layers < 1 ||
-        a->layers > MAX_LAYERS || a->window < 1 || a->window > MAX_WINDOW || a->batch > TRAIN_RNN_MAXB)
-        return fail(MPCDL_ERR_UNSUPPORTED, "recurrent training kernel: kind=%d (1 GRU, 2 LSTM) hidden=%d (16, 32, 64, 128) layers=%d (1..%d) window=%d (1..%d) batch=%d (1..%d)",
-                    a->kind, a->hidden, a->layers, MAX_LAYERS, a->window, MAX_WINDOW, a->batch, TRAIN_RNN_MAXB);
+        a->layers > MAX_LAYERS || a->window < 1 || a->window > MAX_WINDOW)
+        return fail(MPCDL_ERR_UNSUPPORTED, "recurrent training kernel: kind=%d (1 GRU, 2 LSTM) hidden=%d (16, 32, 64, 128) layers=%d (1..%d) window=%d (1..%d)",
+                    a->kind, a->hidden, a->layers, MAX_LAYERS, a->window, MAX_WINDOW);
     if (!(a->lr > 0.0) || !(a->beta1 >= 0.0 && a->beta1 < 1.0) || !(a->beta2 >= 0.0 && a->beta2 < 1.0) || !(a->eps >= 0.0))
         return fail(MPCDL_ERR_ARG, "Adam hyper-parameters out of range (lr=%g beta1=%g beta2=%g eps=%g)", a->lr, a->beta1, a->beta2, a->eps);
     const long long np = train_rnn_param_count(a->kind, a->hidden, a->layers);

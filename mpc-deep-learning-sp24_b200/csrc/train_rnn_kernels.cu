@@ -8,7 +8,8 @@
 // ONE launch runs a whole epoch of one model per CTA (the reference's hidden x layers x ft_size x batch grid, deep_models.py:
 // 182-190, or an ensemble, trains side by side): per batch the forward pass through L layers x T window frames, the L1 loss,
 // back-propagation through time over the window, and the Adam step -- the gradient of a weight matrix is summed over the
-// window and the batch in registers and goes straight into Adam, so no gradient buffer exists.
+// window and the batch in registers and goes straight into Adam (a gradient buffer exists only for batches of more than 16 rows,
+// which run as micro-batches).
 // Parameters (358 KB for GRU 64 x 4) do not fit shared memory: they stay in global memory (L2 / L1) in torch order
 // ([gate rows][in]: lanes over `in` read it coalesced in the backward-data products) and as a k-major copy in the work buffer
 // ([in][gate rows]: lanes over hidden units read it coalesced in the forward pass); Adam writes both.
@@ -23,7 +24,7 @@ namespace mpcdl {
 namespace {
 
 constexpr int TRN_THREADS = 256;
-constexpr int RB = TRAIN_RNN_MAXB;     // batch rows held per step (the reference trains with BATCH_S 8 / 16)
+constexpr int RB = TRAIN_RNN_MAXB;     // batch rows held on chip (the reference's grid trains with BATCH_S 8 / 16; larger batches: micro-batches)
 
 struct RnnOff {                        // float offsets inside the torch-ordered parameter vector
     int wih[MAX_LAYERS], whh[MAX_LAYERS], bih[MAX_LAYERS], bhh[MAX_LAYERS], fcw, fcb, total;
@@ -82,6 +83,7 @@ __global__ void __launch_bounds__(TRN_THREADS, MINB) train_rnn_kernel(const Trai
     float* const GR = GI + (size_t)T * RB * GH;                    // [T][RB][GH]     (recurrent side; differs from GI for the GRU's n gate only)
     float* const DY = GR + (size_t)T * RB * GH;                    // [T][RB][h]      gradient of the layer's output sequence
     float* const X0 = DY + (size_t)T * RB * h;                     // [T][RB][8]      the batch's windows
+    float* const GA = X0 + (size_t)T * RB * 8;                     // [n_params]      gradient sums of the earlier micro-batches of a batch > RB rows
     // shared memory
     float* const xs = sm;                                          // [RB][h]  cell input
     float* const hs = xs + RB * h;                                 // [2][RB][h] h_{f-1} / h_f
@@ -104,10 +106,24 @@ __global__ void __launch_bounds__(TRN_THREADS, MINB) train_rnn_kernel(const Trai
     const int n_batches = (p.n_samples + p.batch - 1) / p.batch;
     for (int bi = 0; bi < n_batches; ++bi) {
         const int b0 = bi * p.batch, B = min(p.batch, p.n_samples - b0);       // DataLoader(drop_last=False): the last batch may be short
-        // ---- gather the windows of this batch: X0[f][b][:] (rows >= B are zero and get zero gradients)
+        // ---- Adam's scalars for this step: python doubles in torch.optim.adam._single_tensor_adam, cast where torch casts them
+        AdamC ac;
+        {
+            const double t = (double)(p.step0 + bi + 1);
+            const double bc1 = 1.0 - pow(p.beta1, t), bc2 = 1.0 - pow(p.beta2, t);
+            ac.step_size = (float)(-(p.lr / bc1)); ac.bc2_sqrt = (float)sqrt(bc2);
+            ac.w1 = (float)(1.0 - p.beta1); ac.w2 = (float)(1.0 - p.beta2); ac.b2 = (float)p.beta2; ac.eps = (float)p.eps;
+        }
+        // A batch of more than RB rows (the shipped checkpoints were trained with BATCH_S 64) runs as micro-batches of RB rows:
+        // forward + backward per micro-batch, parameter gradients summed in GA, ONE Adam step with the last micro-batch.
+        float loss_sum = 0.f;                              // thread 0: sum of |out - label| over the batch
+        for (int mb0 = 0; mb0 < B; mb0 += RB) {
+        const int MB = min(RB, B - mb0);
+        const bool first = mb0 == 0, lastmb = mb0 + RB >= B;
+        // ---- gather the windows of this micro-batch: X0[f][b][:] (rows >= MB are zero and get zero gradients)
         for (int i = tid; i < T * RB * 8; i += TRN_THREADS) {
             const int f = i / (RB * 8), b = (i / 8) % RB, k = i & 7;
-            X0[i] = b < B ? __ldg(p.featrs + ((long long)perm[b0 + b] * T + f) * 8 + k) : 0.f;
+            X0[i] = b < MB ? __ldg(p.featrs + ((long long)perm[b0 + mb0 + b] * T + f) * 8 + k) : 0.f;
         }
         __syncthreads();
         // ================= forward: layer-major, frames ascending
@@ -221,8 +237,8 @@ __global__ void __launch_bounds__(TRN_THREADS, MINB) train_rnn_kernel(const Trai
             const float* w = theta + O.fcw + d * h;
             for (int k = 0; k < h; ++k) s = fmaf(htop[b * h + k], w[k], s);
             float dl = 0.f;
-            if (b < B) {
-                const float diff = s - __ldg(p.labels + (long long)perm[b0 + b] * 6 + d);
+            if (b < MB) {
+                const float diff = s - __ldg(p.labels + (long long)perm[b0 + mb0 + b] * 6 + d);
                 const float inv = 1.0f / (float)(B * 6);
                 loss_part = fabsf(diff);
                 dl = diff > 0.f ? inv : diff < 0.f ? -inv : 0.f;
@@ -235,14 +251,9 @@ __global__ void __launch_bounds__(TRN_THREADS, MINB) train_rnn_kernel(const Trai
             if (tid < o) red[tid] += red[tid + o];
             __syncthreads();
         }
-        if (tid == 0 && p.losses) p.losses[mi * n_batches + bi] = red[0] / (float)(B * 6);
-        // ---- Adam's scalars for this step: python doubles in torch.optim.adam._single_tensor_adam, cast where torch casts them
-        AdamC ac;
-        {
-            const double t = (double)(p.step0 + bi + 1);
-            const double bc1 = 1.0 - pow(p.beta1, t), bc2 = 1.0 - pow(p.beta2, t);
-            ac.step_size = (float)(-(p.lr / bc1)); ac.bc2_sqrt = (float)sqrt(bc2);
-            ac.w1 = (float)(1.0 - p.beta1); ac.w2 = (float)(1.0 - p.beta2); ac.b2 = (float)p.beta2; ac.eps = (float)p.eps;
+        if (tid == 0) {
+            loss_sum += red[0];
+            if (lastmb && p.losses) p.losses[mi * n_batches + bi] = loss_sum / (float)(B * 6);
         }
         // ---- d loss / d h_top into DY[T-1] (the other frames of the top layer receive nothing from above)
         for (int i = tid; i < T * RB * h; i += TRN_THREADS) {
@@ -265,9 +276,14 @@ __global__ void __launch_bounds__(TRN_THREADS, MINB) train_rnn_kernel(const Trai
                 for (int b = 0; b < RB; ++b) g += outs[b * 8 + (i - 6 * h)];
             }
             const int gi = O.fcw + i;
-            float m = am[gi], v = av[gi];
-            theta[gi] = adam_update(theta[gi], g, m, v, ac);
-            am[gi] = m; av[gi] = v;
+            if (!first) g += GA[gi];
+            if (lastmb) {
+                float m = am[gi], v = av[gi];
+                theta[gi] = adam_update(theta[gi], g, m, v, ac);
+                am[gi] = m; av[gi] = v;
+            } else {
+                GA[gi] = g;
+            }
         }
         // ================= backward through time, top layer first
         for (int l = L - 1; l >= 0; --l) {
@@ -398,6 +414,14 @@ __global__ void __launch_bounds__(TRN_THREADS, MINB) train_rnn_kernel(const Trai
 #pragma unroll
                     for (int a = 0; a < 4; ++a) {
                         const int gi = base + (j0 + a) * ncol + k0;
+                        if (!first) {
+                            const float4 gp4 = *reinterpret_cast<const float4*>(GA + gi);
+                            acc[a][0] += gp4.x; acc[a][1] += gp4.y; acc[a][2] += gp4.z; acc[a][3] += gp4.w;
+                        }
+                        if (!lastmb) {
+                            *reinterpret_cast<float4*>(GA + gi) = make_float4(acc[a][0], acc[a][1], acc[a][2], acc[a][3]);
+                            continue;
+                        }
                         float4 w = *reinterpret_cast<const float4*>(theta + gi);
                         float4 m = *reinterpret_cast<const float4*>(am + gi);
                         float4 v = *reinterpret_cast<const float4*>(av + gi);
@@ -419,13 +443,19 @@ __global__ void __launch_bounds__(TRN_THREADS, MINB) train_rnn_kernel(const Trai
                     for (int f = 0; f < T; ++f)
                         for (int b = 0; b < RB; ++b) g += gsrc[((size_t)f * RB + b) * GH + j];
                     const int gi = (ih ? O.bih[l] : O.bhh[l]) + j;
-                    float m = am[gi], v = av[gi];
-                    theta[gi] = adam_update(theta[gi], g, m, v, ac);
-                    am[gi] = m; av[gi] = v;
+                    if (!first) g += GA[gi];
+                    if (lastmb) {
+                        float m = am[gi], v = av[gi];
+                        theta[gi] = adam_update(theta[gi], g, m, v, ac);
+                        am[gi] = m; av[gi] = v;
+                    } else {
+                        GA[gi] = g;
+                    }
                 }
             }
             __syncthreads();
         }
+        }   // micro-batches
     }
 }
 
@@ -439,7 +469,7 @@ long long train_rnn_param_count(int kind, int hidden, int layers) {
 long long train_rnn_work_floats(int kind, int hidden, int layers, int window) {
     const long long G = kind == 1 ? 3 : 4, NS = kind == 1 ? 4 : 5, h = hidden, GH = G * h, T = window, L = layers;
     const long long np = (train_rnn_param_count(kind, hidden, layers) + 3) & ~3LL;
-    return np + L * T * RB * h + L * T * RB * NS * h + 2 * T * RB * GH + T * RB * h + T * RB * 8;
+    return np + L * T * RB * h + L * T * RB * NS * h + 2 * T * RB * GH + T * RB * h + T * RB * 8 + np;      // ... + the gradient sums GA
 }
 
 int train_rnn_smem_bytes(int kind, int hidden) {

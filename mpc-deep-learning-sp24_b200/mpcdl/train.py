@@ -17,7 +17,8 @@ Recurrent models (round 2): ``train_model`` of model_scripts/deep_models.py:106-
 csrc/train_rnn_kernels.cu (forward over the window, L1 loss, back-propagation through time, Adam; one CTA per model).  The
 reference's loop differs from the MLP's in two places, both kept: the DataLoader does NOT shuffle (``shuffle=False``, :112),
 so every epoch walks the random_split subset in the same order; and ``init_hidden`` runs before every batch when STATE_F
-(:118-119), so a training batch always starts from h = 0 whether the model is stateful or not."""
+(:118-119), so a training batch always starts from h = 0 whether the model is stateful or not.  Batches of more than 16
+windows (the shipped checkpoints: BATCH_S 16 and 64) run as micro-batches of 16 whose gradients are summed before the Adam step."""
 from __future__ import annotations
 
 import torch

@@ -189,9 +189,10 @@ def test_recurrent_training_entry_points_without_device():
     # GRU_64_4 89 478 and LSTM_64_4 119 174 parameters
     assert lib.mpcdl_train_rnn_param_count(_lib.GRU, 64, 4) == 89478 and lib.mpcdl_train_rnn_param_count(_lib.LSTM, 64, 4) == 119174
     assert lib.mpcdl_train_rnn_param_count(0, 64, 4) == 0 and lib.mpcdl_train_rnn_work_floats(3, 64, 4, 4) == 0
-    # scratch: k-major weight copies + [L][T][16][h] outputs + [L][T][16][4h | 5h] saved gates + 2 [T][16][Gh] gate gradients + dY + the batch
-    assert lib.mpcdl_train_rnn_work_floats(_lib.GRU, 64, 4, 4) == 89480 + 16384 + 65536 + 2 * 12288 + 4096 + 512
-    assert lib.mpcdl_train_rnn_work_floats(_lib.LSTM, 16, 2, 8) == 3944 + 4096 + 20480 + 2 * 8192 + 2048 + 1024
+    # scratch: k-major weight copies + [L][T][16][h] outputs + [L][T][16][4h | 5h] saved gates + 2 [T][16][Gh] gate gradients + dY + the
+    # micro-batch + the gradient sums of a batch of more than 16 rows
+    assert lib.mpcdl_train_rnn_work_floats(_lib.GRU, 64, 4, 4) == 89480 + 16384 + 65536 + 2 * 12288 + 4096 + 512 + 89480
+    assert lib.mpcdl_train_rnn_work_floats(_lib.LSTM, 16, 2, 8) == 3944 + 4096 + 20480 + 2 * 8192 + 2048 + 1024 + 3944
     assert lib.mpcdl_train_rnn_epoch(None, None) == -1
     a = _lib.TrainRnnArgs()
     assert lib.mpcdl_train_rnn_epoch(C.byref(a), None) == -1 and b"non-NULL" in lib.mpcdl_last_error()
@@ -199,7 +200,7 @@ def test_recurrent_training_entry_points_without_device():
         setattr(a, f, 16)
     a.n_models, a.n_samples, a.batch, a.n_rows, a.kind, a.hidden, a.layers, a.window = 1, 100, 16, 100, _lib.GRU, 64, 4, 4
     a.lr, a.beta1, a.beta2, a.eps, a.param_stride = 1e-3, 0.9, 0.999, 1e-8, 89480
-    for field, bad in (("hidden", 48), ("batch", 17), ("window", 9), ("kind", 0)):
+    for field, bad in (("hidden", 48), ("window", 9), ("kind", 0)):
         good = getattr(a, field)
         setattr(a, field, bad)
         assert lib.mpcdl_train_rnn_epoch(C.byref(a), None) == -2 and f"{field}={bad}".encode() in lib.mpcdl_last_error()   # MPCDL_ERR_UNSUPPORTED
