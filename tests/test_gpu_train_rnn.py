@@ -126,7 +126,13 @@ def test_rnn_ensemble_launch_equals_single_launches_bitwise(bags):
             l1 = train.train_epoch(m1, s1, fd, ld, orders[i], 16, 1e-3)
             assert torch.equal(l1[0], loss[i]) and torch.equal(_flat(m1), _flat(ms[i]))
             assert torch.equal(s1.m[0], st.m[i]) and torch.equal(s1.v[0], st.v[i])
+        # in place of initcheck (compute-sanitizer is closed on this pool): the repeat runs with NaN in every word of the scratch
+        # buffer and NaN-poisoned shared memory on every SM -- a read of anything the launch did not write would show
+        from mpcdl import _lib
         st2 = train.AdamState(3, _flat(again[0]).numel(), DEV)
+        k = _lib.GRU if kind == "gru" else _lib.LSTM
+        st2._work = torch.full((3 * _lib.lib.mpcdl_train_rnn_work_floats(k, 64, 2, 4),), float("nan"), device=DEV)
+        torch.ops.mpcdl.debug_poison_smem(fd)
         loss2 = train.train_epoch(again, st2, fd, ld, orders, 16, 1e-3)
         assert torch.equal(loss2, loss) and all(torch.equal(_flat(a), _flat(b)) for a, b in zip(again, ms))
 
