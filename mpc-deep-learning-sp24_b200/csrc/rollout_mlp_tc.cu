@@ -217,6 +217,23 @@ __global__ void __launch_bounds__(mc_threads(TILES), 1) rollout_mlp_tc_kernel(co
                             float v[16];
                             umma::tmem_ld16(tlane + MC_D + u0 + b * 16, v);
                             umma::wait_ld();
+                            if (!X3 && !last) {
+                                // one-pass TF32, hidden layer: ReLU and the operand's rounding in ONE ALU instruction (the epilogue is
+                                // bound by the half-rate ALU, profiles/r02/mlp_tc4): max(bits(t) + 0x1000, 0x1000) as signed integers
+                                // is bits(relu(t)) + 0x1000 for every finite t (negative t and -0 give 0x1000, which the tensor core
+                                // truncates to +0 like the bits of relu(t) = 0 plus the rounding constant): the same operand bits
+                                uint32_t hi[16];
+#pragma unroll
+                                for (int i = 0; i < 16; i += 4) {
+                                    const float4 bb = bl[b * 4 + i / 4];
+                                    hi[i] = (uint32_t)__viaddmax_s32(__float_as_int(v[i] + bb.x), 0x1000, 0x1000);
+                                    hi[i + 1] = (uint32_t)__viaddmax_s32(__float_as_int(v[i + 1] + bb.y), 0x1000, 0x1000);
+                                    hi[i + 2] = (uint32_t)__viaddmax_s32(__float_as_int(v[i + 2] + bb.z), 0x1000, 0x1000);
+                                    hi[i + 3] = (uint32_t)__viaddmax_s32(__float_as_int(v[i + 3] + bb.w), 0x1000, 0x1000);
+                                }
+                                umma::tmem_st16(tlane + MC_A_HI + u0 + b * 16, hi);
+                                continue;
+                            }
 #pragma unroll
                             for (int i = 0; i < 16; i += 4) {
                                 const float4 bb = bl[b * 4 + i / 4];
