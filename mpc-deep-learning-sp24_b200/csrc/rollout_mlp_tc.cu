@@ -35,7 +35,7 @@ __device__ __forceinline__ void mc_issue_layer(uint32_t tcol, uint32_t sb) {
     constexpr uint32_t LBO = 64 / 8 * 128, BLK = K / 4 * LBO;
     constexpr uint32_t IDESC = umma::idesc_tf32(128, 64);
     const uint64_t d0 = umma::smem_desc_kmajor(sb, LBO, 128u);
-    uint32_t acc = 0;
+    uint32_t acc = X3 ? 0u : 1u;       // one-pass TF32: the epilogue has pre-loaded D with the layer's bias, every MMA accumulates
 #pragma unroll
     for (int pass = X3 ? 0 : 2; pass < 3; ++pass) {
 #pragma unroll
@@ -155,6 +155,20 @@ __global__ void __launch_bounds__(mc_threads(TILES), 1) rollout_mlp_tc_kernel(co
         float* const nzb = nact0 + 2 * nact_flip;
         const int etid = tid - ts * EW * 32;
         uint32_t par = 0;
+        // One-pass TF32: the bias is not added in the epilogue -- D is pre-loaded with it (4 tcgen05.st of 16 columns instead of 64
+        // FADDs per thread and layer) and the layer's MMAs accumulate on top; the epilogue's per-unit work is then one VIADDMNMX.
+        auto put_bias = [&](int l, int b_lo, int b_hi) {
+            const float4* bl = reinterpret_cast<const float4*>(sm + L.bias + l * HID + u0);
+            for (int b = b_lo; b < b_hi; ++b) {
+                uint32_t r[16];
+#pragma unroll
+                for (int i = 0; i < 16; i += 4) {
+                    const float4 bb = bl[b * 4 + i / 4];
+                    r[i] = __float_as_uint(bb.x); r[i + 1] = __float_as_uint(bb.y); r[i + 2] = __float_as_uint(bb.z); r[i + 3] = __float_as_uint(bb.w);
+                }
+                umma::tmem_st16(tlane + MC_D + u0 + b * 16, r);
+            }
+        };
         if (ts < tpc)
             for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
                 const int tile = g * tpc + ts;
@@ -184,8 +198,9 @@ __global__ void __launch_bounds__(mc_threads(TILES), 1) rollout_mlp_tc_kernel(co
                         }
                         umma::tmem_st8(tlane + MC_A_HI, hi);
                         if (X3) umma::tmem_st8(tlane + MC_A_LO, lo);
-                        umma::wait_st();
                     }
+                    if (!X3) put_bias(0, 0, UPT / 16);                   // D <- bias of the input layer (this thread's columns)
+                    umma::wait_st();
                     umma::fence_before_sync();
                     mbar_arrive(&opnd[ts]);
                     if (p.nz.enabled) {
@@ -217,6 +232,7 @@ __global__ void __launch_bounds__(mc_threads(TILES), 1) rollout_mlp_tc_kernel(co
                             float v[16];
                             umma::tmem_ld16(tlane + MC_D + u0 + b * 16, v);
                             umma::wait_ld();
+                            if (!X3 && !last) put_bias(l + 1, b, b + 1);     // these D columns are read: the next layer's bias goes in
                             if (!X3 && !last) {
                                 // one-pass TF32, hidden layer: ReLU and the operand's rounding in ONE ALU instruction (the epilogue is
                                 // bound by the half-rate ALU, profiles/r02/mlp_tc4): max(bits(t) + 0x1000, 0x1000) as signed integers
@@ -224,19 +240,13 @@ __global__ void __launch_bounds__(mc_threads(TILES), 1) rollout_mlp_tc_kernel(co
                                 // truncates to +0 like the bits of relu(t) = 0 plus the rounding constant): the same operand bits
                                 uint32_t hi[16];
 #pragma unroll
-                                for (int i = 0; i < 16; i += 4) {
-                                    const float4 bb = bl[b * 4 + i / 4];
-                                    hi[i] = (uint32_t)__viaddmax_s32(__float_as_int(v[i] + bb.x), 0x1000, 0x1000);
-                                    hi[i + 1] = (uint32_t)__viaddmax_s32(__float_as_int(v[i + 1] + bb.y), 0x1000, 0x1000);
-                                    hi[i + 2] = (uint32_t)__viaddmax_s32(__float_as_int(v[i + 2] + bb.z), 0x1000, 0x1000);
-                                    hi[i + 3] = (uint32_t)__viaddmax_s32(__float_as_int(v[i + 3] + bb.w), 0x1000, 0x1000);
-                                }
+                                for (int i = 0; i < 16; ++i) hi[i] = (uint32_t)__viaddmax_s32(__float_as_int(v[i]), 0x1000, 0x1000);
                                 umma::tmem_st16(tlane + MC_A_HI + u0 + b * 16, hi);
                                 continue;
                             }
 #pragma unroll
                             for (int i = 0; i < 16; i += 4) {
-                                const float4 bb = bl[b * 4 + i / 4];
+                                const float4 bb = X3 ? bl[b * 4 + i / 4] : make_float4(0.f, 0.f, 0.f, 0.f);   // TF32: D already holds the bias
                                 v[i] = fmaxf(v[i] + bb.x, 0.f); v[i + 1] = fmaxf(v[i + 1] + bb.y, 0.f);
                                 v[i + 2] = fmaxf(v[i + 2] + bb.z, 0.f); v[i + 3] = fmaxf(v[i + 3] + bb.w, 0.f);
                             }
